@@ -1,0 +1,90 @@
+/* mrz_gpu.h — C-ABI of the B200 rzip pre-processor (libmrz_gpu.so).
+ *
+ * This is the drop-in boundary for modern-rzip's hot path.  Each entry point replaces a piece of
+ * /root/reference/src/rzip.c as cited; plain pointers and sizes only, no CUDA or torch types.
+ * The host side (modern-rzip_b200/host/rzip_fd.c) keeps the reference's
+ *     void rzip_fd(rzip_control *control, int fd_in, int fd_out)         (include/rzip.h:25)
+ * and calls mrz_rzip_chunk() where the reference calls hash_search()      (src/rzip.c:507, :773).
+ *
+ * All functions return 0 on success or a negative MRZ_E_* code; mrz_last_error() gives text.
+ * There is NO CPU fallback: without a CUDA device every compute entry point fails with
+ * MRZ_E_NODEVICE.
+ */
+#ifndef MRZ_GPU_H
+#define MRZ_GPU_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MRZ_OK 0
+#define MRZ_E_NODEVICE (-1)   /* no CUDA device / driver */
+#define MRZ_E_CUDA (-2)       /* a CUDA call failed; see mrz_last_error */
+#define MRZ_E_ARG (-3)        /* bad argument */
+#define MRZ_E_NOMEM (-4)      /* device or pinned-host allocation failed */
+#define MRZ_E_CAPACITY (-5)   /* caller's output buffer too small */
+#define MRZ_E_INTERNAL (-6)   /* device automaton reported an inconsistency */
+
+typedef struct mrz_ctx mrz_ctx;
+
+/* Inputs that src/rzip.c reads from rzip_control / rzip_state (mrzip_private.h:388-416). */
+typedef struct {
+    int32_t level;            /* index into levels[] (rzip.c:65-73, :896): 0..9 */
+    int32_t chunk_bytes;      /* st->chunk_bytes (rzip.c:1006-1008): width of match distances */
+    int64_t victim_round_in;  /* the static in insert_hash (rzip.c:259), carried across chunks */
+    int64_t hash_index[256];  /* st->hash_index (rzip.c:669-673) computed on the host with random() */
+} mrz_params;
+
+/* Outputs of hash_search: st->stats (rzip.c:1108-1115) and stream lengths. */
+typedef struct {
+    int64_t s0_len;           /* stream 0 bytes incl. terminator + 4 CRC bytes (rzip.c:664-665) */
+    int64_t s1_len;           /* stream 1 (literal) bytes */
+    int64_t matches, match_bytes, literals, literal_bytes, tag_hits, tag_misses, inserts;
+    int64_t victim_round_out; /* value of the static after this chunk */
+    int64_t victim_events;    /* number of victim evictions (0 => result independent of victim_round_in) */
+    int64_t final_min_mask;   /* st->minimum_tag_mask at the end (the "Starting sweep for mask" trace) */
+    int64_t n_ops;            /* positions that passed the lookup gate (rzip.c:573) */
+    uint32_t crc32;           /* IEEE CRC32 of the chunk (rzip.c:662) */
+    uint32_t reserved;
+    double ms_kernels;        /* device time of the resident path (CUDA events), milliseconds */
+    double ms_tagscan, ms_automaton, ms_emit;   /* its parts */
+    int64_t gpu_launches;     /* kernels launched for this chunk */
+} mrz_result;
+
+/* library / device ------------------------------------------------------------------------------ */
+int mrz_device_count(void);                       /* >=0, or MRZ_E_NODEVICE */
+const char *mrz_version(void);
+const char *mrz_last_error(const mrz_ctx *ctx);   /* ctx may be NULL: last error of a failed create */
+
+/* A context owns one device's buffers for chunks up to max_chunk bytes: the chunk, the hash table
+ * (levels[].mb_used MiB, rzip.c:518-531), candidate lists, tokens and the two output streams. */
+int mrz_ctx_create(int device, int64_t max_chunk, mrz_ctx **out);
+void mrz_ctx_destroy(mrz_ctx *ctx);
+
+/* hash_search (rzip.c:507-667) for one chunk, host buffers in and out.
+ * Copies the chunk H2D, runs the kernels, copies stream 0 / stream 1 D2H.
+ * s0 needs up to n/2+64 bytes, s1 up to n bytes (pass capacities). */
+int mrz_rzip_chunk(mrz_ctx *ctx, const uint8_t *chunk, int64_t n, const mrz_params *prm,
+                   uint8_t *s0, int64_t s0_cap, uint8_t *s1, int64_t s1_cap, mrz_result *res);
+
+/* The same in three steps, for pipelining and for device-resident timing. */
+int mrz_upload(mrz_ctx *ctx, const uint8_t *chunk, int64_t n);                 /* H2D, synchronous */
+int mrz_run_resident(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result *res); /* kernels only */
+int mrz_download(mrz_ctx *ctx, uint8_t *s0, int64_t s0_cap, uint8_t *s1, int64_t s1_cap); /* D2H */
+
+/* Pinned host memory for the e2e path (cudaHostAlloc); optional. */
+void *mrz_host_alloc(int64_t bytes);
+void mrz_host_free(void *p);
+
+/* Building blocks exposed for parity tests (each is also used inside mrz_run_resident). */
+/* single_full_tag for every position (rzip.c:348-358): tags[p] for p in [0, n-30). */
+int mrz_debug_tags(mrz_ctx *ctx, int64_t n, const int64_t hash_index[256], int64_t *tags_out, int64_t count);
+/* per-chunk CRC32 as gcry_md_write(crc_handle) accumulates it (rzip.c:494, :648-662) */
+int mrz_debug_crc32(mrz_ctx *ctx, int64_t n, uint32_t *crc_out);
+/* un-split match tokens of the last run: triples (pos, len, ofs) */
+int mrz_debug_tokens(mrz_ctx *ctx, int64_t *triples, int64_t cap, int64_t *count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,474 @@
+// mrz_gpu.cu — C-ABI of libmrz_gpu.so (see include/mrz_gpu.h) and the per-chunk orchestration.
+//
+// Pipeline for one chunk (replaces hash_search, rzip.c:507-667):
+//   H2D chunk -> memset table (rzip.c:518-519) -> { tag_scan segment -> automaton } until p == end
+//   -> item sizes -> two exclusive scans -> stream 0 / stream 1 emission + CRC32 -> D2H streams.
+// No CPU fallback: every entry point needs a CUDA device.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+
+#include "../../include/mrz_gpu.h"
+#include "mrz_common.cuh"
+
+extern "C" {
+void mrz_launch_scan(const u8 *, const i64 *, AutoState *, int *, i64 *, u32 *, i64 *, int, cudaStream_t);
+void mrz_launch_debug_tags(const u8 *, const i64 *, i64, i64, i64 *, cudaStream_t);
+void mrz_launch_automaton(const u8 *, Slot *, const i64 *, AutoState *, const i64 *, const u32 *, const i64 *,
+                          Token *, cudaStream_t);
+void mrz_crc_upload_consts(const void *);
+void mrz_launch_crc(const u8 *, i64, u32 *, u32 *, u32 *, cudaStream_t, int *);
+void mrz_launch_exclusive_scan(const i64 *, i64 *, i64, i64 *, i64 *, cudaStream_t, int *);
+void mrz_launch_item_sizes(const Token *, i64, i64, int, i64 *, i64 *, EmitTotals *, cudaStream_t);
+void mrz_launch_emit(const u8 *, const Token *, i64, i64, int, const i64 *, const i64 *, i64, u8 *, u8 *,
+                     const u32 *, cudaStream_t, int *);
+}
+
+static const struct { i64 mb; int freq; int chain; } kLevels[10] = {  // rzip.c:65-73
+    {1, 4, 1}, {2, 4, 2}, {4, 4, 2}, {8, 4, 2}, {16, 4, 3}, {32, 4, 4}, {32, 2, 6}, {64, 1, 16}, {64, 1, 32}, {64, 1, 128}};
+
+static thread_local std::string g_err;
+
+struct mrz_ctx {
+    int device;
+    i64 max_chunk;
+    cudaStream_t stream;
+    cudaEvent_t ev[4];
+    // device buffers
+    u8 *d_buf_alloc, *d_buf;  // chunk with MRZ_PAD slack on both sides
+    Slot *d_tab; i64 tab_slots;
+    i64 *d_hidx;
+    AutoState *d_st;
+    int *d_tile_cnt; i64 *d_tile_off; u32 *d_cand_pos; i64 *d_cand_tag;
+    Token *d_toks; i64 tok_cap;
+    i64 *d_a0, *d_a1, *d_off0, *d_off1, *d_bsum; i64 item_cap;
+    EmitTotals *d_tot;
+    u8 *d_s0; i64 s0_cap; u8 *d_s1; i64 s1_cap;
+    u32 *d_crc_part, *d_crc_part2, *d_crc_misc;  // misc[0]=tail, misc[1]=final
+    // host staging
+    u32 *h_crc; i64 h_crc_cap;
+    // last run
+    i64 last_n, last_s0, last_s1, last_ntok;
+    std::string err;
+};
+
+#define CK(call)                                                                                    \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess) {                                                                    \
+            char b_[512];                                                                           \
+            snprintf(b_, sizeof b_, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            if (ctx) ctx->err = b_;                                                                 \
+            g_err = b_;                                                                             \
+            return e_ == cudaErrorMemoryAllocation ? MRZ_E_NOMEM : MRZ_E_CUDA;                      \
+        }                                                                                           \
+    } while (0)
+
+// ---- CRC32 shift operators over GF(2) (host) ---------------------------------------------------
+struct CrcConstHost {
+    u32 tab[4][256];
+    u32 shift_sub[5][32];
+    u32 shift_blk[5][32];
+};
+static CrcConstHost g_crc;
+static u32 g_byte_mat[32];  // advance a raw CRC register over one zero byte
+static bool g_crc_ready = false;
+
+static u32 h_apply(const u32 *m, u32 v) {
+    u32 r = 0;
+    for (int b = 0; v; v >>= 1, b++)
+        if (v & 1) r ^= m[b];
+    return r;
+}
+static void h_square(u32 *dst, const u32 *m) {
+    for (int b = 0; b < 32; b++) dst[b] = h_apply(m, m[b]);
+}
+static void h_mul(u32 *dst, const u32 *a, const u32 *b) {  // dst = a o b
+    u32 t[32];
+    for (int i = 0; i < 32; i++) t[i] = h_apply(a, b[i]);
+    memcpy(dst, t, sizeof t);
+}
+static void shift_matrix(u32 *out, u64 nbytes) {  // operator: register -> register after nbytes zero bytes
+    u32 res[32], cur[32], tmp[32];
+    for (int b = 0; b < 32; b++) res[b] = 1u << b;
+    memcpy(cur, g_byte_mat, sizeof cur);
+    while (nbytes) {
+        if (nbytes & 1) h_mul(res, cur, res);
+        h_square(tmp, cur);
+        memcpy(cur, tmp, sizeof cur);
+        nbytes >>= 1;
+    }
+    memcpy(out, res, sizeof res);
+}
+static u32 crc_shift(u32 crc, u64 nbytes) {
+    u32 m[32];
+    shift_matrix(m, nbytes);
+    return h_apply(m, crc);
+}
+static void crc_host_init() {
+    if (g_crc_ready) return;
+    for (u32 i = 0; i < 256; i++) {
+        u32 c = i;
+        for (int k = 0; k < 8; k++) c = (c >> 1) ^ (0xEDB88320u & (0u - (c & 1)));
+        g_crc.tab[0][i] = c;
+    }
+    for (u32 i = 0; i < 256; i++)
+        for (int t = 1; t < 4; t++)
+            g_crc.tab[t][i] = (g_crc.tab[t - 1][i] >> 8) ^ g_crc.tab[0][g_crc.tab[t - 1][i] & 255];
+    // one zero bit: reflected register shifts right, bit 0 feeds the polynomial
+    u32 bit[32], m2[32], m4[32];
+    bit[0] = 0xEDB88320u;
+    for (int b = 1; b < 32; b++) bit[b] = 1u << (b - 1);
+    h_square(m2, bit);
+    h_square(m4, m2);
+    h_square(g_byte_mat, m4);
+    for (int j = 0; j < 5; j++) {
+        shift_matrix(g_crc.shift_sub[j], (u64)512 << j);
+        shift_matrix(g_crc.shift_blk[j], (u64)16384 << j);
+    }
+    g_crc_ready = true;
+}
+
+// ---- library -----------------------------------------------------------------------------------
+extern "C" const char *mrz_version(void) { return "mrz_gpu 0.1 (sm_100a)"; }
+
+extern "C" int mrz_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        g_err = std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e);
+        return MRZ_E_NODEVICE;
+    }
+    return n;
+}
+
+extern "C" const char *mrz_last_error(const mrz_ctx *ctx) { return ctx ? ctx->err.c_str() : g_err.c_str(); }
+
+extern "C" void *mrz_host_alloc(int64_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+    return p;
+}
+extern "C" void mrz_host_free(void *p) {
+    if (p) cudaFreeHost(p);
+}
+
+static int ensure_tokens(mrz_ctx *ctx, i64 cap) {
+    if (cap <= ctx->tok_cap) return 0;
+    if (ctx->d_toks) cudaFree(ctx->d_toks);
+    ctx->d_toks = nullptr; ctx->tok_cap = 0;
+    CK(cudaMalloc(&ctx->d_toks, (size_t)cap * sizeof(Token)));
+    ctx->tok_cap = cap;
+    return 0;
+}
+static int ensure_items(mrz_ctx *ctx, i64 items) {
+    if (items + 2 <= ctx->item_cap) return 0;
+    i64 cap = items + 2 + items / 4;
+    cudaFree(ctx->d_a0); cudaFree(ctx->d_a1); cudaFree(ctx->d_off0); cudaFree(ctx->d_off1); cudaFree(ctx->d_bsum);
+    ctx->d_a0 = ctx->d_a1 = ctx->d_off0 = ctx->d_off1 = ctx->d_bsum = nullptr; ctx->item_cap = 0;
+    CK(cudaMalloc(&ctx->d_a0, (size_t)cap * 8));
+    CK(cudaMalloc(&ctx->d_a1, (size_t)cap * 8));
+    CK(cudaMalloc(&ctx->d_off0, (size_t)cap * 8));
+    CK(cudaMalloc(&ctx->d_off1, (size_t)cap * 8));
+    CK(cudaMalloc(&ctx->d_bsum, (size_t)(cap / 4096 + 2) * 8));
+    ctx->item_cap = cap;
+    return 0;
+}
+static int ensure_s0(mrz_ctx *ctx, i64 bytes) {
+    if (bytes <= ctx->s0_cap) return 0;
+    if (ctx->d_s0) cudaFree(ctx->d_s0);
+    ctx->d_s0 = nullptr; ctx->s0_cap = 0;
+    i64 cap = bytes + bytes / 4 + 4096;
+    CK(cudaMalloc(&ctx->d_s0, (size_t)cap));
+    ctx->s0_cap = cap;
+    return 0;
+}
+
+extern "C" void mrz_ctx_destroy(mrz_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaFree(ctx->d_buf_alloc); cudaFree(ctx->d_tab); cudaFree(ctx->d_hidx); cudaFree(ctx->d_st);
+    cudaFree(ctx->d_tile_cnt); cudaFree(ctx->d_tile_off); cudaFree(ctx->d_cand_pos); cudaFree(ctx->d_cand_tag);
+    cudaFree(ctx->d_toks); cudaFree(ctx->d_a0); cudaFree(ctx->d_a1); cudaFree(ctx->d_off0); cudaFree(ctx->d_off1);
+    cudaFree(ctx->d_bsum); cudaFree(ctx->d_tot); cudaFree(ctx->d_s0); cudaFree(ctx->d_s1);
+    cudaFree(ctx->d_crc_part); cudaFree(ctx->d_crc_part2); cudaFree(ctx->d_crc_misc);
+    free(ctx->h_crc);
+    for (auto &e : ctx->ev)
+        if (e) cudaEventDestroy(e);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
+    CK(cudaSetDevice(device));
+    crc_host_init();
+    mrz_crc_upload_consts(&g_crc);
+    CK(cudaGetLastError());
+    ctx->device = device;
+    ctx->max_chunk = max_chunk;
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    for (auto &e : ctx->ev) CK(cudaEventCreate(&e));
+    CK(cudaMalloc(&ctx->d_buf_alloc, (size_t)max_chunk + 2 * MRZ_PAD + 64));
+    ctx->d_buf = ctx->d_buf_alloc + MRZ_PAD;
+    CK(cudaMemset(ctx->d_buf_alloc, 0, MRZ_PAD));
+    ctx->tab_slots = (i64)64 * 65536;  // largest levels[].mb_used = 64 MiB
+    CK(cudaMalloc(&ctx->d_tab, (size_t)ctx->tab_slots * sizeof(Slot)));
+    CK(cudaMalloc(&ctx->d_hidx, 256 * 8));
+    CK(cudaMalloc(&ctx->d_st, sizeof(AutoState)));
+    CK(cudaMalloc(&ctx->d_tile_cnt, (SEG_MAX_TILES + 1) * sizeof(int)));
+    CK(cudaMalloc(&ctx->d_tile_off, (SEG_MAX_TILES + 2) * sizeof(i64)));
+    CK(cudaMalloc(&ctx->d_cand_pos, (size_t)(SEG_CAND_CAP + 64) * sizeof(u32)));
+    CK(cudaMalloc(&ctx->d_cand_tag, (size_t)(SEG_CAND_CAP + 64) * sizeof(i64)));
+    CK(cudaMalloc(&ctx->d_tot, sizeof(EmitTotals)));
+    CK(cudaMalloc(&ctx->d_s1, (size_t)max_chunk + 64));
+    ctx->s1_cap = max_chunk + 64;
+    i64 nblk = max_chunk / 16384 + 1;
+    CK(cudaMalloc(&ctx->d_crc_part, (size_t)nblk * 4));
+    CK(cudaMalloc(&ctx->d_crc_part2, (size_t)(nblk / 32 + 1) * 4));
+    CK(cudaMalloc(&ctx->d_crc_misc, 16));
+    ctx->h_crc_cap = nblk / 32 + 64;
+    ctx->h_crc = (u32 *)malloc((size_t)ctx->h_crc_cap * 4);
+    if (!ctx->h_crc) return MRZ_E_NOMEM;
+    int rc;
+    if ((rc = ensure_tokens(ctx, max_chunk / 256 + 1024))) return rc;
+    if ((rc = ensure_items(ctx, max_chunk / 256 + 1024))) return rc;
+    if ((rc = ensure_s0(ctx, max_chunk / 32 + 4096))) return rc;
+    return 0;
+}
+
+extern "C" int mrz_ctx_create(int device, int64_t max_chunk, mrz_ctx **out) {
+    if (!out || max_chunk < 0) return MRZ_E_ARG;
+    *out = nullptr;
+    int n = mrz_device_count();
+    if (n <= 0) {
+        if (n == 0) g_err = "no CUDA device";
+        return MRZ_E_NODEVICE;
+    }
+    if (device < 0 || device >= n) { g_err = "bad device index"; return MRZ_E_ARG; }
+    mrz_ctx *ctx = new mrz_ctx();
+    int rc = ctx_create_impl(ctx, device, max_chunk);
+    if (rc) {
+        g_err = ctx->err;
+        mrz_ctx_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return 0;
+}
+
+extern "C" int mrz_upload(mrz_ctx *ctx, const uint8_t *chunk, int64_t n) {
+    if (!ctx || n < 0 || n > ctx->max_chunk || (n && !chunk)) return MRZ_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (n) CK(cudaMemcpyAsync(ctx->d_buf, chunk, (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_buf + n, 0, MRZ_PAD + 64, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// One attempt with the current token capacity.  Returns 1 when the token buffer overflowed.
+static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res) {
+    cudaStream_t s = ctx->stream;
+    const int L = prm->level;
+    AutoState h;
+    memset(&h, 0, sizeof h);
+    h.n = n;
+    h.end = n - MRZ_MIN_MATCH;
+    i64 hashsize = kLevels[L].mb * (1048576 / 16);
+    int bits = 0;
+    while (((i64)1 << bits) < hashsize) bits++;  // rzip.c:521-523
+    h.hsize = (i64)1 << bits;
+    h.hmask = h.hsize - 1;
+    h.limit = h.hsize / 3 * 2;  // rzip.c:529
+    h.chain = kLevels[L].chain;
+    h.min_mask = h.ins_mask = ((i64)1 << kLevels[L].freq) - 1;  // rzip.c:509, :533
+    h.victim_round = prm->victim_round_in;
+    h.tok_cap = ctx->tok_cap;
+    h.done = h.end <= 0 ? 1 : 0;
+    int launches = 0;
+    float ms_scan = 0, ms_auto = 0, ms_emit = 0, ms_total = 0;
+
+    CK(cudaEventRecord(ctx->ev[0], s));
+    CK(cudaMemcpyAsync(ctx->d_hidx, prm->hash_index, 256 * 8, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(ctx->d_st, &h, sizeof h, cudaMemcpyHostToDevice, s));
+    CK(cudaMemsetAsync(ctx->d_tab, 0, (size_t)h.hsize * sizeof(Slot), s));  // rzip.c:518-519
+    CK(cudaMemsetAsync(ctx->d_tot, 0, sizeof(EmitTotals), s));
+    launches += 2;
+    // CRC of the chunk (independent of the automaton)
+    mrz_launch_crc(ctx->d_buf, n, ctx->d_crc_part, ctx->d_crc_part2, ctx->d_crc_misc, s, &launches);
+
+    while (!h.done) {
+        int k = __builtin_popcountll((unsigned long long)h.min_mask);
+        i64 len = (i64)SEG_CAND_TARGET << (k < 20 ? k : 20);
+        i64 maxlen = (i64)SEG_MAX_TILES * SCAN_TILE;
+        if (len > maxlen) len = maxlen;
+        i64 span = h.end + 1 - (h.p + 1);
+        if (span > len) span = len;
+        int tiles = (int)((span + SCAN_TILE - 1) / SCAN_TILE);
+        CK(cudaEventRecord(ctx->ev[1], s));
+        mrz_launch_scan(ctx->d_buf, ctx->d_hidx, ctx->d_st, ctx->d_tile_cnt, ctx->d_tile_off, ctx->d_cand_pos,
+                        ctx->d_cand_tag, tiles, s);
+        CK(cudaEventRecord(ctx->ev[2], s));
+        mrz_launch_automaton(ctx->d_buf, ctx->d_tab, ctx->d_hidx, ctx->d_st, ctx->d_tile_off, ctx->d_cand_pos,
+                             ctx->d_cand_tag, ctx->d_toks, s);
+        CK(cudaEventRecord(ctx->ev[3], s));
+        launches += 4;
+        i64 prev_p = h.p;
+        CK(cudaMemcpyAsync(&h, ctx->d_st, sizeof h, cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        CK(cudaGetLastError());
+        float a = 0, b = 0;
+        cudaEventElapsedTime(&a, ctx->ev[1], ctx->ev[2]);
+        cudaEventElapsedTime(&b, ctx->ev[2], ctx->ev[3]);
+        ms_scan += a;
+        ms_auto += b;
+        if (h.error == 2) return 1;
+        if (h.error) {
+            char m[128];
+            snprintf(m, sizeof m, "device automaton error %d at p=%lld", h.error, (long long)h.p);
+            ctx->err = m;
+            return MRZ_E_INTERNAL;
+        }
+        if (!h.done && h.p <= prev_p) {
+            ctx->err = "automaton made no progress";
+            return MRZ_E_INTERNAL;
+        }
+    }
+
+    // ---- emission ----
+    CK(cudaEventRecord(ctx->ev[1], s));
+    i64 m = h.ntok, items = m + 1;
+    int rc;
+    if ((rc = ensure_items(ctx, items))) return rc;
+    mrz_launch_item_sizes(ctx->d_toks, m, n, prm->chunk_bytes, ctx->d_a0, ctx->d_a1, ctx->d_tot, s);
+    launches++;
+    mrz_launch_exclusive_scan(ctx->d_a0, ctx->d_off0, items, ctx->d_bsum, ctx->d_off0 + items, s, &launches);
+    mrz_launch_exclusive_scan(ctx->d_a1, ctx->d_off1, items, ctx->d_bsum, ctx->d_off1 + items, s, &launches);
+    i64 totals[2];
+    CK(cudaMemcpyAsync(&totals[0], ctx->d_off0 + items, 8, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(&totals[1], ctx->d_off1 + items, 8, cudaMemcpyDeviceToHost, s));
+    // CRC partials -> host combine
+    i64 nblk = n / 16384, ngrp = nblk / 32, nrest = nblk - ngrp * 32;
+    u32 tailcrc = 0;
+    if (ngrp) CK(cudaMemcpyAsync(ctx->h_crc, ctx->d_crc_part2, (size_t)ngrp * 4, cudaMemcpyDeviceToHost, s));
+    if (nrest)
+        CK(cudaMemcpyAsync(ctx->h_crc + ngrp, ctx->d_crc_part + ngrp * 32, (size_t)nrest * 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(&tailcrc, ctx->d_crc_misc, 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    u32 raw = 0;
+    {
+        u32 m512k[32], m16k[32];
+        shift_matrix(m512k, 512 * 1024);
+        shift_matrix(m16k, 16384);
+        for (i64 g = 0; g < ngrp; g++) raw = h_apply(m512k, raw) ^ ctx->h_crc[g];
+        for (i64 r = 0; r < nrest; r++) raw = h_apply(m16k, raw) ^ ctx->h_crc[ngrp + r];
+        i64 tl = n - nblk * 16384;
+        raw = crc_shift(raw, (u64)tl) ^ tailcrc;
+    }
+    u32 crc = raw ^ crc_shift(0xFFFFFFFFu, (u64)n) ^ 0xFFFFFFFFu;
+    CK(cudaMemcpyAsync(ctx->d_crc_misc + 1, &crc, 4, cudaMemcpyHostToDevice, s));
+    if ((rc = ensure_s0(ctx, totals[0]))) return rc;
+    mrz_launch_emit(ctx->d_buf, ctx->d_toks, m, n, prm->chunk_bytes, ctx->d_off0, ctx->d_off1, totals[1], ctx->d_s0,
+                    ctx->d_s1, ctx->d_crc_misc + 1, s, &launches);
+    EmitTotals tot;
+    CK(cudaMemcpyAsync(&tot, ctx->d_tot, sizeof tot, cudaMemcpyDeviceToHost, s));
+    CK(cudaEventRecord(ctx->ev[2], s));
+    CK(cudaStreamSynchronize(s));
+    CK(cudaGetLastError());
+    cudaEventElapsedTime(&ms_emit, ctx->ev[1], ctx->ev[2]);
+    cudaEventElapsedTime(&ms_total, ctx->ev[0], ctx->ev[2]);
+
+    memset(res, 0, sizeof *res);
+    res->s0_len = totals[0];
+    res->s1_len = totals[1];
+    res->matches = tot.matches;
+    res->match_bytes = tot.match_bytes;
+    res->literals = tot.literals;
+    res->literal_bytes = totals[1];
+    res->tag_hits = h.tag_hits;
+    res->tag_misses = h.tag_misses;
+    res->inserts = h.inserts;
+    res->victim_round_out = h.victim_round;
+    res->victim_events = h.victim_events;
+    res->final_min_mask = h.min_mask;
+    res->n_ops = h.n_ops;
+    res->crc32 = crc;
+    res->ms_kernels = ms_total;
+    res->ms_tagscan = ms_scan;
+    res->ms_automaton = ms_auto;
+    res->ms_emit = ms_emit;
+    res->gpu_launches = launches;
+    ctx->last_n = n; ctx->last_s0 = totals[0]; ctx->last_s1 = totals[1]; ctx->last_ntok = m;
+    return 0;
+}
+
+extern "C" int mrz_run_resident(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result *res) {
+    if (!ctx || !prm || !res || n < 0 || n > ctx->max_chunk) return MRZ_E_ARG;
+    if (prm->level < 0 || prm->level > 9 || prm->chunk_bytes < 1 || prm->chunk_bytes > 8) return MRZ_E_ARG;
+    if (prm->victim_round_in < 0 || prm->victim_round_in >= kLevels[prm->level].chain) return MRZ_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    for (;;) {
+        int rc = run_once(ctx, n, prm, res);
+        if (rc != 1) return rc;
+        // token buffer overflowed: grow (bounded by one match per 31 bytes) and redo the chunk
+        i64 cap = ctx->tok_cap * 8;
+        i64 hard = n / MRZ_MIN_MATCH + 16;
+        if (cap > hard) cap = hard;
+        if (cap <= ctx->tok_cap) { ctx->err = "token capacity exhausted"; return MRZ_E_INTERNAL; }
+        if ((rc = ensure_tokens(ctx, cap))) return rc;
+    }
+}
+
+extern "C" int mrz_download(mrz_ctx *ctx, uint8_t *s0, int64_t s0_cap, uint8_t *s1, int64_t s1_cap) {
+    if (!ctx) return MRZ_E_ARG;
+    if (ctx->last_s0 > s0_cap || ctx->last_s1 > s1_cap) return MRZ_E_CAPACITY;
+    CK(cudaSetDevice(ctx->device));
+    if (ctx->last_s0) CK(cudaMemcpyAsync(s0, ctx->d_s0, (size_t)ctx->last_s0, cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->last_s1) CK(cudaMemcpyAsync(s1, ctx->d_s1, (size_t)ctx->last_s1, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int mrz_rzip_chunk(mrz_ctx *ctx, const uint8_t *chunk, int64_t n, const mrz_params *prm, uint8_t *s0,
+                              int64_t s0_cap, uint8_t *s1, int64_t s1_cap, mrz_result *res) {
+    int rc = mrz_upload(ctx, chunk, n);
+    if (rc) return rc;
+    rc = mrz_run_resident(ctx, n, prm, res);
+    if (rc) return rc;
+    return mrz_download(ctx, s0, s0_cap, s1, s1_cap);
+}
+
+extern "C" int mrz_debug_tags(mrz_ctx *ctx, int64_t n, const int64_t hash_index[256], int64_t *tags_out,
+                              int64_t count) {
+    if (!ctx || count < 0 || count + 30 > n) return MRZ_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    i64 *d_tags = nullptr;
+    CK(cudaMalloc(&d_tags, (size_t)(count + 1) * 8));
+    cudaError_t e = cudaMemcpyAsync(ctx->d_hidx, hash_index, 256 * 8, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) {
+        mrz_launch_debug_tags(ctx->d_buf, ctx->d_hidx, n, count, d_tags, ctx->stream);
+        e = cudaMemcpyAsync(tags_out, d_tags, (size_t)count * 8, cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_tags);
+    CK(e);
+    return 0;
+}
+
+extern "C" int mrz_debug_crc32(mrz_ctx *ctx, int64_t n, uint32_t *crc_out) {
+    if (!ctx || !crc_out) return MRZ_E_ARG;
+    (void)n;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpy(crc_out, ctx->d_crc_misc + 1, 4, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int mrz_debug_tokens(mrz_ctx *ctx, int64_t *triples, int64_t cap, int64_t *count) {
+    if (!ctx || !count) return MRZ_E_ARG;
+    *count = ctx->last_ntok;
+    if (ctx->last_ntok > cap) return MRZ_E_CAPACITY;
+    CK(cudaSetDevice(ctx->device));
+    if (ctx->last_ntok)
+        CK(cudaMemcpy(triples, ctx->d_toks, (size_t)ctx->last_ntok * sizeof(Token), cudaMemcpyDeviceToHost));
+    return 0;
+}

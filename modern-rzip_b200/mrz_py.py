@@ -1,0 +1,153 @@
+"""ctypes view of the C-ABI in include/mrz_gpu.h (used by tests/, bench.py and __graft_entry__.py).
+
+The product's host side is C (host/); this module only lets the Python harness call the same
+entry points.  It never falls back to a CPU implementation: if libmrz_gpu.so is missing or no CUDA
+device is present, calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libmrz_gpu.so")
+
+DECLARED_SYMBOLS = [
+    "mrz_device_count", "mrz_version", "mrz_last_error", "mrz_ctx_create", "mrz_ctx_destroy",
+    "mrz_rzip_chunk", "mrz_upload", "mrz_run_resident", "mrz_download", "mrz_host_alloc", "mrz_host_free",
+    "mrz_debug_tags", "mrz_debug_crc32", "mrz_debug_tokens",
+]
+
+
+class MrzParams(C.Structure):
+    _fields_ = [("level", C.c_int32), ("chunk_bytes", C.c_int32), ("victim_round_in", C.c_int64),
+                ("hash_index", C.c_int64 * 256)]
+
+
+class MrzResult(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in (
+        "s0_len", "s1_len", "matches", "match_bytes", "literals", "literal_bytes", "tag_hits", "tag_misses",
+        "inserts", "victim_round_out", "victim_events", "final_min_mask", "n_ops")] + [
+        ("crc32", C.c_uint32), ("reserved", C.c_uint32),
+        ("ms_kernels", C.c_double), ("ms_tagscan", C.c_double), ("ms_automaton", C.c_double),
+        ("ms_emit", C.c_double), ("gpu_launches", C.c_int64)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class MrzError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise MrzError("libmrz_gpu.so not built (run `make -C modern-rzip_b200`); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        L.mrz_version.restype = C.c_char_p
+        L.mrz_last_error.restype = C.c_char_p
+        L.mrz_last_error.argtypes = [C.c_void_p]
+        L.mrz_ctx_create.argtypes = [C.c_int, C.c_int64, C.POINTER(C.c_void_p)]
+        L.mrz_ctx_destroy.argtypes = [C.c_void_p]
+        L.mrz_rzip_chunk.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(MrzParams), C.c_void_p, C.c_int64,
+                                     C.c_void_p, C.c_int64, C.POINTER(MrzResult)]
+        L.mrz_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        L.mrz_run_resident.argtypes = [C.c_void_p, C.c_int64, C.POINTER(MrzParams), C.POINTER(MrzResult)]
+        L.mrz_download.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
+        L.mrz_host_alloc.restype = C.c_void_p
+        L.mrz_host_alloc.argtypes = [C.c_int64]
+        L.mrz_host_free.argtypes = [C.c_void_p]
+        L.mrz_debug_tags.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_int64]
+        L.mrz_debug_crc32.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_uint32)]
+        L.mrz_debug_tokens.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
+        _lib = L
+    return _lib
+
+
+def make_params(level, chunk_bytes, hash_index, victim_round_in=0):
+    p = MrzParams()
+    p.level = level
+    p.chunk_bytes = chunk_bytes
+    p.victim_round_in = victim_round_in
+    for i in range(256):
+        p.hash_index[i] = int(hash_index[i])
+    return p
+
+
+class PinnedBuffer:
+    """cudaHostAlloc'd byte buffer exposed as a numpy array."""
+
+    def __init__(self, nbytes):
+        self.ptr = lib().mrz_host_alloc(max(1, nbytes))
+        if not self.ptr:
+            raise MrzError("mrz_host_alloc failed")
+        self.nbytes = nbytes
+        self.array = np.ctypeslib.as_array(C.cast(self.ptr, C.POINTER(C.c_uint8)), shape=(max(1, nbytes),))
+
+    def free(self):
+        if self.ptr:
+            lib().mrz_host_free(self.ptr)
+            self.ptr = None
+
+
+class Context:
+    def __init__(self, device=0, max_chunk=1 << 28):
+        self.h = C.c_void_p()
+        rc = lib().mrz_ctx_create(device, max_chunk, C.byref(self.h))
+        if rc:
+            raise MrzError("mrz_ctx_create rc=%d: %s" % (rc, lib().mrz_last_error(None).decode()))
+        self.max_chunk = max_chunk
+
+    def close(self):
+        if self.h:
+            lib().mrz_ctx_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def _check(self, rc, what):
+        if rc:
+            raise MrzError("%s rc=%d: %s" % (what, rc, lib().mrz_last_error(self.h).decode()))
+
+    def upload(self, arr):
+        arr = np.ascontiguousarray(arr, dtype=np.uint8)
+        self._check(lib().mrz_upload(self.h, arr.ctypes.data if arr.size else None, arr.size), "mrz_upload")
+
+    def run_resident(self, n, params):
+        res = MrzResult()
+        self._check(lib().mrz_run_resident(self.h, n, C.byref(params), C.byref(res)), "mrz_run_resident")
+        return res
+
+    def download(self, res, s0=None, s1=None):
+        s0 = np.empty(max(1, res.s0_len), dtype=np.uint8) if s0 is None else s0
+        s1 = np.empty(max(1, res.s1_len), dtype=np.uint8) if s1 is None else s1
+        self._check(lib().mrz_download(self.h, s0.ctypes.data, s0.size, s1.ctypes.data, s1.size), "mrz_download")
+        return s0[:res.s0_len], s1[:res.s1_len]
+
+    def rzip_chunk(self, arr, params, s0=None, s1=None):
+        """hash_search for one chunk through the host-buffer entry point (H2D + kernels + D2H)."""
+        arr = np.ascontiguousarray(arr, dtype=np.uint8)
+        n = arr.size
+        s0 = np.empty(n // 2 + 64, dtype=np.uint8) if s0 is None else s0
+        s1 = np.empty(n + 16, dtype=np.uint8) if s1 is None else s1
+        res = MrzResult()
+        rc = lib().mrz_rzip_chunk(self.h, arr.ctypes.data if n else None, n, C.byref(params), s0.ctypes.data, s0.size,
+                                  s1.ctypes.data, s1.size, C.byref(res))
+        self._check(rc, "mrz_rzip_chunk")
+        return res, s0[:res.s0_len], s1[:res.s1_len]
+
+    def debug_tags(self, n, hash_index, count):
+        hi = (C.c_int64 * 256)(*[int(x) for x in hash_index])
+        out = np.empty(count, dtype=np.int64)
+        self._check(lib().mrz_debug_tags(self.h, n, hi, out.ctypes.data, count), "mrz_debug_tags")
+        return out
+
+    def debug_tokens(self):
+        cnt = C.c_int64()
+        lib().mrz_debug_tokens(self.h, None, 0, C.byref(cnt))
+        out = np.empty((max(1, cnt.value), 3), dtype=np.int64)
+        self._check(lib().mrz_debug_tokens(self.h, out.ctypes.data, cnt.value, C.byref(cnt)), "mrz_debug_tokens")
+        return out[:cnt.value]

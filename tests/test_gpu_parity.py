@@ -1,0 +1,130 @@
+"""GPU parity: the CUDA path through the C-ABI vs the CPU oracle, bit-exact (streams, counters, victim carry)."""
+import numpy as np
+import pytest
+
+import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+STAT_KEYS = ("matches", "match_bytes", "literals", "literal_bytes", "tag_hits", "tag_misses", "inserts")
+
+
+def first_token_diff(ctx, ref):
+    got = [tuple(int(x) for x in r) for r in ctx.debug_tokens()]
+    want = [t for t in ref["tokens"] if t[2] >= 0]
+    for i, (g, w) in enumerate(zip(got, want)):
+        if g != w:
+            return "token %d: got %r want %r" % (i, g, w)
+    return "token counts: got %d want %d" % (len(got), len(want))
+
+
+def check(ctx, data, level=7, vr_in=0, cb=None):
+    import mrz_py
+    data = H.as_u8(data)
+    cb = cb or H.chunk_bytes(data.size)
+    hidx = H.hash_index()
+    ref = H.oracle_chunk(data, level=level, cb=cb, vr_in=vr_in, hidx=hidx, want_tokens=True)
+    prm = mrz_py.make_params(level, cb, hidx, vr_in)
+    res, s0, s1 = ctx.rzip_chunk(data, prm)
+    if s0.tobytes() != ref["s0"] or s1.tobytes() != ref["s1"]:
+        pytest.fail("stream mismatch (n=%d level=%d): %s" % (data.size, level, first_token_diff(ctx, ref)))
+    for k in STAT_KEYS:
+        assert getattr(res, k) == ref["stats"][k], k
+    assert res.victim_round_out == ref["vr_out"]
+    assert res.victim_events == ref["stats"]["victim_events"]
+    assert res.final_min_mask == ref["stats"]["final_min_mask"]
+    assert res.n_ops == ref["stats"]["lookups"]
+    assert res.gpu_launches > 0
+    return res, ref
+
+
+@pytest.mark.parametrize("n", [0, 1, 30, 31, 32, 33, 62, 63, 64, 650, 8191, 8192, 8193, 8222, 8223, 8224, 100003])
+def test_tiny_and_ragged(gpu_ctx, n):
+    seq = (b"abcdefghijklmnopqrstuvwxyz012345" * (n // 32 + 1))[:n]
+    check(gpu_ctx, seq)
+    check(gpu_ctx, H.gen_random(n, seed=n + 1) if n else b"")
+
+
+def test_survey_650_byte_example(gpu_ctx):
+    import random
+    random.seed(1)
+    A = bytes(random.getrandbits(8) for _ in range(300))
+    B = bytes(random.getrandbits(8) for _ in range(100))
+    Cc = bytes(random.getrandbits(8) for _ in range(50))
+    res, ref = check(gpu_ctx, A + B + A[:200] + Cc)
+    assert res.matches == 1 and res.s0_len == 18 and res.s1_len == 450
+
+
+def test_random_with_repeats(gpu_ctx):
+    res, _ = check(gpu_ctx, H.gen_random_repeats(8 << 20, 60))
+    assert res.matches > 50
+
+
+def test_motif_level1_victims_and_sweeps(gpu_ctx):
+    res, ref = check(gpu_ctx, H.gen_motif(3 << 20, 3000), level=1)
+    assert ref["stats"]["victim_events"] > 0 and ref["stats"]["sweeps_wrapped"] > 0
+
+
+@pytest.mark.parametrize("vr", [0, 1])
+def test_victim_round_carry(gpu_ctx, vr):
+    check(gpu_ctx, H.gen_motif(3 << 20, 3000), level=1, vr_in=vr)
+
+
+def test_vm_like(gpu_ctx):
+    check(gpu_ctx, H.gen_vm_like(16 << 20))
+
+
+def test_dense(gpu_ctx):
+    check(gpu_ctx, H.gen_dense(16 << 20))
+
+
+def test_dense_level9(gpu_ctx):
+    check(gpu_ctx, H.gen_dense(8 << 20), level=9)
+
+
+def test_random_sweeps(gpu_ctx):
+    res, ref = check(gpu_ctx, H.gen_random(32 << 20))
+    assert ref["stats"]["sweeps_wrapped"] >= 2
+
+
+def test_tar_like(gpu_ctx):
+    check(gpu_ctx, H.gen_tar_like(16 << 20))
+
+
+@pytest.mark.parametrize("level", [0, 1, 2, 3, 4, 5, 6, 8, 9])
+def test_levels(gpu_ctx, level):
+    check(gpu_ctx, H.gen_vm_like(2 << 20, seed=level + 10), level=level)
+    check(gpu_ctx, H.gen_motif(1 << 20, 2000, seed=level), level=level)
+
+
+def test_constant_and_periodic(gpu_ctx):
+    check(gpu_ctx, np.zeros(1 << 20, dtype=np.uint8))
+    check(gpu_ctx, np.full(1 << 20, 255, dtype=np.uint8))
+    check(gpu_ctx, np.tile(np.arange(7, dtype=np.uint8), (1 << 20) // 7))
+    check(gpu_ctx, np.tile(H.gen_random(4099, seed=9), 300))
+
+
+def test_wide_chunk_bytes(gpu_ctx):
+    # distances written with 5 bytes, as for chunks >= 4 GiB (rzip.c:1006-1008)
+    check(gpu_ctx, H.gen_random_repeats(2 << 20, 40, lo=1024, hi=65536), cb=5)
+
+
+def test_tags_match_full_tag(gpu_ctx):
+    data = H.gen_random(100000, seed=77)
+    hidx = H.hash_index()
+    gpu_ctx.upload(data)
+    tags = gpu_ctx.debug_tags(data.size, hidx, data.size - 30)
+    h = hidx[data]
+    x = np.concatenate([[0], np.bitwise_xor.accumulate(h)])
+    want = x[31:] ^ x[:-31]
+    assert np.array_equal(tags, want)
+
+
+def test_crc_matches_zlib(gpu_ctx):
+    import zlib
+    import mrz_py
+    hidx = H.hash_index()
+    for n in (0, 5, 16384, 16385, 524288, 524288 + 16384 * 3 + 77, 3 << 20):
+        data = H.gen_random(n, seed=n % 97 + 1)
+        res, _, _ = gpu_ctx.rzip_chunk(data, mrz_py.make_params(7, 4, hidx))
+        assert res.crc32 == zlib.crc32(data.tobytes()), n
