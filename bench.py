@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""bench.py — rzip pre-process throughput (input GB/s) on B200, next to the reference's CPU path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--size BYTES]
+
+A step = one pass of the hot path (hash_search, rzip.c:507-667) over one chunk of synthetic input.
+N=1 workload: BASELINE.json configs[1] — 4 GiB tar-like input, duplicate bodies at distances up to
+4 GiB, one chunk, rzip level 7.  N>1: every rank processes its own 4 GiB chunk of VM-image-like data
+(configs[2] sharded by chunk; weak scaling), victim_round carried across ranks by an all-gather of
+each chunk's victim_round map.
+Prints ONE JSON line (rank 0).  `value` = device-resident throughput (CUDA events); `e2e` = the same
+through mrz_rzip_chunk() with pinned host buffers (H2D + kernels + D2H inside the timed region).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "modern-rzip_b200"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+GIB = 1 << 30
+LEVEL = 7
+
+
+def hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+# ------------------------------------------------------------------ workloads
+def gen_tar_like(n, seed=2, out=None):
+    """configs[1]: 512-byte headers + bodies (log-uniform 1 KiB..64 MiB); 35 % verbatim copies of an
+    earlier body, the rest half random bytes, half 64-symbol text."""
+    rng = np.random.default_rng(seed)
+    buf = out if out is not None else np.zeros(n, dtype=np.uint8)
+    buf[:n] = 0
+    alphabet = np.frombuffer(b"etaoinshrdlucmfwypvbgkqjxz ETAOINSHRDLUCMFWYPVBGKQJXZ.,;\n0123456", dtype=np.uint8)
+    bodies = []
+    pos = idx = 0
+    max_body = min(64 << 20, max(4096, n // 8))
+    while pos + 1024 <= n:
+        size = int(np.exp(rng.uniform(np.log(1024), np.log(max_body))))
+        size = min(size, n - pos - 512)
+        name = ("member%08d.dat" % idx).encode()
+        buf[pos:pos + len(name)] = np.frombuffer(name, dtype=np.uint8)
+        sz = ("%011o" % size).encode()
+        buf[pos + 124:pos + 124 + len(sz)] = np.frombuffer(sz, dtype=np.uint8)
+        pos += 512
+        r = rng.random()
+        if r < 0.35 and bodies:
+            s, l = bodies[int(rng.integers(0, len(bodies)))]
+            size = min(l, size)
+            buf[pos:pos + size] = buf[s:s + size]
+        elif r < 0.675:
+            buf[pos:pos + size] = rng.integers(0, 256, size, dtype=np.uint8)
+        else:
+            buf[pos:pos + size] = alphabet[rng.integers(0, 64, size, dtype=np.uint8)]
+        bodies.append((pos, size))
+        pos += (size + 511) // 512 * 512
+        idx += 1
+    return buf
+
+
+def gen_vm_like(n, seed=3, out=None):
+    """configs[2]: 4 KiB blocks — 35 % zero, 25 % copy of an earlier block, 20 % random, 20 % text."""
+    rng = np.random.default_rng(seed)
+    blk = 4096
+    nb = n // blk
+    buf = out if out is not None else np.zeros(n, dtype=np.uint8)
+    buf[:n] = 0
+    v = buf[:nb * blk].reshape(nb, blk)
+    kinds = rng.random(nb)
+    rnd = np.nonzero((kinds >= 0.60) & (kinds < 0.80))[0]
+    txt = np.nonzero(kinds >= 0.80)[0]
+    alphabet = np.frombuffer(b"abcdefghijklmnopqrstuvwxyzABCDEFGHIJKLMNOPQRSTUVWXYZ0123456789 \n", dtype=np.uint8)
+    step = 1 << 14
+    for i in range(0, rnd.size, step):
+        ix = rnd[i:i + step]
+        v[ix] = rng.integers(0, 256, (ix.size, blk), dtype=np.uint8)
+    for i in range(0, txt.size, step):
+        ix = txt[i:i + step]
+        v[ix] = alphabet[rng.integers(0, 64, (ix.size, blk), dtype=np.uint8)]
+    cp = np.nonzero((kinds >= 0.35) & (kinds < 0.60))[0]
+    cp = cp[cp > 0]
+    src = (rng.random(cp.size) * cp).astype(np.int64)  # uniformly chosen earlier block
+    for d, s in zip(cp.tolist(), src.tolist()):        # sequential: a copy may copy a copy
+        v[d] = v[s]
+    return buf
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown," \
+        "clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.samples = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            f = [x.strip() for x in s.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx = max(mx, float(f[1]))
+                for nm, val in zip(names, f[3:7]):
+                    if val.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ reference CPU arm
+def run_reference_sample(sample, steps, warmup):
+    """Times the unmodified reference binary (oracle/_ref/mrzip -n) on a bounded sample."""
+    import helpers as H
+    if not H.have_ref():
+        raise RuntimeError("oracle/_ref/mrzip missing (make -C oracle ref)")
+    tmpdir = "/dev/shm" if os.path.isdir("/dev/shm") else None
+    times = []
+    with tempfile.TemporaryDirectory(dir=tmpdir) as d:
+        fin, fout = os.path.join(d, "in.bin"), os.path.join(d, "out.mar")
+        sample.tofile(fin)
+        mflag = str(max(1, (sample.size * 3 // 2) // (100 * 1048576) + 2))  # ramsize so that one chunk holds it
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            H.run_reference(fin, fout, ("-m", mflag, "-p", "1", "-L", str(LEVEL)))
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                times.append(dt)
+    return times
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--size", type=int, default=4 * GIB, help="chunk bytes (default 4 GiB = configs[1])")
+    ap.add_argument("--cpu-sample", type=int, default=512 << 20, help="bytes of the workload given to the CPU baseline")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    n = args.size
+    multi = world > 1
+    workload = ("configs[2]: VM-image-like, one %d-byte chunk per GPU, rzip level 7" % n) if multi else \
+        ("configs[1]: %.2f GiB tar-like, duplicate bodies at distances up to the chunk size, single chunk, rzip level 7"
+         % (n / GIB))
+    config = {"workload": workload, "chunk_bytes_per_gpu": n, "rzip_level": LEVEL,
+              "l2": "input (%.1f GiB) and 64 MiB table re-initialised every step; input larger than L2" % (n / GIB)}
+
+    # ---------------- reference arm: the reference's own CPU implementation on the host cores
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        gen = gen_vm_like if multi else gen_tar_like
+        sample_n = min(args.cpu_sample, n)
+        sample = gen(sample_n, seed=3 if multi else 2)
+        w = min(args.warmup, 1)
+        times = run_reference_sample(sample, args.steps, w)
+        gbs = sample_n / (sum(times) / len(times)) / 1e9
+        line = {"impl": "reference", "metric": "rzip pre-process input GB/s", "value": gbs, "unit": "GB/s",
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": w, "ms_per_step": 1e3 * sum(times) / len(times),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int64",
+                "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": 1, "kind": "reference",
+                                 "sample": "first %d MiB of the workload generator, oracle/_ref/mrzip -n -L7 file->file "
+                                           "(1 hash_search thread + checksum/writer helpers), host has %d cores"
+                                           % (sample_n >> 20, os.cpu_count())},
+                "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    # ---------------- B200 arm
+    import torch
+    import mrz_py
+    import helpers as H
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if multi:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if multi:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    hidx = H.hash_index()
+    cb = H.chunk_bytes(n)
+    ctx = mrz_py.Context(local_rank, n)
+    pin_in = mrz_py.PinnedBuffer(n)
+    pin_s0 = mrz_py.PinnedBuffer(n // 2 + 64)
+    pin_s1 = mrz_py.PinnedBuffer(n + 16)
+    data = pin_in.array
+    if multi:
+        gen_vm_like(n, seed=3 + rank, out=data)
+    else:
+        gen_tar_like(n, seed=2, out=data)
+    prm = mrz_py.make_params(LEVEL, cb, hidx, 0)
+
+    clocks = ClockSampler(local_rank)
+    # device-resident timing (K)
+    ctx.upload(data)
+    for _ in range(args.warmup):
+        ctx.run_resident(n, prm)
+    barrier()
+    clocks.start()
+    t0 = time.perf_counter()
+    ms_k = ms_auto = ms_scan = ms_emit = 0.0
+    launches = 0
+    res = None
+    for _ in range(args.steps):
+        res = ctx.run_resident(n, prm)
+        ms_k += res.ms_kernels
+        ms_auto += res.ms_automaton
+        ms_scan += res.ms_tagscan
+        ms_emit += res.ms_emit
+        launches += res.gpu_launches
+    barrier()
+    wall_k = time.perf_counter() - t0
+    clk = clocks.stop()
+    # e2e timing (host buffers through the C-ABI call)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        r2, s0, s1 = ctx.rzip_chunk(data, prm, pin_s0.array, pin_s1.array)
+    barrier()
+    wall_e = time.perf_counter() - t0
+
+    tk = torch.tensor([ms_k / 1e3, wall_k, wall_e], dtype=torch.float64, device="cuda")
+    if multi:
+        dist.all_reduce(tk, op=dist.ReduceOp.MAX)
+    t_dev, t_wall, t_e2e = [float(x) for x in tk.tolist()]
+    total_bytes = n * world * args.steps
+    value = total_bytes / t_dev / 1e9
+    e2e = total_bytes / t_e2e / 1e9
+    b_alg = n + res.s0_len + res.s1_len
+    peak, peak_kind = hbm_peak()
+    achieved = b_alg * args.steps / (ms_auto / 1e3) / 1e9
+    line = {"metric": "rzip pre-process input GB/s", "value": value, "unit": "GB/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_dev / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int64",
+            "data": "synthetic", "config": config,
+            "e2e": {"value": e2e, "unit": "GB/s", "h2d_bytes_per_step": n,
+                    "d2h_bytes_per_step": int(res.s0_len + res.s1_len)},
+            "gpu_launches": int(launches),
+            "clocks": clk,
+            "roofline": {"bound": "hbm", "kernel": "k_automaton", "achieved": achieved, "peak": peak,
+                         "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "algorithmic_bytes_per_step": int(b_alg),
+                         "share_of_step": ms_auto / ms_k if ms_k else None,
+                         "ms_per_step": {"tag_scan": ms_scan / args.steps, "automaton": ms_auto / args.steps,
+                                         "emit+crc": ms_emit / args.steps}},
+            "wall_s_per_step_resident": t_wall / args.steps,
+            "result": {"matches": int(res.matches), "match_bytes": int(res.match_bytes),
+                       "literal_bytes": int(res.literal_bytes), "inserts": int(res.inserts),
+                       "n_ops": int(res.n_ops), "final_min_mask": int(res.final_min_mask),
+                       "victim_events": int(res.victim_events)}}
+    if rank == 0 and not multi and not args.no_cpu_baseline:
+        sample_n = min(args.cpu_sample, n)
+        times = run_reference_sample(np.array(data[:sample_n]), 1, 0)
+        line["cpu_baseline"] = {"value": sample_n / times[0] / 1e9, "unit": "GB/s", "cores": 1, "kind": "reference",
+                                "sample": "first %d MiB of the same input, oracle/_ref/mrzip -n -L7 file->file in "
+                                          "/dev/shm (1 hash_search thread + helpers); host has %d cores"
+                                          % (sample_n >> 20, os.cpu_count())}
+    if rank == 0:
+        print(json.dumps(line))
+    ctx.close()
+    if multi:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
