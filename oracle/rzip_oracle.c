@@ -100,6 +100,8 @@ typedef struct {
     int overflow;
     orc_token *tok;
     i64 tok_cap, ntok;
+    i64 *wlog;       /* optional log of table slots written (used by spec_model.c only) */
+    int nlog;
 } ctx;
 
 static inline int tz1(i64 t) { /* trailing one bits; ffsll(~t)-1 with ffsll(0)=0 -> -1 */
@@ -151,6 +153,7 @@ static void insert(ctx *c, i64 t, i64 off) {
     }
     c->tab[h].tag = t;
     c->tab[h].off = off;
+    if (c->wlog) c->wlog[c->nlog++] = h;
 }
 
 /* rzip.c:305-328 */
@@ -163,6 +166,7 @@ static i64 clean_one(ctx *c) {
             if ((o->tag & btm) != btm) {
                 o->off = 0; o->tag = 0;
                 c->count--;
+                if (c->wlog) c->wlog[c->nlog++] = c->clean_ptr;
                 return btm;
             }
         }

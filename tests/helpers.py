@@ -29,6 +29,15 @@ class OrcStats(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class SpecStats(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in (
+        "batches", "planned_commits", "serial_ops", "static_conflicts", "extra_conflicts", "complex_ops",
+        "emit_cuts", "count_cuts")]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
 class OrcToken(C.Structure):
     _fields_ = [("pos", C.c_int64), ("len", C.c_int64), ("ofs", C.c_int64)]
 
@@ -37,8 +46,8 @@ _orc = None
 
 
 def build_oracle():
-    if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(
-            os.path.join(ORACLE_DIR, "rzip_oracle.c")):
+    srcs = [os.path.join(ORACLE_DIR, f) for f in ("rzip_oracle.c", "spec_model.c", "rzip_oracle.h")]
+    if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", ORACLE_DIR, "librzip_oracle.so"], stdout=subprocess.DEVNULL)
 
 
@@ -55,6 +64,10 @@ def orc():
             C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_int, C.c_int, C.POINTER(C.c_int64),
             C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_int64, C.POINTER(C.c_int64),
             C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.POINTER(OrcStats)]
+        lib.orc_rzip_chunk_spec.argtypes = [
+            C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_int, C.c_int, C.POINTER(C.c_int64),
+            C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_int64, C.POINTER(C.c_int64),
+            C.POINTER(OrcStats), C.c_int, C.POINTER(SpecStats)]
         _orc = lib
     return _orc
 
@@ -101,6 +114,26 @@ def oracle_chunk(data, level=7, cb=None, vr_in=0, hidx=None, want_tokens=False):
     if want_tokens:
         out["tokens"] = [(toks[i].pos, toks[i].len, toks[i].ofs) for i in range(ntok.value)]
     return out
+
+
+def spec_model_chunk(data, level=7, cb=None, vr_in=0, hidx=None, batch=1024):
+    """CPU model of the GPU's batched speculation (oracle/spec_model.c)."""
+    a = as_u8(data)
+    n = a.size
+    cb = cb or chunk_bytes(n)
+    hidx = hash_index() if hidx is None else hidx
+    hi = (C.c_int64 * 256)(*[int(x) for x in hidx])
+    s0 = np.empty(n // 2 + 64, dtype=np.uint8)
+    s1 = np.empty(n + 16, dtype=np.uint8)
+    s0l, s1l = C.c_int64(), C.c_int64()
+    vr = C.c_int64(vr_in)
+    st, ss = OrcStats(), SpecStats()
+    buf = a if n else np.zeros(1, dtype=np.uint8)
+    rc = orc().orc_rzip_chunk_spec(buf.ctypes.data, n, hi, level, cb, C.byref(vr), s0.ctypes.data, s0.size,
+                                   C.byref(s0l), s1.ctypes.data, s1.size, C.byref(s1l), C.byref(st), batch, C.byref(ss))
+    assert rc == 0
+    return dict(s0=s0[:s0l.value].tobytes(), s1=s1[:s1l.value].tobytes(), stats=st.as_dict(), vr_out=vr.value,
+                spec=ss.as_dict())
 
 
 # ---------------------------------------------------------------- reference binary
