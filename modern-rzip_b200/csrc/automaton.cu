@@ -339,5 +339,5 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
 
 extern "C" void mrz_launch_automaton(const u8 *buf, Slot *tab, const i64 *hidx, AutoState *st, const i64 *tile_off,
                                      const u32 *cand_pos, const i64 *cand_tag, Token *toks, cudaStream_t s) {
-    k_automaton<<<1, 32, 0, s>>>(buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks);
+    MRZ_LAUNCH(k_automaton, 1, 32, s, buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks);
 }

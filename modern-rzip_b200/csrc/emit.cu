@@ -267,36 +267,36 @@ extern "C" void mrz_crc_upload_consts(const void *host_consts) {
 
 extern "C" void mrz_launch_crc(const u8 *buf, i64 n, u32 *part, u32 *part2, u32 *tail, cudaStream_t s, int *launches) {
     i64 nblk = n / CRC_BLK, ngrp = nblk / 32;
-    if (nblk) { k_crc_blocks<<<(unsigned)((nblk + 3) / 4), 128, 0, s>>>(buf, nblk, part); (*launches)++; }
-    if (ngrp) { k_crc_level2<<<(unsigned)((ngrp + 3) / 4), 128, 0, s>>>(part, ngrp, part2); (*launches)++; }
-    k_crc_tail<<<1, 1, 0, s>>>(buf, nblk * CRC_BLK, n - nblk * CRC_BLK, tail);
+    if (nblk) { MRZ_LAUNCH(k_crc_blocks, (unsigned)((nblk + 3) / 4), 128, s, buf, nblk, part); (*launches)++; }
+    if (ngrp) { MRZ_LAUNCH(k_crc_level2, (unsigned)((ngrp + 3) / 4), 128, s, part, ngrp, part2); (*launches)++; }
+    MRZ_LAUNCH(k_crc_tail, 1, 1, s, buf, nblk * CRC_BLK, n - nblk * CRC_BLK, tail);
     (*launches)++;
 }
 
 extern "C" void mrz_launch_exclusive_scan(const i64 *in, i64 *out, i64 cnt, i64 *bsum, i64 *total, cudaStream_t s,
                                           int *launches) {
     i64 nb = (cnt + SCAN_BLK - 1) / SCAN_BLK;
-    k_scan_local<<<(unsigned)nb, SCAN_B, 0, s>>>(in, out, cnt, bsum);
-    k_scan_bsums<<<1, SCAN_B, 0, s>>>(bsum, nb, total);
-    k_scan_add<<<(unsigned)nb, SCAN_B, 0, s>>>(out, cnt, bsum);
+    MRZ_LAUNCH(k_scan_local, (unsigned)nb, SCAN_B, s, in, out, cnt, bsum);
+    MRZ_LAUNCH(k_scan_bsums, 1, SCAN_B, s, bsum, nb, total);
+    MRZ_LAUNCH(k_scan_add, (unsigned)nb, SCAN_B, s, out, cnt, bsum);
     *launches += 3;
 }
 
 extern "C" void mrz_launch_item_sizes(const Token *toks, i64 m, i64 n, int cb, i64 *a0, i64 *a1, EmitTotals *tot,
                                       cudaStream_t s) {
     i64 items = m + 1;
-    k_item_sizes<<<(unsigned)((items + 255) / 256), 256, 0, s>>>(toks, m, n, cb, a0, a1, tot);
+    MRZ_LAUNCH(k_item_sizes, (unsigned)((items + 255) / 256), 256, s, toks, m, n, cb, a0, a1, tot);
 }
 
 extern "C" void mrz_launch_emit(const u8 *buf, const Token *toks, i64 m, i64 n, int cb, const i64 *off0,
                                 const i64 *off1, i64 s1_len, u8 *s0, u8 *s1, const u32 *crc, cudaStream_t s,
                                 int *launches) {
     i64 items = m + 1;
-    k_emit_s0<<<(unsigned)((items * 32 + 255) / 256), 256, 0, s>>>(toks, m, n, cb, off0, s0, crc);
+    MRZ_LAUNCH(k_emit_s0, (unsigned)((items * 32 + 255) / 256), 256, s, toks, m, n, cb, off0, s0, crc);
     (*launches)++;
     if (s1_len > 0) {
         i64 thr = (s1_len + 15) / 16;
-        k_emit_s1<<<(unsigned)((thr + 255) / 256), 256, 0, s>>>(buf, toks, m, n, off1, s1_len, s1);
+        MRZ_LAUNCH(k_emit_s1, (unsigned)((thr + 255) / 256), 256, s, buf, toks, m, n, off1, s1_len, s1);
         (*launches)++;
     }
 }

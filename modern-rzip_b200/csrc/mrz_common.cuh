@@ -2,7 +2,10 @@
 // Semantics follow /root/reference/src/rzip.c (cited per function); the code is a new design:
 // candidate lists instead of a per-byte loop, a warp-wide probe of 32 slots, token triples.
 #pragma once
+#ifndef MRZ_CUSIM   // tests/cusim compiles these sources for the CPU emulator with -include cusim.h
 #include <cuda_runtime.h>
+#define MRZ_LAUNCH(kernel, grid, block, stream, ...) kernel<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__)
+#endif
 #include <stdint.h>
 
 typedef long long i64;

@@ -205,12 +205,12 @@ k_debug_tags(const u8 *__restrict__ buf, const i64 *__restrict__ hidx, i64 n, i6
 extern "C" void mrz_launch_scan(const u8 *buf, const i64 *hidx, AutoState *st, int *tile_cnt, i64 *tile_off,
                                 u32 *cand_pos, i64 *cand_tag, int tiles, cudaStream_t s) {
     if (tiles < 1) tiles = 1;
-    k_scan_count<<<tiles, SCAN_THREADS, 0, s>>>(buf, hidx, st, tile_cnt);
-    k_scan_offsets<<<1, 1024, 0, s>>>(st, tile_cnt, tile_off);
-    k_scan_emit<<<tiles, SCAN_THREADS, 0, s>>>(buf, hidx, st, tile_off, cand_pos, cand_tag);
+    MRZ_LAUNCH(k_scan_count, tiles, SCAN_THREADS, s, buf, hidx, st, tile_cnt);
+    MRZ_LAUNCH(k_scan_offsets, 1, 1024, s, st, tile_cnt, tile_off);
+    MRZ_LAUNCH(k_scan_emit, tiles, SCAN_THREADS, s, buf, hidx, st, tile_off, cand_pos, cand_tag);
 }
 
 extern "C" void mrz_launch_debug_tags(const u8 *buf, const i64 *hidx, i64 n, i64 count, i64 *tags, cudaStream_t s) {
     int tiles = (int)((count + SCAN_TILE - 1) / SCAN_TILE);
-    if (tiles > 0) k_debug_tags<<<tiles, SCAN_THREADS, 0, s>>>(buf, hidx, n, count, tags);
+    if (tiles > 0) MRZ_LAUNCH(k_debug_tags, tiles, SCAN_THREADS, s, buf, hidx, n, count, tags);
 }

@@ -43,12 +43,11 @@ class MrzError(RuntimeError):
 _lib = None
 
 
-def lib():
-    global _lib
-    if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            raise MrzError("libmrz_gpu.so not built (run `make -C modern-rzip_b200`); there is no CPU fallback")
-        L = C.CDLL(LIB_PATH)
+def bind(path):
+    """Load a library exporting include/mrz_gpu.h and set the ctypes prototypes.  The product library is
+    LIB_PATH; tests/cusim builds an emulator library with the same ABI for CPU-only kernel tests."""
+    L = C.CDLL(path)
+    if True:
         L.mrz_version.restype = C.c_char_p
         L.mrz_last_error.restype = C.c_char_p
         L.mrz_last_error.argtypes = [C.c_void_p]
@@ -65,7 +64,15 @@ def lib():
         L.mrz_debug_tags.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_int64]
         L.mrz_debug_crc32.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_uint32)]
         L.mrz_debug_tokens.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
-        _lib = L
+    return L
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise MrzError("libmrz_gpu.so not built (run `make -C modern-rzip_b200`); there is no CPU fallback")
+        _lib = bind(LIB_PATH)
     return _lib
 
 
@@ -96,35 +103,36 @@ class PinnedBuffer:
 
 
 class Context:
-    def __init__(self, device=0, max_chunk=1 << 28):
+    def __init__(self, device=0, max_chunk=1 << 28, library=None):
+        self.L = library if library is not None else lib()
         self.h = C.c_void_p()
-        rc = lib().mrz_ctx_create(device, max_chunk, C.byref(self.h))
+        rc = self.L.mrz_ctx_create(device, max_chunk, C.byref(self.h))
         if rc:
-            raise MrzError("mrz_ctx_create rc=%d: %s" % (rc, lib().mrz_last_error(None).decode()))
+            raise MrzError("mrz_ctx_create rc=%d: %s" % (rc, self.L.mrz_last_error(None).decode()))
         self.max_chunk = max_chunk
 
     def close(self):
         if self.h:
-            lib().mrz_ctx_destroy(self.h)
+            self.L.mrz_ctx_destroy(self.h)
             self.h = C.c_void_p()
 
     def _check(self, rc, what):
         if rc:
-            raise MrzError("%s rc=%d: %s" % (what, rc, lib().mrz_last_error(self.h).decode()))
+            raise MrzError("%s rc=%d: %s" % (what, rc, self.L.mrz_last_error(self.h).decode()))
 
     def upload(self, arr):
         arr = np.ascontiguousarray(arr, dtype=np.uint8)
-        self._check(lib().mrz_upload(self.h, arr.ctypes.data if arr.size else None, arr.size), "mrz_upload")
+        self._check(self.L.mrz_upload(self.h, arr.ctypes.data if arr.size else None, arr.size), "mrz_upload")
 
     def run_resident(self, n, params):
         res = MrzResult()
-        self._check(lib().mrz_run_resident(self.h, n, C.byref(params), C.byref(res)), "mrz_run_resident")
+        self._check(self.L.mrz_run_resident(self.h, n, C.byref(params), C.byref(res)), "mrz_run_resident")
         return res
 
     def download(self, res, s0=None, s1=None):
         s0 = np.empty(max(1, res.s0_len), dtype=np.uint8) if s0 is None else s0
         s1 = np.empty(max(1, res.s1_len), dtype=np.uint8) if s1 is None else s1
-        self._check(lib().mrz_download(self.h, s0.ctypes.data, s0.size, s1.ctypes.data, s1.size), "mrz_download")
+        self._check(self.L.mrz_download(self.h, s0.ctypes.data, s0.size, s1.ctypes.data, s1.size), "mrz_download")
         return s0[:res.s0_len], s1[:res.s1_len]
 
     def rzip_chunk(self, arr, params, s0=None, s1=None):
@@ -134,7 +142,7 @@ class Context:
         s0 = np.empty(n // 2 + 64, dtype=np.uint8) if s0 is None else s0
         s1 = np.empty(n + 16, dtype=np.uint8) if s1 is None else s1
         res = MrzResult()
-        rc = lib().mrz_rzip_chunk(self.h, arr.ctypes.data if n else None, n, C.byref(params), s0.ctypes.data, s0.size,
+        rc = self.L.mrz_rzip_chunk(self.h, arr.ctypes.data if n else None, n, C.byref(params), s0.ctypes.data, s0.size,
                                   s1.ctypes.data, s1.size, C.byref(res))
         self._check(rc, "mrz_rzip_chunk")
         return res, s0[:res.s0_len], s1[:res.s1_len]
@@ -142,12 +150,12 @@ class Context:
     def debug_tags(self, n, hash_index, count):
         hi = (C.c_int64 * 256)(*[int(x) for x in hash_index])
         out = np.empty(count, dtype=np.int64)
-        self._check(lib().mrz_debug_tags(self.h, n, hi, out.ctypes.data, count), "mrz_debug_tags")
+        self._check(self.L.mrz_debug_tags(self.h, n, hi, out.ctypes.data, count), "mrz_debug_tags")
         return out
 
     def debug_tokens(self):
         cnt = C.c_int64()
-        lib().mrz_debug_tokens(self.h, None, 0, C.byref(cnt))
+        self.L.mrz_debug_tokens(self.h, None, 0, C.byref(cnt))
         out = np.empty((max(1, cnt.value), 3), dtype=np.int64)
-        self._check(lib().mrz_debug_tokens(self.h, out.ctypes.data, cnt.value, C.byref(cnt)), "mrz_debug_tokens")
+        self._check(self.L.mrz_debug_tokens(self.h, out.ctypes.data, cnt.value, C.byref(cnt)), "mrz_debug_tokens")
         return out[:cnt.value]

@@ -18,3 +18,15 @@ def gpu_ctx():
     ctx = mrz_py.Context(0, 1 << 28)
     yield ctx
     ctx.close()
+
+
+@pytest.fixture(scope="session")
+def sim_ctx():
+    """The same kernel sources compiled for the CPU emulator (tests/cusim) — no GPU needed."""
+    import subprocess
+    import mrz_py
+    d = os.path.join(ROOT, "tests", "cusim")
+    subprocess.check_call(["make", "-C", d, "libmrz_sim.so"], stdout=subprocess.DEVNULL)
+    ctx = mrz_py.Context(0, 1 << 26, library=mrz_py.bind(os.path.join(d, "libmrz_sim.so")))
+    yield ctx
+    ctx.close()

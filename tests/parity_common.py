@@ -1,0 +1,36 @@
+"""Shared parity checker: a context (CUDA library on the GPU, or the cusim build of the same kernel sources on
+the CPU) against the CPU oracle, bit-exact (streams, counters, victim carry).  TEST INFRASTRUCTURE."""
+import pytest
+
+import helpers as H
+
+STAT_KEYS = ("matches", "match_bytes", "literals", "literal_bytes", "tag_hits", "tag_misses", "inserts")
+
+
+def first_token_diff(ctx, ref):
+    got = [tuple(int(x) for x in r) for r in ctx.debug_tokens()]
+    want = [t for t in ref["tokens"] if t[2] >= 0]
+    for i, (g, w) in enumerate(zip(got, want)):
+        if g != w:
+            return "token %d: got %r want %r" % (i, g, w)
+    return "token counts: got %d want %d" % (len(got), len(want))
+
+
+def check(ctx, data, level=7, vr_in=0, cb=None):
+    import mrz_py
+    data = H.as_u8(data)
+    cb = cb or H.chunk_bytes(data.size)
+    hidx = H.hash_index()
+    ref = H.oracle_chunk(data, level=level, cb=cb, vr_in=vr_in, hidx=hidx, want_tokens=True)
+    prm = mrz_py.make_params(level, cb, hidx, vr_in)
+    res, s0, s1 = ctx.rzip_chunk(data, prm)
+    if s0.tobytes() != ref["s0"] or s1.tobytes() != ref["s1"]:
+        pytest.fail("stream mismatch (n=%d level=%d): %s" % (data.size, level, first_token_diff(ctx, ref)))
+    for k in STAT_KEYS:
+        assert getattr(res, k) == ref["stats"][k], k
+    assert res.victim_round_out == ref["vr_out"]
+    assert res.victim_events == ref["stats"]["victim_events"]
+    assert res.final_min_mask == ref["stats"]["final_min_mask"]
+    assert res.n_ops == ref["stats"]["lookups"]
+    assert res.gpu_launches > 0
+    return res, ref

@@ -1,0 +1,56 @@
+"""CPU-only parity: the product's kernel sources (modern-rzip_b200/csrc/*.cu) compiled for the fiber emulator in
+tests/cusim and driven through the same C-ABI, against the oracle.  Catches logic errors in the kernels without a
+GPU; the `-m gpu` tests in test_gpu_parity.py remain the parity tests proper."""
+import numpy as np
+import pytest
+
+import helpers as H
+from parity_common import check
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 32, 64, 650, 8193, 8223, 100003])
+def test_tiny_and_ragged(sim_ctx, n):
+    seq = (b"abcdefghijklmnopqrstuvwxyz012345" * (n // 32 + 1))[:n]
+    check(sim_ctx, seq)
+    check(sim_ctx, H.gen_random(n, seed=n + 1) if n else b"")
+
+
+def test_random_with_repeats(sim_ctx):
+    res, _ = check(sim_ctx, H.gen_random_repeats(4 << 20, 40, lo=2048, hi=65536))
+    assert res.matches > 30
+
+
+@pytest.mark.parametrize("vr", [0, 1])
+def test_motif_level1_victims_and_sweeps(sim_ctx, vr):
+    res, ref = check(sim_ctx, H.gen_motif(3 << 20, 3000), level=1, vr_in=vr)
+    assert ref["stats"]["victim_events"] > 0 and ref["stats"]["sweeps_wrapped"] > 0
+
+
+def test_vm_like(sim_ctx):
+    check(sim_ctx, H.gen_vm_like(4 << 20))
+
+
+def test_dense_level9(sim_ctx):
+    check(sim_ctx, H.gen_dense(4 << 20), level=9)
+
+
+def test_tar_like(sim_ctx):
+    check(sim_ctx, H.gen_tar_like(4 << 20))
+
+
+def test_sweeps_small_table(sim_ctx):
+    res, ref = check(sim_ctx, H.gen_random(8 << 20, seed=21), level=2)
+    assert ref["stats"]["sweeps_wrapped"] >= 1
+
+
+@pytest.mark.parametrize("level", [0, 1, 3, 5, 6, 8])
+def test_levels(sim_ctx, level):
+    check(sim_ctx, H.gen_vm_like(1 << 20, seed=level + 10), level=level)
+    check(sim_ctx, H.gen_motif(1 << 20, 2000, seed=level), level=level)
+
+
+def test_degenerate(sim_ctx):
+    check(sim_ctx, np.zeros(1 << 18, dtype=np.uint8))
+    check(sim_ctx, np.full(1 << 18, 255, dtype=np.uint8))
+    check(sim_ctx, np.tile(np.arange(7, dtype=np.uint8), (1 << 18) // 7))
+    check(sim_ctx, np.tile(H.gen_random(4099, seed=9), 100))
