@@ -1,16 +1,44 @@
-// automaton.cu — the exact sequential core of hash_search, one warp per chunk automaton.
+// automaton.cu — the table automaton of hash_search, exact, as one 1024-thread CTA per chunk.
 //
 // Reproduces, operation for operation, the table semantics of src/rzip.c:
 //   find_best_match (rzip.c:426-462), insert_hash (rzip.c:256-301), clean_one_from_hash
 //   (rzip.c:305-328), single_match_len (rzip.c:372-397) and the greedy/lazy emission rule of
 //   hash_search (rzip.c:571-599).
-// B200 design: the per-byte loop is gone (candidates come from tag_scan.cu); every probe looks at
-// 32 consecutive 16-byte slots at once (one coalesced 512 B read from the L2-resident table) and
-// resolves walk termination, equal-tag chains and the victim index with ballots; match extension
-// compares 256 bytes per warp step; recursion in insert_hash is an explicit stack.
+//
+// B200 design (not the reference's loop):
+//   * the per-byte loop is gone: candidates (positions whose tag passes the lookup gate) come from
+//     tag_scan.cu as a position-ordered list;
+//   * BATCHED SPECULATION: the next <=1024 candidate ops are *planned* in parallel, one thread
+//     each, against the live table read-only (probe walk, insert target, one level of
+//     displacement).  Plans are then committed in order: a plan is valid as long as no earlier op
+//     of the batch wrote a slot inside its read ranges (checked exactly through a shared-memory
+//     hash of the batch's write slots), it met no equal tag (=> match_len needed), and it stays
+//     clear of the sweep window of clean_one_from_hash.  Everything else - typically <1 % of the
+//     ops - is executed by warp 0 on the live table with the reference semantics (32-slot probe,
+//     ballots for walk termination / equal-tag chains / the victim index, 256-byte-per-step
+//     match extension), after which later plans that read a slot it wrote are invalidated.
+//   * the sweep of clean_one_from_hash is pre-resolved per batch: a parallel scan keeps a queue of
+//     the next eligible slots, so the n-th overflow of a batch zeroes the n-th queued slot.
+//   oracle/spec_model.c is the CPU model of exactly this scheme; tests/test_spec_model.py proves
+//   it equivalent to the sequential restatement, tests/test_sim_parity.py runs this very file on
+//   the CPU emulator, tests/test_gpu_parity.py on the B200.
 #include "mrz_common.cuh"
 
 #define FULL 0xffffffffu
+#define AT 1024            // threads per CTA = ops per batch
+#define EQ_CAP 4096        // eligible-slot ring (power of two)
+#define WH_CAP 4096        // write-slot hash (power of two, >= 2 * AT)
+#define MAXWALK 4096       // longer probe walks are left to the serial path
+#define WLOG_CAP 64
+
+enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8 };
+
+// Running state of the automaton, shared by the whole CTA (rzip_state, mrzip_private.h:388-416).
+struct Run {
+    i64 p, last, cur_p, cur_len, cur_ofs, min_mask, ins_mask, clean_ptr, count, vr;
+    i64 hits, misses, inserts, vevents, nops, ntok;
+    int error;
+};
 
 struct Warp {
     // constants
@@ -23,6 +51,29 @@ struct Warp {
     i64 p, last, cur_p, cur_len, cur_ofs, min_mask, ins_mask, clean_ptr, count, vr;
     i64 hits, misses, inserts, vevents, nops, ntok;
     int error;
+    // write log of the current op: (slot << 1) | zeroed; nlog > WLOG_CAP means overflow
+    int *wlog;
+    int nlog;
+    i64 clean_hint;   // no eligible slot exists in [clean_ptr, clean_hint)
+
+    __device__ __forceinline__ void load(const Run &r) {
+        p = r.p; last = r.last; cur_p = r.cur_p; cur_len = r.cur_len; cur_ofs = r.cur_ofs;
+        min_mask = r.min_mask; ins_mask = r.ins_mask; clean_ptr = r.clean_ptr; count = r.count; vr = r.vr;
+        hits = r.hits; misses = r.misses; inserts = r.inserts; vevents = r.vevents; nops = r.nops; ntok = r.ntok;
+        error = r.error;
+    }
+    __device__ __forceinline__ void store(Run &r) const {
+        if (lane == 0) {
+            r.p = p; r.last = last; r.cur_p = cur_p; r.cur_len = cur_len; r.cur_ofs = cur_ofs;
+            r.min_mask = min_mask; r.ins_mask = ins_mask; r.clean_ptr = clean_ptr; r.count = count; r.vr = vr;
+            r.hits = hits; r.misses = misses; r.inserts = inserts; r.vevents = vevents; r.nops = nops; r.ntok = ntok;
+            r.error = error;
+        }
+    }
+    __device__ __forceinline__ void log_write(i64 slot, int zeroed) {
+        if (nlog < WLOG_CAP && lane == 0) wlog[nlog] = (int)(slot << 1) | zeroed;
+        nlog++;
+    }
 
     // rzip.c:372-397.  Returns total length (0 if < 31) and the backward part in rev.
     __device__ __forceinline__ i64 match_len(i64 p0, i64 op, i64 &rev) {
@@ -155,18 +206,22 @@ struct Warp {
                 continue;
             }
             if (lane == 0) st_slot(&tab[target], coff, ct);
+            log_write(target, 0);
             __syncwarp();
             break;
         }
         while (sp > 0) {
             sp--;
             if (lane == 0) st_slot(&tab[stk[3 * sp]], stk[3 * sp + 2], stk[3 * sp + 1]);
+            log_write(stk[3 * sp], 0);
             __syncwarp();
         }
     }
 
     // rzip.c:305-328
     __device__ __forceinline__ void clean_one() {
+        if (clean_ptr < clean_hint) clean_ptr = clean_hint;   // nothing eligible before the hint
+        clean_hint = 0;
         for (;;) {
             i64 btm = (min_mask << 1) | 1;
             while (clean_ptr < hsize) {
@@ -181,6 +236,7 @@ struct Warp {
                     int l = __ffs(m) - 1;
                     clean_ptr += l;
                     if (lane == l) st_slot(&tab[idx], 0, 0);
+                    log_write(clean_ptr, 1);
                     __syncwarp();
                     count--;
                     ins_mask = btm;
@@ -227,7 +283,7 @@ __device__ __forceinline__ i64 xor_scan_incl(i64 v, int lane) {
     return v;
 }
 
-// First index in [lo, hi) whose cand_pos >= rel (hi if none); 32-ary search.
+// First index in [lo, hi) whose cand_pos >= rel (hi if none); 32-ary search by one warp.
 __device__ __forceinline__ i64 list_seek(const u32 *cand_pos, i64 lo, i64 hi, u32 rel, int lane) {
     while (hi - lo > 32) {
         i64 len = hi - lo;
@@ -250,94 +306,468 @@ __device__ __forceinline__ i64 list_seek(const u32 *cand_pos, i64 lo, i64 hi, u3
     return ge ? lo + (__ffs(ge) - 1) : hi;
 }
 
+// ---- shared memory of the CTA ------------------------------------------------------------------
+struct Smem {
+    i64 hx[256];
+    i64 stk[3 * 64];
+    i64 b_tag[AT];          // batch: tag of op j
+    Run run;
+    i64 e_scan;             // slots in [run.clean_ptr, e_scan) have been examined for the queue
+    i64 li;                 // next candidate-list index
+    u32 b_rel[AT];          // batch: position of op j relative to seg_lo
+    int b_li[AT];           // batch: candidate-list index of op j
+    int pre[AT];            // inclusive prefix over planned ops: (insert count << 16) | dcount sum
+    int E[EQ_CAP];          // ring of eligible slots, ascending
+    int wh_key[WH_CAP];     // write-slot hash: slot (or -1)
+    int wh_val[WH_CAP];     //                  smallest op index writing it
+    int wlog[WLOG_CAP];
+    int wsum[40];
+    unsigned e_idx, e_cnt;  // ring counters (monotonic)
+    int nr, pos, k, nlog, jumped, ended, bmax, red;
+};
+
+#ifdef MRZ_CUSIM
+#define MRZ_SMEM_PTR(T, name) static T name##_storage; T *name = &name##_storage
+#else
+#define MRZ_SMEM_PTR(T, name) extern __shared__ __align__(16) unsigned char name##_raw[]; T *name = reinterpret_cast<T *>(name##_raw)
+#endif
+
+// exclusive prefix sum of v over the CTA (thread order); total in `total`.  Two barriers.
+__device__ __forceinline__ int block_excl_scan(int v, int *wsum, int &total) {
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        int u = __shfl_up_sync(FULL, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) wsum[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int w = wsum[lane], wi = w;
+        for (int o = 1; o < 32; o <<= 1) {
+            int u = __shfl_up_sync(FULL, wi, o);
+            if (lane >= o) wi += u;
+        }
+        wsum[lane] = wi - w;
+        if (lane == 31) wsum[32] = wi;
+    }
+    __syncthreads();
+    total = wsum[32];
+    int r = wsum[wid] + inc - v;
+    return r;
+}
+
+// minimum of v over the CTA.  Two barriers; `red` must not be in use.
+__device__ __forceinline__ int block_min(int v, int *red) {
+    for (int o = 16; o; o >>= 1) {
+        int u = __shfl_xor_sync(FULL, v, o);
+        v = u < v ? u : v;
+    }
+    if (threadIdx.x == 0) *red = 0x7fffffff;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) atomicMin(red, v);
+    __syncthreads();
+    return *red;
+}
+
+__device__ __forceinline__ unsigned wh_hash(int slot) { return ((unsigned)slot * 2654435761u) >> 20; }  // 12 bits
+
+__device__ __forceinline__ void wh_insert(Smem *S, int slot, int j) {
+    unsigned h = wh_hash(slot) & (WH_CAP - 1);
+    for (;;) {
+        int k = atomicCAS(&S->wh_key[h], -1, slot);
+        if (k == -1 || k == slot) { atomicMin(&S->wh_val[h], j); return; }
+        h = (h + 1) & (WH_CAP - 1);
+    }
+}
+// true when some op with index < j writes a slot in [lo, hi]
+__device__ __forceinline__ bool wh_range_hit(const Smem *S, int lo, int hi, int j) {
+    for (int s = lo; s <= hi; s++) {
+        unsigned h = wh_hash(s) & (WH_CAP - 1);
+        for (;;) {
+            int k = S->wh_key[h];
+            if (k == -1) break;
+            if (k == s) { if (S->wh_val[h] < j) return true; break; }
+            h = (h + 1) & (WH_CAP - 1);
+        }
+    }
+    return false;
+}
+
+struct Plan {
+    int flags, dcount;
+    int rd_lo, rd_hi, rd2_lo, rd2_hi;   // inclusive slot ranges read; rd2_lo < 0: none
+    int w1_slot, w2_slot;               // displaced occupant's new home; where (tag, pos) goes
+    i64 w1_off, w1_tag;
+};
+
+__device__ __forceinline__ bool slot_empty(const Slot &e) { return (e.off | e.tag) == 0; }
+
+// Phase A: plan one op against the table without modifying anything (oracle/spec_model.c plan_op).
+__device__ __forceinline__ void plan_op(Plan &r, const Slot *tab, i64 tag, i64 hmask, i64 hsize, i64 min_mask,
+                                        i64 ins_mask, int chain, i64 w_lo, i64 w_hi) {
+    r.flags = 0; r.dcount = 0; r.rd2_lo = -1; r.rd2_hi = -1; r.w1_slot = -1; r.w2_slot = -1; r.w1_off = 0; r.w1_tag = 0;
+    const i64 btm = (min_mask << 1) | 1;
+    const bool want = (tag & ins_mask) == ins_mask;
+    const int myz = tz1(tag);
+    const i64 h0 = tag & hmask;
+    i64 h = h0;
+    int kind = 0;            // 0: none yet, 1: overwrite a due-for-sweep entry, 2: displace a lesser entry
+    i64 stop = -1, otag = 0, ooff = 0;
+    r.rd_lo = (int)h0; r.rd_hi = (int)h0;
+    for (;;) {
+        Slot e[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) e[q] = ld_slot(&tab[h + q]);   // the table has 4 slots of slack
+        bool done = false;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            if (done) continue;
+            if (h + q >= hsize) { r.flags |= F_COMPLEX; return; }
+            if (slot_empty(e[q])) { r.rd_hi = (int)(h + q); done = true; continue; }
+            if (e[q].tag == tag) { r.flags |= F_COMPLEX; return; }
+            if (want && kind == 0) {
+                if ((e[q].tag & btm) != btm) { kind = 1; stop = h + q; }
+                else if (tz1(e[q].tag) < myz) { kind = 2; stop = h + q; otag = e[q].tag; ooff = e[q].off; }
+            }
+        }
+        if (done) break;
+        h += 4;
+        if (h - h0 > MAXWALK) { r.flags |= F_COMPLEX; return; }
+    }
+    if (want) {
+        r.flags |= F_INSERT;
+        if (kind == 0) { r.w2_slot = r.rd_hi; r.dcount = 1; }
+        else if (kind == 1) { r.w2_slot = (int)stop; r.dcount = 0; }
+        else {
+            // one level of displacement (rzip.c:275-277): where does the occupant go?
+            const int oz = tz1(otag);
+            const i64 g0 = otag & hmask;
+            i64 g = g0;
+            int round = 0, d2 = 0;
+            for (;;) {
+                Slot e[4];
+#pragma unroll
+                for (int q = 0; q < 4; q++) e[q] = ld_slot(&tab[g + q]);
+                bool done = false;
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    if (done) continue;
+                    if (g + q >= hsize) { r.flags |= F_COMPLEX; return; }
+                    if (slot_empty(e[q])) { g += q; done = true; continue; }
+                    if ((e[q].tag & btm) != btm) { d2 = -1; g += q; done = true; continue; }
+                    if (tz1(e[q].tag) < oz) { r.flags |= F_COMPLEX; return; }
+                    if (e[q].tag == otag && ++round == chain) { r.flags |= F_COMPLEX; return; }
+                }
+                if (done) break;
+                g += 4;
+                if (g - g0 > MAXWALK) { r.flags |= F_COMPLEX; return; }
+            }
+            r.flags |= F_W1;
+            r.rd2_lo = (int)g0; r.rd2_hi = (int)g;
+            r.w1_slot = (int)g; r.w1_off = ooff; r.w1_tag = otag;
+            r.w2_slot = (int)stop; r.dcount = 1 + d2;
+        }
+    }
+    // anything touching the sweep window is left to the serial path
+    if (r.rd_hi >= w_lo && r.rd_lo < w_hi) r.flags |= F_COMPLEX;
+    if (r.rd2_lo >= 0 && r.rd2_hi >= w_lo && r.rd2_lo < w_hi) r.flags |= F_COMPLEX;
+}
+
+// Refill the ring of eligible slots (those clean_one_from_hash will zero next, in order) by a
+// parallel scan of the table from e_scan; only meaningful once ins_mask == 2*min_mask+1.
+__device__ __forceinline__ void refill_queue(Smem *S, const Slot *tab, i64 hsize, int want) {
+    const int tid = threadIdx.x;
+    const i64 btm = (S->run.min_mask << 1) | 1;
+    for (;;) {
+        __syncthreads();
+        int avail = (int)(S->e_cnt - S->e_idx);
+        i64 scan = S->e_scan;
+        if (avail >= want || scan >= hsize || avail + 2 * AT > EQ_CAP) break;
+        // each thread examines two consecutive slots
+        i64 s0 = scan + 2 * tid;
+        bool g0 = false, g1 = false;
+        if (s0 < hsize) { Slot e = ld_slot(&tab[s0]); g0 = !slot_empty(e) && (e.tag & btm) != btm; }
+        if (s0 + 1 < hsize) { Slot e = ld_slot(&tab[s0 + 1]); g1 = !slot_empty(e) && (e.tag & btm) != btm; }
+        int total;
+        int ex = block_excl_scan((int)g0 + (int)g1, S->wsum, total);
+        unsigned base = S->e_cnt + (unsigned)ex;
+        if (g0) S->E[base++ & (EQ_CAP - 1)] = (int)s0;
+        if (g1) S->E[base & (EQ_CAP - 1)] = (int)(s0 + 1);
+        __syncthreads();
+        if (tid == 0) {
+            S->e_cnt += (unsigned)total;
+            i64 ns = scan + 2 * AT;
+            S->e_scan = ns < hsize ? ns : hsize;
+        }
+    }
+}
+
+// After a serial op (thread 0): bring the queue back in step with what the op wrote.
+__device__ __forceinline__ void sync_queue(Smem *S, int nlog) {
+    for (int w = 0; w < nlog; w++) {
+        int sl = S->wlog[w] >> 1;
+        if (S->wlog[w] & 1) {                    // zeroed by clean_one: consume the queue up to it
+            while (S->e_idx != S->e_cnt && S->E[S->e_idx & (EQ_CAP - 1)] <= sl) S->e_idx++;
+        } else if (sl < S->e_scan) {             // overwritten by an insert: if queued, cut the queue there
+            unsigned a = S->e_idx, b = S->e_cnt;
+            while (a != b) {
+                unsigned m = a + (b - a) / 2;
+                if (S->E[m & (EQ_CAP - 1)] < sl) a = m + 1; else b = m;
+            }
+            if (a != S->e_cnt && S->E[a & (EQ_CAP - 1)] == sl) { S->e_cnt = a; S->e_scan = sl; }
+        }
+    }
+}
+
 // Runs the automaton over the current segment's candidate list (or to the end of the chunk).
-__global__ void __launch_bounds__(32, 1)
+__global__ void __launch_bounds__(AT, 1)
 k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx, AutoState *st,
             const i64 *__restrict__ tile_off, const u32 *__restrict__ cand_pos,
             const i64 *__restrict__ cand_tag, Token *toks) {
     if (st->done || st->error) return;
-    __shared__ i64 hx[256];
-    __shared__ i64 stk[3 * 64];
-    const int lane = threadIdx.x;
-    for (int i = lane; i < 256; i += 32) hx[i] = hidx[i];
-    __syncwarp();
-
-    Warp w;
-    w.buf = buf; w.tab = tab; w.toks = toks; w.lane = lane;
-    w.n = st->n; w.end = st->end; w.hmask = st->hmask; w.hsize = st->hsize; w.limit = st->limit;
-    w.tok_cap = st->tok_cap; w.chain = st->chain;
-    w.p = st->p; w.last = st->last; w.cur_p = st->cur_p; w.cur_len = st->cur_len; w.cur_ofs = st->cur_ofs;
-    w.min_mask = st->min_mask; w.ins_mask = st->ins_mask; w.clean_ptr = st->clean_ptr; w.count = st->count;
-    w.vr = st->victim_round;
-    w.hits = st->tag_hits; w.misses = st->tag_misses; w.inserts = st->inserts; w.vevents = st->victim_events;
-    w.nops = st->n_ops; w.ntok = st->ntok; w.error = 0;
-
+    MRZ_SMEM_PTR(Smem, S);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid < 256) S->hx[tid] = hidx[tid];
+    const i64 n = st->n, end = st->end, hmask = st->hmask, hsize = st->hsize, limit = st->limit;
+    const int chain = st->chain;
     const i64 seg_lo = st->seg_lo, seg_hi = st->seg_hi, ncand = st->seg_ncand;
-    i64 i = 0;
-    while (i < ncand && !w.error) {
-        i64 idx = i + lane;
-        u32 rp = 0; i64 tg = 0;
-        if (idx < ncand) { rp = __ldcg(cand_pos + idx); tg = __ldcg(cand_tag + idx); }
-        int cnt = (ncand - i) < 32 ? (int)(ncand - i) : 32;
-        bool jumped = false;
-        for (int j = 0; j < cnt; j++) {
-            i64 pj = seg_lo + (i64)__shfl_sync(FULL, rp, j);
-            i64 tj = __shfl_sync(FULL, tg, j);
-            if (pj <= w.p) continue;
-            if ((tj & w.min_mask) != w.min_mask) continue;
-            w.p = pj;
-            if (w.op(pj, tj, stk)) { jumped = true; break; }
+    if (tid == 0) {
+        Run &r = S->run;
+        r.p = st->p; r.last = st->last; r.cur_p = st->cur_p; r.cur_len = st->cur_len; r.cur_ofs = st->cur_ofs;
+        r.min_mask = st->min_mask; r.ins_mask = st->ins_mask; r.clean_ptr = st->clean_ptr; r.count = st->count;
+        r.vr = st->victim_round;
+        r.hits = st->tag_hits; r.misses = st->tag_misses; r.inserts = st->inserts; r.vevents = st->victim_events;
+        r.nops = st->n_ops; r.ntok = st->ntok; r.error = 0;
+        S->e_idx = S->e_cnt = 0; S->e_scan = r.clean_ptr;
+        S->li = 0; S->bmax = AT;
+    }
+    Warp w;   // used by warp 0 only
+    w.buf = buf; w.tab = tab; w.toks = toks; w.lane = lane;
+    w.n = n; w.end = end; w.hmask = hmask; w.hsize = hsize; w.limit = limit; w.tok_cap = st->tok_cap; w.chain = chain;
+    w.wlog = S->wlog; w.nlog = 0; w.clean_hint = 0;
+    __syncthreads();
+
+    for (;;) {
+        // ---------------------------------------------------------------- batch set-up
+        if (S->run.error || S->li >= ncand) break;
+        const i64 min_mask = S->run.min_mask, ins_mask = S->run.ins_mask;
+        const i64 btm = (min_mask << 1) | 1;
+        const bool steady = ins_mask == btm;   // inserts can no longer create sweep-eligible entries
+        const int bmax = S->bmax;
+        if (steady) {
+            if (tid == 0 && S->e_scan < S->run.clean_ptr) S->e_scan = S->run.clean_ptr;
+            refill_queue(S, tab, hsize, bmax);
+        } else if (tid == 0) {
+            S->e_idx = S->e_cnt = 0; S->e_scan = S->run.clean_ptr;
         }
-        if (!jumped) { i += 32; continue; }
-        // ---- after a match: p jumped to last_match.  Examine the next positions directly from the
-        // bytes (dense-match regime), then re-synchronise with the list.
+        __syncthreads();
+        const i64 w_lo = S->run.clean_ptr, w_hi = steady ? S->e_scan : S->run.clean_ptr;
+        // ---------------------------------------------------------------- gather the next candidates
+        int nr = 0;
+        i64 li = S->li;
+        const i64 p_now = S->run.p;
         for (;;) {
-            if (w.error || w.p >= w.end) break;
-            i64 base = w.p + 1;                       // positions base + lane
-            i64 v0 = hx[__ldg(buf + base + lane)];
-            i64 v1 = hx[__ldg(buf + base + 32 + lane)];
-            i64 P0 = xor_scan_incl(v0, lane);
-            i64 tot0 = __shfl_sync(FULL, P0, 31);
-            i64 P1 = tot0 ^ xor_scan_incl(v1, lane);
-            int hi_i = lane + 30;
-            i64 a0 = __shfl_sync(FULL, P0, hi_i & 31);
-            i64 a1 = __shfl_sync(FULL, P1, hi_i & 31);
-            i64 lo_v = __shfl_up_sync(FULL, P0, 1);
-            if (lane == 0) lo_v = 0;
-            i64 tq = (hi_i < 32 ? a0 : a1) ^ lo_v;
-            bool again = false;
-            int lim = (w.end - w.p) < 32 ? (int)(w.end - w.p) : 32;   // positions base..min(base+31,end)
-            for (int j = 0; j < lim; j++) {
-                i64 tj = __shfl_sync(FULL, tq, j);
-                if ((tj & w.min_mask) != w.min_mask) continue;
-                w.p = base + j;
-                if (w.op(base + j, tj, stk)) { again = true; break; }
+            int room = bmax - nr;
+            if (room <= 0 || li >= ncand) break;
+            int m = (ncand - li) < room ? (int)(ncand - li) : room;
+            bool valid = false;
+            u32 rp = 0; i64 tg = 0;
+            if (tid < m) {
+                rp = __ldcg(cand_pos + li + tid); tg = __ldcg(cand_tag + li + tid);
+                valid = seg_lo + (i64)rp > p_now && (tg & min_mask) == min_mask;
             }
-            if (again) continue;
-            w.p = base + lim - 1;
-            break;
+            int total;
+            int ex = block_excl_scan((int)valid, S->wsum, total);
+            if (valid) { S->b_rel[nr + ex] = rp; S->b_tag[nr + ex] = tg; S->b_li[nr + ex] = (int)(li + tid); }
+            nr += total;
+            li += m;
+            if (nr * 2 >= bmax) break;
         }
-        if (w.error || w.p >= w.end || w.p + 1 >= seg_hi) break;
-        {
-            i64 rel = w.p + 1 - seg_lo;
-            i64 tile = rel / SCAN_TILE;
-            i = list_seek(cand_pos, tile_off[tile], tile_off[tile + 1], (u32)rel, lane);
+        __syncthreads();
+        if (nr == 0) { if (tid == 0) S->li = li; __syncthreads(); continue; }
+        // ---------------------------------------------------------------- phase A: plan
+        Plan pl;
+        pl.flags = F_COMPLEX; pl.dcount = 0;
+        i64 my_pos = 0, my_tag = 0;
+        for (int q = tid; q < WH_CAP; q += AT) { S->wh_key[q] = -1; S->wh_val[q] = 0x7fffffff; }
+        if (tid < nr) {
+            my_pos = seg_lo + (i64)S->b_rel[tid]; my_tag = S->b_tag[tid];
+            plan_op(pl, tab, my_tag, hmask, hsize, min_mask, ins_mask, chain, w_lo, w_hi);
         }
+        __syncthreads();
+        const bool planned_ins = tid < nr && (pl.flags & (F_COMPLEX | F_INSERT)) == F_INSERT;
+        if (planned_ins) {
+            wh_insert(S, pl.w2_slot, tid);
+            if (pl.flags & F_W1) wh_insert(S, pl.w1_slot, tid);
+        }
+        __syncthreads();
+        if (tid < nr && !(pl.flags & F_COMPLEX)) {
+            if (wh_range_hit(S, pl.rd_lo, pl.rd_hi, tid) ||
+                (pl.rd2_lo >= 0 && wh_range_hit(S, pl.rd2_lo, pl.rd2_hi, tid)))
+                pl.flags |= F_CONF;
+        }
+        {   // inclusive prefix of (insert count, dcount) over ops that still hold a valid plan
+            int v = (tid < nr && (pl.flags & (F_COMPLEX | F_CONF | F_INSERT)) == F_INSERT) ? ((1 << 16) | pl.dcount) : 0;
+            int total;
+            int ex = block_excl_scan(v, S->wsum, total);
+            S->pre[tid] = ex + v;
+        }
+        if (tid == 0) { S->pos = 0; S->ended = 0; S->jumped = 0; }
+        __syncthreads();
+        // ---------------------------------------------------------------- phase B: in-order commit
+        for (;;) {
+            const int pos = S->pos;
+            const int base = pos ? S->pre[pos - 1] : 0;
+            const i64 cnt0 = S->run.count;
+            const int avail = (int)(S->e_cnt - S->e_idx);
+            const i64 cur_len = S->run.cur_len, cur_p = S->run.cur_p;
+            int cut = nr;
+            if (tid >= pos && tid < nr) {
+                bool c = (pl.flags & (F_COMPLEX | F_CONF)) != 0;
+                c = c || (cur_len >= MRZ_MIN_MATCH && my_pos >= cur_p + MRZ_MIN_MATCH);   // an emission is due
+                if (!c && (pl.flags & F_INSERT) && pl.dcount == 1) {
+                    i64 T = cnt0 + ((S->pre[tid] - base) & 0xffff);
+                    if (T > limit && (!steady || T - limit > avail)) c = true;             // needs a serial sweep step
+                }
+                if (c) cut = tid;
+            }
+            const int k = block_min(cut, &S->red);
+            // commit [pos, k)
+            if (tid >= pos && tid < k && (pl.flags & F_INSERT)) {
+                if (pl.flags & F_W1) st_slot(&tab[pl.w1_slot], pl.w1_off, pl.w1_tag);
+                st_slot(&tab[pl.w2_slot], my_pos, my_tag);
+            }
+            int cleans = 0;
+            if (k > pos) {
+                const int d = S->pre[k - 1] - base;
+                i64 T = cnt0 + (d & 0xffff);
+                cleans = T > limit ? (int)(T - limit) : 0;
+                if (tid < cleans) st_slot(&tab[S->E[(S->e_idx + tid) & (EQ_CAP - 1)]], 0, 0);
+                __syncthreads();   // everyone has read run.count / e_idx
+                if (tid == 0) {
+                    Run &r = S->run;
+                    r.count = T - cleans;
+                    r.inserts += d >> 16;
+                    r.nops += k - pos;
+                    r.p = seg_lo + (i64)S->b_rel[k - 1];
+                    if (cleans) {
+                        S->e_idx += (unsigned)cleans;
+                        r.clean_ptr = S->E[(S->e_idx - 1) & (EQ_CAP - 1)];   // pointer stays on the last zeroed slot
+                    }
+                }
+            }
+            if (k >= nr) { __syncthreads(); break; }
+            __syncthreads();
+            // ---- op k on the live table, reference semantics (warp 0)
+            if (wid == 0) {
+                w.load(S->run);
+                w.nlog = 0;
+                i64 hint = w.clean_ptr;
+                if (steady) hint = (S->e_cnt != S->e_idx) ? (i64)S->E[S->e_idx & (EQ_CAP - 1)] : (S->e_scan > hint ? S->e_scan : hint);
+                w.clean_hint = hint;
+                const i64 pk = seg_lo + (i64)S->b_rel[k], tk = S->b_tag[k];
+                w.p = pk;
+                bool jumped = w.op(pk, tk, S->stk);
+                w.clean_hint = 0;
+                if (jumped && !w.error) {
+                    // dense-match regime: examine the next positions directly from the bytes until a
+                    // window of 32 positions passes without an emission, then re-synchronise with the list
+                    for (;;) {
+                        if (w.error || w.p >= w.end) break;
+                        i64 b0 = w.p + 1;                       // positions b0 + lane
+                        i64 v0 = S->hx[__ldg(buf + b0 + lane)];
+                        i64 v1 = S->hx[__ldg(buf + b0 + 32 + lane)];
+                        i64 P0 = xor_scan_incl(v0, lane);
+                        i64 tot0 = __shfl_sync(FULL, P0, 31);
+                        i64 P1 = tot0 ^ xor_scan_incl(v1, lane);
+                        int hi_i = lane + 30;
+                        i64 a0 = __shfl_sync(FULL, P0, hi_i & 31);
+                        i64 a1 = __shfl_sync(FULL, P1, hi_i & 31);
+                        i64 lo_v = __shfl_up_sync(FULL, P0, 1);
+                        if (lane == 0) lo_v = 0;
+                        i64 tq = (hi_i < 32 ? a0 : a1) ^ lo_v;
+                        bool again = false;
+                        int lim = (w.end - w.p) < 32 ? (int)(w.end - w.p) : 32;   // positions b0..min(b0+31,end)
+                        for (int j = 0; j < lim; j++) {
+                            i64 tj = __shfl_sync(FULL, tq, j);
+                            if ((tj & w.min_mask) != w.min_mask) continue;
+                            w.p = b0 + j;
+                            if (w.op(b0 + j, tj, S->stk)) { again = true; break; }
+                        }
+                        if (again) continue;
+                        w.p = b0 + lim - 1;
+                        break;
+                    }
+                    i64 nli = ncand;
+                    if (!w.error && w.p < w.end && w.p + 1 < seg_hi) {
+                        i64 rel = w.p + 1 - seg_lo;
+                        i64 tile = rel / SCAN_TILE;
+                        nli = list_seek(cand_pos, tile_off[tile], tile_off[tile + 1], (u32)rel, lane);
+                    }
+                    if (lane == 0) S->li = nli;
+                }
+                w.store(S->run);
+                if (lane == 0) {
+                    bool mask_changed = w.min_mask != min_mask || w.ins_mask != ins_mask;
+                    bool overflow = w.nlog > WLOG_CAP;
+                    S->jumped = jumped;
+                    S->nlog = overflow ? 0 : w.nlog;
+                    if (jumped || mask_changed || overflow || w.error) {
+                        S->ended = 1;
+                        S->e_idx = S->e_cnt = 0; S->e_scan = w.clean_ptr;    // rebuild the queue
+                        if (!jumped) S->li = (i64)S->b_li[k] + 1;
+                    } else {
+                        if (steady) sync_queue(S, w.nlog);
+                        S->pos = k + 1;
+                    }
+                }
+            }
+            __syncthreads();
+            if (S->ended) break;
+            // later plans that read a slot this op wrote are no longer valid
+            if (tid > k && tid < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
+                const int nl = S->nlog;
+                for (int q = 0; q < nl; q++) {
+                    int sl = S->wlog[q] >> 1;
+                    if ((sl >= pl.rd_lo && sl <= pl.rd_hi) || (pl.rd2_lo >= 0 && sl >= pl.rd2_lo && sl <= pl.rd2_hi)) {
+                        pl.flags |= F_CONF;
+                        break;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        // ---------------------------------------------------------------- batch epilogue
+        if (tid == 0) {
+            if (!S->ended) S->li = li;                       // whole batch consumed
+            // batch size: small after an emission (the plans behind a jump are wasted), growing back
+            if (S->jumped) S->bmax = 64;
+            else if (S->bmax < AT) S->bmax *= 2;
+        }
+        __syncthreads();
     }
     // segment exhausted (or chunk finished)
-    if (!w.error && w.p < seg_hi - 1) w.p = seg_hi - 1;
-    if (lane == 0) {
-        st->p = w.p; st->last = w.last; st->cur_p = w.cur_p; st->cur_len = w.cur_len; st->cur_ofs = w.cur_ofs;
-        st->min_mask = w.min_mask; st->ins_mask = w.ins_mask; st->clean_ptr = w.clean_ptr; st->count = w.count;
-        st->victim_round = w.vr;
-        st->tag_hits = w.hits; st->tag_misses = w.misses; st->inserts = w.inserts; st->victim_events = w.vevents;
-        st->n_ops = w.nops; st->ntok = w.ntok;
-        if (w.error) st->error = w.error;
-        if (w.p >= w.end) st->done = 1;
+    if (tid == 0) {
+        const Run &r = S->run;
+        i64 p = r.p;
+        if (!r.error && p < seg_hi - 1) p = seg_hi - 1;
+        st->p = p; st->last = r.last; st->cur_p = r.cur_p; st->cur_len = r.cur_len; st->cur_ofs = r.cur_ofs;
+        st->min_mask = r.min_mask; st->ins_mask = r.ins_mask; st->clean_ptr = r.clean_ptr; st->count = r.count;
+        st->victim_round = r.vr;
+        st->tag_hits = r.hits; st->tag_misses = r.misses; st->inserts = r.inserts; st->victim_events = r.vevents;
+        st->n_ops = r.nops; st->ntok = r.ntok;
+        if (r.error) st->error = r.error;
+        if (p >= end) st->done = 1;
     }
 }
 
 extern "C" void mrz_launch_automaton(const u8 *buf, Slot *tab, const i64 *hidx, AutoState *st, const i64 *tile_off,
                                      const u32 *cand_pos, const i64 *cand_tag, Token *toks, cudaStream_t s) {
-    MRZ_LAUNCH(k_automaton, 1, 32, s, buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks);
+#ifndef MRZ_CUSIM
+    cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks);
+#else
+    MRZ_LAUNCH(k_automaton, 1, AT, s, buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks);
+#endif
 }

@@ -213,7 +213,7 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     ctx->d_buf = ctx->d_buf_alloc + MRZ_PAD;
     CK(cudaMemset(ctx->d_buf_alloc, 0, MRZ_PAD));
     ctx->tab_slots = (i64)64 * 65536;  // largest levels[].mb_used = 64 MiB
-    CK(cudaMalloc(&ctx->d_tab, (size_t)ctx->tab_slots * sizeof(Slot)));
+    CK(cudaMalloc(&ctx->d_tab, (size_t)(ctx->tab_slots + 8) * sizeof(Slot)));  // + slack for 4-slot probe loads
     CK(cudaMalloc(&ctx->d_hidx, 256 * 8));
     CK(cudaMalloc(&ctx->d_st, sizeof(AutoState)));
     CK(cudaMalloc(&ctx->d_tile_cnt, (SEG_MAX_TILES + 1) * sizeof(int)));
@@ -291,7 +291,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaEventRecord(ctx->ev[0], s));
     CK(cudaMemcpyAsync(ctx->d_hidx, prm->hash_index, 256 * 8, cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(ctx->d_st, &h, sizeof h, cudaMemcpyHostToDevice, s));
-    CK(cudaMemsetAsync(ctx->d_tab, 0, (size_t)h.hsize * sizeof(Slot), s));  // rzip.c:518-519
+    CK(cudaMemsetAsync(ctx->d_tab, 0, (size_t)(h.hsize + 8) * sizeof(Slot), s));  // rzip.c:518-519
     CK(cudaMemsetAsync(ctx->d_tot, 0, sizeof(EmitTotals), s));
     launches += 2;
     // CRC of the chunk (independent of the automaton)
