@@ -524,9 +524,14 @@ __device__ __forceinline__ void sync_queue(Smem *S, int nlog) {
 __global__ void __launch_bounds__(AT, 1)
 k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx, AutoState *st,
             const i64 *__restrict__ tile_off, const u32 *__restrict__ cand_pos,
-            const i64 *__restrict__ cand_tag, Token *toks) {
+            const i64 *__restrict__ cand_tag, Token *toks, i64 *dbg) {
     if (st->done || st->error) return;
     MRZ_SMEM_PTR(Smem, S);
+    i64 tm[12];
+#pragma unroll
+    for (int q = 0; q < 12; q++) tm[q] = 0;
+    i64 t_prev = clock64();
+#define TICK(slot) do { i64 t_now = clock64(); tm[slot] += t_now - t_prev; t_prev = t_now; } while (0)
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (tid < 256) S->hx[tid] = hidx[tid];
     const i64 n = st->n, end = st->end, hmask = st->hmask, hsize = st->hsize, limit = st->limit;
@@ -562,6 +567,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
             S->e_idx = S->e_cnt = 0; S->e_scan = S->run.clean_ptr;
         }
         __syncthreads();
+        TICK(0);   // queue refill
         const i64 w_lo = S->run.clean_ptr, w_hi = steady ? S->e_scan : S->run.clean_ptr;
         // ---------------------------------------------------------------- gather the next candidates
         int nr = 0;
@@ -585,7 +591,9 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
             if (nr * 2 >= bmax) break;
         }
         __syncthreads();
+        TICK(1);   // gather
         if (nr == 0) { if (tid == 0) S->li = li; __syncthreads(); continue; }
+        tm[8] += nr; tm[9] += 1;
         // ---------------------------------------------------------------- phase A: plan
         Plan pl;
         pl.flags = F_COMPLEX; pl.dcount = 0;
@@ -596,6 +604,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
             plan_op(pl, tab, my_tag, hmask, hsize, min_mask, ins_mask, chain, w_lo, w_hi);
         }
         __syncthreads();
+        TICK(2);   // plan
         const bool planned_ins = tid < nr && (pl.flags & (F_COMPLEX | F_INSERT)) == F_INSERT;
         if (planned_ins) {
             wh_insert(S, pl.w2_slot, tid);
@@ -615,6 +624,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
         }
         if (tid == 0) { S->pos = 0; S->ended = 0; S->jumped = 0; }
         __syncthreads();
+        TICK(3);   // conflicts + prefix
         // ---------------------------------------------------------------- phase B: in-order commit
         for (;;) {
             const int pos = S->pos;
@@ -657,8 +667,10 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
                     }
                 }
             }
-            if (k >= nr) { __syncthreads(); break; }
+            if (k >= nr) { __syncthreads(); TICK(4); break; }
             __syncthreads();
+            TICK(4);   // cut search + commit
+            tm[10] += 1;
             // ---- op k on the live table, reference semantics (warp 0)
             if (wid == 0) {
                 w.load(S->run);
@@ -724,6 +736,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
                 }
             }
             __syncthreads();
+            TICK(5);   // serial op
             if (S->ended) break;
             // later plans that read a slot this op wrote are no longer valid
             if (tid > k && tid < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
@@ -737,6 +750,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
                 }
             }
             __syncthreads();
+            TICK(6);   // invalidation
         }
         // ---------------------------------------------------------------- batch epilogue
         if (tid == 0) {
@@ -746,7 +760,10 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
             else if (S->bmax < AT) S->bmax *= 2;
         }
         __syncthreads();
+        TICK(7);
     }
+    if (tid == 0 && dbg)
+        for (int q = 0; q < 12; q++) dbg[q] += tm[q];
     // segment exhausted (or chunk finished)
     if (tid == 0) {
         const Run &r = S->run;
@@ -763,11 +780,11 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
 }
 
 extern "C" void mrz_launch_automaton(const u8 *buf, Slot *tab, const i64 *hidx, AutoState *st, const i64 *tile_off,
-                                     const u32 *cand_pos, const i64 *cand_tag, Token *toks, cudaStream_t s) {
+                                     const u32 *cand_pos, const i64 *cand_tag, Token *toks, i64 *dbg, cudaStream_t s) {
 #ifndef MRZ_CUSIM
     cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks);
+    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
 #else
-    MRZ_LAUNCH(k_automaton, 1, AT, s, buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks);
+    MRZ_LAUNCH(k_automaton, 1, AT, s, buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
 #endif
 }

@@ -16,7 +16,7 @@ extern "C" {
 void mrz_launch_scan(const u8 *, const i64 *, AutoState *, int *, i64 *, u32 *, i64 *, int, cudaStream_t);
 void mrz_launch_debug_tags(const u8 *, const i64 *, i64, i64, i64 *, cudaStream_t);
 void mrz_launch_automaton(const u8 *, Slot *, const i64 *, AutoState *, const i64 *, const u32 *, const i64 *,
-                          Token *, cudaStream_t);
+                          Token *, i64 *, cudaStream_t);
 void mrz_crc_upload_consts(const void *);
 void mrz_launch_crc(const u8 *, i64, u32 *, u32 *, u32 *, cudaStream_t, int *);
 void mrz_launch_exclusive_scan(const i64 *, i64 *, i64, i64 *, i64 *, cudaStream_t, int *);
@@ -44,6 +44,8 @@ struct mrz_ctx {
     Token *d_toks; i64 tok_cap;
     i64 *d_a0, *d_a1, *d_off0, *d_off1, *d_bsum; i64 item_cap;
     EmitTotals *d_tot;
+    i64 *d_dbg;          // phase cycle counters of k_automaton (MRZ_PROFILE=1), else NULL
+    i64 h_dbg[12];
     u8 *d_s0; i64 s0_cap; u8 *d_s1; i64 s1_cap;
     u32 *d_crc_part, *d_crc_part2, *d_crc_misc;  // misc[0]=tail, misc[1]=final
     // host staging
@@ -191,7 +193,7 @@ extern "C" void mrz_ctx_destroy(mrz_ctx *ctx) {
     cudaFree(ctx->d_buf_alloc); cudaFree(ctx->d_tab); cudaFree(ctx->d_hidx); cudaFree(ctx->d_st);
     cudaFree(ctx->d_tile_cnt); cudaFree(ctx->d_tile_off); cudaFree(ctx->d_cand_pos); cudaFree(ctx->d_cand_tag);
     cudaFree(ctx->d_toks); cudaFree(ctx->d_a0); cudaFree(ctx->d_a1); cudaFree(ctx->d_off0); cudaFree(ctx->d_off1);
-    cudaFree(ctx->d_bsum); cudaFree(ctx->d_tot); cudaFree(ctx->d_s0); cudaFree(ctx->d_s1);
+    cudaFree(ctx->d_bsum); cudaFree(ctx->d_tot); cudaFree(ctx->d_dbg); cudaFree(ctx->d_s0); cudaFree(ctx->d_s1);
     cudaFree(ctx->d_crc_part); cudaFree(ctx->d_crc_part2); cudaFree(ctx->d_crc_misc);
     free(ctx->h_crc);
     for (auto &e : ctx->ev)
@@ -221,6 +223,7 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     CK(cudaMalloc(&ctx->d_cand_pos, (size_t)(SEG_CAND_CAP + 64) * sizeof(u32)));
     CK(cudaMalloc(&ctx->d_cand_tag, (size_t)(SEG_CAND_CAP + 64) * sizeof(i64)));
     CK(cudaMalloc(&ctx->d_tot, sizeof(EmitTotals)));
+    if (getenv("MRZ_PROFILE")) CK(cudaMalloc(&ctx->d_dbg, 12 * 8));
     CK(cudaMalloc(&ctx->d_s1, (size_t)max_chunk + 64));
     ctx->s1_cap = max_chunk + 64;
     i64 nblk = max_chunk / 16384 + 1;
@@ -293,6 +296,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaMemcpyAsync(ctx->d_st, &h, sizeof h, cudaMemcpyHostToDevice, s));
     CK(cudaMemsetAsync(ctx->d_tab, 0, (size_t)(h.hsize + 8) * sizeof(Slot), s));  // rzip.c:518-519
     CK(cudaMemsetAsync(ctx->d_tot, 0, sizeof(EmitTotals), s));
+    if (ctx->d_dbg) CK(cudaMemsetAsync(ctx->d_dbg, 0, 12 * 8, s));
     launches += 2;
     // CRC of the chunk (independent of the automaton)
     mrz_launch_crc(ctx->d_buf, n, ctx->d_crc_part, ctx->d_crc_part2, ctx->d_crc_misc, s, &launches);
@@ -310,7 +314,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
                         ctx->d_cand_tag, tiles, s);
         CK(cudaEventRecord(ctx->ev[2], s));
         mrz_launch_automaton(ctx->d_buf, ctx->d_tab, ctx->d_hidx, ctx->d_st, ctx->d_tile_off, ctx->d_cand_pos,
-                             ctx->d_cand_tag, ctx->d_toks, s);
+                             ctx->d_cand_tag, ctx->d_toks, ctx->d_dbg, s);
         CK(cudaEventRecord(ctx->ev[3], s));
         launches += 4;
         i64 prev_p = h.p;
@@ -335,6 +339,14 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
         }
     }
 
+    if (ctx->d_dbg) {
+        CK(cudaMemcpyAsync(ctx->h_dbg, ctx->d_dbg, 12 * 8, cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        static const char *nm[12] = {"refill", "gather", "plan", "conflict", "commit", "serial", "inval", "epilogue", "ops", "batches", "serial_ops", ""};
+        fprintf(stderr, "[mrz profile] automaton cycles:");
+        for (int q = 0; q < 11; q++) fprintf(stderr, " %s=%lld", nm[q], (long long)ctx->h_dbg[q]);
+        fprintf(stderr, "\n");
+    }
     // ---- emission ----
     CK(cudaEventRecord(ctx->ev[1], s));
     i64 m = h.ntok, items = m + 1;

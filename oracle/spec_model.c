@@ -12,8 +12,9 @@
  * product links this file.
  */
 #include "rzip_oracle.c"
+#include <stdio.h>
 
-enum { F_SKIP = 1, F_COMPLEX = 2, F_INSERT = 4, F_W1 = 8 };
+enum { F_SKIP = 1, F_COMPLEX = 2, F_INSERT = 4, F_W1 = 8, F_FOLLOW = 16 };
 #define MAXWALK 16384
 
 typedef struct {
@@ -30,47 +31,93 @@ typedef struct {
 
 static int nonempty(const slot *s) { return (s->off | s->tag) != 0; }
 
+/* Tag filter: one 64-bit word per hash bucket, 3 bits per tag (blocked Bloom filter).  No false
+ * negatives: every tag ever inserted into the table during this chunk has its bits set, so a
+ * negative answer proves that no entry with this tag exists => the lookup walk can be skipped. */
+#define FILT_BITS 24
+typedef uint64_t u64;
+static inline void filt_hash(i64 tag, u64 *word, u64 *bits) {
+    u64 x = (u64)tag;
+    x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+    *word = x >> (64 - FILT_BITS);
+    *bits = ((u64)1 << (x & 63)) | ((u64)1 << ((x >> 6) & 63)) | ((u64)1 << ((x >> 12) & 63));
+}
+static inline int filt_query(const u64 *F, i64 tag) { u64 w, b; filt_hash(tag, &w, &b); return (F[w] & b) == b; }
+static inline void filt_set(u64 *F, i64 tag) { u64 w, b; filt_hash(tag, &w, &b); F[w] |= b; }
+
 /* phase A: plan one op against the current table without modifying anything */
-static void plan_op(const ctx *c, rec *r, i64 pos, i64 tag, i64 ins_mask, i64 w_lo, i64 w_hi) {
+static void plan_op(const ctx *c, const u64 *F, rec *r, i64 pos, i64 tag, i64 ins_mask, i64 w_lo, i64 w_hi) {
     memset(r, 0, sizeof *r);
     r->pos = pos; r->tag = tag; r->rd2_lo = -1;
-    i64 h0 = tag & c->hmask, h = h0, steps = 0;
-    while (nonempty(&c->tab[h])) {
-        if (c->tab[h].tag == tag) { r->flags |= F_COMPLEX; return; }
-        if (++h == c->hsize || ++steps > MAXWALK) { r->flags |= F_COMPLEX; return; }
-    }
-    r->rd_lo = h0; r->rd_hi = h;
-    if ((tag & ins_mask) == ins_mask) {
-        i64 btm = (c->min_mask << 1) | 1;
-        r->flags |= F_INSERT;
-        for (h = h0; nonempty(&c->tab[h]); h++) {
-            const slot *o = &c->tab[h];
-            if ((o->tag & btm) != btm) { r->w2_slot = h; r->dcount = 0; goto planned; }
-            if (tz1(o->tag) < tz1(tag)) {
-                /* one level of displacement (rzip.c:275-277) */
-                i64 ot = o->tag, g = ot & c->hmask, round = 0, st2 = 0;
-                int d2 = 0;
-                for (;; g++) {
-                    if (g == c->hsize || ++st2 > MAXWALK) { r->flags |= F_COMPLEX; return; }
-                    const slot *q = &c->tab[g];
-                    if (!nonempty(q)) break;
-                    if ((q->tag & btm) != btm) { d2 = -1; break; }
-                    if (tz1(q->tag) < tz1(ot)) { r->flags |= F_COMPLEX; return; }
-                    if (q->tag == ot && ++round == c->chain) { r->flags |= F_COMPLEX; return; }
-                }
-                r->flags |= F_W1;
-                r->rd2_lo = ot & c->hmask; r->rd2_hi = g;
-                r->w1_slot = g; r->w1_off = o->off; r->w1_tag = ot;
-                r->w2_slot = h; r->dcount = 1 + d2;
-                goto planned;
+    r->rd_lo = 1; r->rd_hi = 0;                       /* empty read range */
+    if (filt_query(F, tag)) { r->flags |= F_COMPLEX; return; }   /* an equal tag may exist: match_len, chains */
+    if ((tag & ins_mask) != ins_mask) return;         /* lookup only, and nothing to find */
+    i64 h0 = tag & c->hmask, h, steps = 0;
+    i64 btm = (c->min_mask << 1) | 1;
+    r->flags |= F_INSERT;
+    r->rd_lo = h0;
+    for (h = h0;; h++) {
+        if (h == c->hsize || ++steps > MAXWALK) { r->flags |= F_COMPLEX; return; }
+        const slot *o = &c->tab[h];
+        if (!nonempty(o)) { r->w2_slot = h; r->dcount = 1; break; }
+        if (o->tag == tag) { r->flags |= F_COMPLEX; return; }   /* cannot happen with a sound filter */
+        if ((o->tag & btm) != btm) { r->w2_slot = h; r->dcount = 0; break; }
+        if (tz1(o->tag) < tz1(tag)) {
+            /* one level of displacement (rzip.c:275-277) */
+            i64 ot = o->tag, g = ot & c->hmask, round = 0, st2 = 0;
+            int d2 = 0;
+            for (;; g++) {
+                if (g == c->hsize || ++st2 > MAXWALK) { r->flags |= F_COMPLEX; return; }
+                const slot *q = &c->tab[g];
+                if (!nonempty(q)) break;
+                if ((q->tag & btm) != btm) { d2 = -1; break; }
+                if (tz1(q->tag) < tz1(ot)) { r->flags |= F_COMPLEX; return; }
+                if (q->tag == ot && ++round == c->chain) { r->flags |= F_COMPLEX; return; }
             }
+            r->flags |= F_W1;
+            r->rd2_lo = ot & c->hmask; r->rd2_hi = g;
+            r->w1_slot = g; r->w1_off = o->off; r->w1_tag = ot;
+            r->w2_slot = h; r->dcount = 1 + d2;
+            break;
         }
-        r->w2_slot = h; r->dcount = 1; /* empty slot */
     }
-planned:
+    r->rd_hi = r->w2_slot;
     /* anything touching the clean window is left to the serial path */
     if (r->rd_hi >= w_lo && r->rd_lo < w_hi) r->flags |= F_COMPLEX;
     if (r->rd2_lo >= 0 && r->rd2_hi >= w_lo && r->rd2_lo < w_hi) r->flags |= F_COMPLEX;
+}
+
+/* "Twin": position p+1 has the same tag as p (buf[p] == buf[p+31]) and both pass the gates.  The second op
+ * (B) sees the entry the first (A) has just inserted: its lookup meets exactly that one equal tag (the filter
+ * was negative, so no other exists) and match_len(p+1, p) almost always fails (tag_misses++); its insert walk
+ * passes A's entry (round = 1 < max_chain_len) and goes on from the next slot.  Planned when A's plan is the
+ * simple kind (no displacement); everything else is left to the serial path. */
+static void plan_follower(const ctx *c, const rec *A, rec *B, i64 pos, i64 tag, i64 w_lo, i64 w_hi) {
+    memset(B, 0, sizeof *B);
+    B->pos = pos; B->tag = tag; B->rd2_lo = -1; B->rd_lo = 1; B->rd_hi = 0;
+    if (A->flags & F_COMPLEX) { B->flags |= F_COMPLEX; return; }
+    if (!(A->flags & F_INSERT)) return;               /* both lookup-only, nothing to find */
+    if ((A->flags & F_W1) || c->chain == 1) { B->flags |= F_COMPLEX; return; }
+    i64 rev = 0;
+    if (match_len(c, pos, A->pos, &rev)) { B->flags |= F_COMPLEX; return; }   /* a genuine run: real match */
+    i64 btm = (c->min_mask << 1) | 1, steps = 0, h;
+    B->flags |= F_INSERT | F_FOLLOW;
+    B->rd_lo = A->rd_lo;
+    if ((tag & btm) != btm) {   /* A's own entry is due for sweeping (only before the first overflow): B overwrites it */
+        B->w2_slot = A->w2_slot; B->rd_hi = A->w2_slot; B->dcount = 0;
+        if (B->rd_hi >= w_lo && B->rd_lo < w_hi) B->flags |= F_COMPLEX;
+        return;
+    }
+    for (h = A->w2_slot + 1;; h++) {
+        if (h == c->hsize || ++steps > MAXWALK) { B->flags |= F_COMPLEX; return; }
+        const slot *o = &c->tab[h];
+        if (!nonempty(o)) { B->dcount = 1; break; }
+        if (o->tag == tag) { B->flags |= F_COMPLEX; return; }
+        if ((o->tag & btm) != btm) { B->dcount = 0; break; }
+        if (tz1(o->tag) < tz1(tag)) { B->flags |= F_COMPLEX; return; }
+    }
+    B->w2_slot = h; B->rd_hi = h;
+    if (B->rd_hi >= w_lo && B->rd_lo < w_hi) B->flags |= F_COMPLEX;
 }
 
 static int in_ranges(const rec *r, i64 s) {
@@ -122,6 +169,7 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
         tags[0] = full_tag(&c, 0);
         for (i64 q = 1; q < npos; q++) tags[q] = tags[q - 1] ^ hash_index[buf[q - 1]] ^ hash_index[buf[q + MIN_MATCH - 1]];
     }
+    u64 *F = calloc((size_t)1 << FILT_BITS, sizeof(u64));
     rec *R = malloc((size_t)B * sizeof(rec));
     wkey *W = malloc((size_t)B * 2 * sizeof(wkey));
     char *conf = malloc((size_t)B);
@@ -152,7 +200,13 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
         int nr = 0;
         i64 q = p + 1;
         for (; q <= c.end && nr < B; q++)
-            if ((tags[q] & c.min_mask) == c.min_mask) plan_op(&c, &R[nr++], q, tags[q], ins_mask, w_lo, w_hi);
+            if ((tags[q] & c.min_mask) == c.min_mask) {
+                if (nr > 0 && R[nr - 1].pos == q - 1 && R[nr - 1].tag == tags[q] && !(R[nr - 1].flags & F_FOLLOW) && !getenv("SPEC_NOTWIN"))
+                    plan_follower(&c, &R[nr - 1], &R[nr], q, tags[q], w_lo, w_hi);
+                else
+                    plan_op(&c, F, &R[nr], q, tags[q], ins_mask, w_lo, w_hi);
+                nr++;
+            }
         i64 scanned_to = q - 1; /* positions <= scanned_to were examined for this batch */
         if (!nr) { p = c.end; break; }
         ss->batches++;
@@ -167,7 +221,7 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
         for (int j = 0; j < nr; j++) {
             conf[j] = 0;
             if (R[j].flags & F_COMPLEX) { ss->complex_ops++; continue; }
-            if (range_hit(W, nw, R[j].rd_lo, R[j].rd_hi, j) ||
+            if (range_hit(W, nw, R[j].rd_lo, R[j].rd_hi, (R[j].flags & F_FOLLOW) ? j - 1 : j) ||
                 (R[j].rd2_lo >= 0 && range_hit(W, nw, R[j].rd2_lo, R[j].rd2_hi, j))) { conf[j] = 1; ss->static_conflicts++; }
         }
         /* ---- phase B */
@@ -196,6 +250,9 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
                 stats->inserts++;
                 if (R[j].flags & F_W1) { c.tab[R[j].w1_slot].off = R[j].w1_off; c.tab[R[j].w1_slot].tag = R[j].w1_tag; stats->displaced++; }
                 c.tab[R[j].w2_slot].off = R[j].pos; c.tab[R[j].w2_slot].tag = R[j].tag;
+                if (R[j].flags & F_FOLLOW) { stats->tag_misses++;
+                    }
+                filt_set(F, R[j].tag);
                 ss->planned_commits++;
             }
             for (i64 e = 0; e < cleans; e++) { c.tab[E[e_idx + e]].off = 0; c.tab[E[e_idx + e]].tag = 0; }
@@ -211,6 +268,7 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
             c.nlog = 0;
             i64 best = 0, bofs = 0, brev = 0;
             stats->lookups++;
+            if (filt_query(F, t))   /* a negative filter proves the walk would find nothing */
             for (i64 h = t & c.hmask; nonempty(&c.tab[h]); h = (h + 1) & c.hmask)
                 if (c.tab[h].tag == t) {
                     i64 rev = 0, m = match_len(&c, p, c.tab[h].off, &rev);
@@ -221,6 +279,7 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
                 stats->inserts++;
                 c.count++;
                 insert(&c, t, p);
+                filt_set(F, t);
                 if (c.count > c.limit) ins_mask = clean_one(&c);
             }
             if (best > cur.len) { cur.p = p - brev; cur.len = best; cur.ofs = bofs; }
@@ -246,6 +305,7 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
             }
             if (c.min_mask != old_min || ins_mask != old_ins) { e_idx = e_cnt = 0; e_scan = c.clean_ptr; } /* new mask: rebuild */
             if (jumped || c.min_mask != old_min || ins_mask != old_ins) { ended = 1; break; }
+            if (k + 1 < nr && (R[k + 1].flags & F_FOLLOW)) conf[k + 1] = 1;   /* its plan assumed the leader's planned write */
             for (int j = k + 1; j < nr; j++)
                 if (!conf[j] && !(R[j].flags & F_COMPLEX))
                     for (int w = 0; w < c.nlog; w++)
@@ -261,6 +321,6 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
     s0_put(&c, cb4, 4);
     stats->final_min_mask = c.min_mask;
     *s0_len = c.s0_len; *s1_len = c.s1_len;
-    free(c.tab); free(tags); free(R); free(W); free(conf); free(E);
+    free(c.tab); free(tags); free(F); free(R); free(W); free(conf); free(E);
     return c.overflow ? -1 : 0;
 }

@@ -183,6 +183,7 @@ template <class T> static inline T __ldg(const T *p) { return *p; }
 template <class T> static inline T __ldcg(const T *p) { return *(const volatile T *)p; }
 static inline longlong2 __ldcg(const longlong2 *p) { longlong2 v; v.x = ((const volatile long long *)p)[0]; v.y = ((const volatile long long *)p)[1]; return v; }
 template <class T> static inline void __stcg(T *p, T v) { *p = v; }
+static inline long long clock64() { return (long long)__builtin_ia32_rdtsc(); }
 static inline void __threadfence() {}
 static inline void __threadfence_block() {}
 static inline void __nanosleep(unsigned) {}
