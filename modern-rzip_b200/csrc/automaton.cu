@@ -17,6 +17,11 @@
 //     ops - is executed by warp 0 on the live table with the reference semantics (32-slot probe,
 //     ballots for walk termination / equal-tag chains / the victim index, 256-byte-per-step
 //     match extension), after which later plans that read a slot it wrote are invalidated.
+//   * TAG FILTER: a blocked Bloom filter over every tag inserted in this chunk (one 64-bit word,
+//     three bits per tag, no false negatives).  A negative answer proves that no entry with an
+//     equal tag exists, so find_best_match's walk to the end of the probe cluster - hundreds of
+//     slots at high mask levels - is skipped altogether, and lookup-only ops touch no table slot.
+//   * TWINS: positions p and p+1 with equal tags (buf[p] == buf[p+31]) are planned as a pair.
 //   * the sweep of clean_one_from_hash is pre-resolved per batch: a parallel scan keeps a queue of
 //     the next eligible slots, so the n-th overflow of a batch zeroes the n-th queued slot.
 //   oracle/spec_model.c is the CPU model of exactly this scheme; tests/test_spec_model.py proves
@@ -31,7 +36,26 @@
 #define MAXWALK 4096       // longer probe walks are left to the serial path
 #define WLOG_CAP 64
 
-enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8 };
+enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8, F_FOLLOW = 16 };
+
+// Blocked Bloom filter over inserted tags: word index and 3-bit mask (oracle/spec_model.c filt_hash).
+#define FILT_BITS 24
+__device__ __forceinline__ void filt_hash(i64 tag, u64 &word, u64 &bits) {
+    u64 x = (u64)tag;
+    x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+    word = x >> (64 - FILT_BITS);
+    bits = ((u64)1 << (x & 63)) | ((u64)1 << ((x >> 6) & 63)) | ((u64)1 << ((x >> 12) & 63));
+}
+__device__ __forceinline__ bool filt_query(const u64 *F, i64 tag) {
+    u64 w, b;
+    filt_hash(tag, w, b);
+    return (__ldcg(F + w) & b) == b;
+}
+__device__ __forceinline__ void filt_set(u64 *F, i64 tag) {
+    u64 w, b;
+    filt_hash(tag, w, b);
+    atomicOr((unsigned long long *)(F + w), (unsigned long long)b);
+}
 
 // Running state of the automaton, shared by the whole CTA (rzip_state, mrzip_private.h:388-416).
 struct Run {
@@ -44,6 +68,7 @@ struct Warp {
     // constants
     const u8 *buf;
     Slot *tab;
+    u64 *filt;
     Token *toks;
     i64 n, end, hmask, hsize, limit, tok_cap;
     int chain, lane;
@@ -254,11 +279,13 @@ struct Warp {
     __device__ __forceinline__ bool op(i64 pp, i64 t, i64 *stk) {
         nops++;
         i64 bofs = 0, brev = 0;
-        i64 best = lookup(t, pp, bofs, brev);
+        i64 best = filt_query(filt, t) ? lookup(t, pp, bofs, brev) : 0;   // negative: nothing to find
         if ((t & ins_mask) == ins_mask) {
             inserts++;
             count++;
             insert(t, pp, stk);
+            if (lane == 0) filt_set(filt, t);
+            __syncwarp();
             if (count > limit) clean_one();
         }
         if (best > cur_len) { cur_p = pp - brev; cur_len = best; cur_ofs = bofs; }
@@ -316,7 +343,8 @@ struct Smem {
     i64 li;                 // next candidate-list index
     u32 b_rel[AT];          // batch: position of op j relative to seg_lo
     int b_li[AT];           // batch: candidate-list index of op j
-    int pre[AT];            // inclusive prefix over planned ops: (insert count << 16) | dcount sum
+    int pre[AT];            // inclusive prefix over planned ops: misses << 22 | inserts << 11 | dcount sum
+    int pl_fl[AT], pl_w2[AT];   // plan flags / insert slot of op j, for its twin
     int E[EQ_CAP];          // ring of eligible slots, ascending
     int wh_key[WH_CAP];     // write-slot hash: slot (or -1)
     int wh_val[WH_CAP];     //                  smallest op index writing it
@@ -404,74 +432,118 @@ struct Plan {
 __device__ __forceinline__ bool slot_empty(const Slot &e) { return (e.off | e.tag) == 0; }
 
 // Phase A: plan one op against the table without modifying anything (oracle/spec_model.c plan_op).
+// Only the insert walk is needed: the caller has established (tag filter) that no equal tag exists.
 __device__ __forceinline__ void plan_op(Plan &r, const Slot *tab, i64 tag, i64 hmask, i64 hsize, i64 min_mask,
-                                        i64 ins_mask, int chain, i64 w_lo, i64 w_hi) {
-    r.flags = 0; r.dcount = 0; r.rd2_lo = -1; r.rd2_hi = -1; r.w1_slot = -1; r.w2_slot = -1; r.w1_off = 0; r.w1_tag = 0;
+                                        int chain, i64 w_lo, i64 w_hi) {
     const i64 btm = (min_mask << 1) | 1;
-    const bool want = (tag & ins_mask) == ins_mask;
     const int myz = tz1(tag);
     const i64 h0 = tag & hmask;
     i64 h = h0;
-    int kind = 0;            // 0: none yet, 1: overwrite a due-for-sweep entry, 2: displace a lesser entry
-    i64 stop = -1, otag = 0, ooff = 0;
-    r.rd_lo = (int)h0; r.rd_hi = (int)h0;
+    int kind = -1;           // 0: empty slot, 1: overwrite a due-for-sweep entry, 2: displace a lesser entry
+    i64 otag = 0, ooff = 0;
+    r.flags |= F_INSERT;
+    r.rd_lo = (int)h0;
     for (;;) {
         Slot e[4];
 #pragma unroll
-        for (int q = 0; q < 4; q++) e[q] = ld_slot(&tab[h + q]);   // the table has 4 slots of slack
-        bool done = false;
+        for (int q = 0; q < 4; q++) e[q] = ld_slot(&tab[h + q]);   // the table has slack slots past hsize
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-            if (done) continue;
+            if (kind >= 0) continue;
             if (h + q >= hsize) { r.flags |= F_COMPLEX; return; }
-            if (slot_empty(e[q])) { r.rd_hi = (int)(h + q); done = true; continue; }
-            if (e[q].tag == tag) { r.flags |= F_COMPLEX; return; }
-            if (want && kind == 0) {
-                if ((e[q].tag & btm) != btm) { kind = 1; stop = h + q; }
-                else if (tz1(e[q].tag) < myz) { kind = 2; stop = h + q; otag = e[q].tag; ooff = e[q].off; }
-            }
+            if (slot_empty(e[q])) { kind = 0; h += q; }
+            else if (e[q].tag == tag) { r.flags |= F_COMPLEX; return; }          // cannot happen with a sound filter
+            else if ((e[q].tag & btm) != btm) { kind = 1; h += q; }
+            else if (tz1(e[q].tag) < myz) { kind = 2; h += q; otag = e[q].tag; ooff = e[q].off; }
         }
-        if (done) break;
+        if (kind >= 0) break;
         h += 4;
         if (h - h0 > MAXWALK) { r.flags |= F_COMPLEX; return; }
     }
-    if (want) {
-        r.flags |= F_INSERT;
-        if (kind == 0) { r.w2_slot = r.rd_hi; r.dcount = 1; }
-        else if (kind == 1) { r.w2_slot = (int)stop; r.dcount = 0; }
-        else {
-            // one level of displacement (rzip.c:275-277): where does the occupant go?
-            const int oz = tz1(otag);
-            const i64 g0 = otag & hmask;
-            i64 g = g0;
-            int round = 0, d2 = 0;
-            for (;;) {
-                Slot e[4];
+    r.w2_slot = (int)h; r.rd_hi = (int)h;
+    if (kind == 0) r.dcount = 1;
+    else if (kind == 1) r.dcount = 0;
+    else {
+        // one level of displacement (rzip.c:275-277): where does the occupant go?
+        const int oz = tz1(otag);
+        const i64 g0 = otag & hmask;
+        i64 g = g0;
+        int round = 0, d2 = 0;
+        bool done = false;
+        for (;;) {
+            Slot e[4];
 #pragma unroll
-                for (int q = 0; q < 4; q++) e[q] = ld_slot(&tab[g + q]);
-                bool done = false;
+            for (int q = 0; q < 4; q++) e[q] = ld_slot(&tab[g + q]);
 #pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    if (done) continue;
-                    if (g + q >= hsize) { r.flags |= F_COMPLEX; return; }
-                    if (slot_empty(e[q])) { g += q; done = true; continue; }
-                    if ((e[q].tag & btm) != btm) { d2 = -1; g += q; done = true; continue; }
-                    if (tz1(e[q].tag) < oz) { r.flags |= F_COMPLEX; return; }
-                    if (e[q].tag == otag && ++round == chain) { r.flags |= F_COMPLEX; return; }
-                }
-                if (done) break;
-                g += 4;
-                if (g - g0 > MAXWALK) { r.flags |= F_COMPLEX; return; }
+            for (int q = 0; q < 4; q++) {
+                if (done) continue;
+                if (g + q >= hsize) { r.flags |= F_COMPLEX; return; }
+                if (slot_empty(e[q])) { g += q; done = true; continue; }
+                if ((e[q].tag & btm) != btm) { d2 = -1; g += q; done = true; continue; }
+                if (tz1(e[q].tag) < oz) { r.flags |= F_COMPLEX; return; }
+                if (e[q].tag == otag && ++round == chain) { r.flags |= F_COMPLEX; return; }
             }
-            r.flags |= F_W1;
-            r.rd2_lo = (int)g0; r.rd2_hi = (int)g;
-            r.w1_slot = (int)g; r.w1_off = ooff; r.w1_tag = otag;
-            r.w2_slot = (int)stop; r.dcount = 1 + d2;
+            if (done) break;
+            g += 4;
+            if (g - g0 > MAXWALK) { r.flags |= F_COMPLEX; return; }
         }
+        r.flags |= F_W1;
+        r.rd2_lo = (int)g0; r.rd2_hi = (int)g;
+        r.w1_slot = (int)g; r.w1_off = ooff; r.w1_tag = otag;
+        r.dcount = 1 + d2;
     }
     // anything touching the sweep window is left to the serial path
     if (r.rd_hi >= w_lo && r.rd_lo < w_hi) r.flags |= F_COMPLEX;
     if (r.rd2_lo >= 0 && r.rd2_hi >= w_lo && r.rd2_lo < w_hi) r.flags |= F_COMPLEX;
+}
+
+// "Twin" (oracle/spec_model.c plan_follower): position p+1 has the same tag as p and both insert.  B's
+// lookup meets exactly the entry A has just inserted and match_len(p+1, p) fails (tag_misses++) unless
+// the bytes form a genuine run; B's insert walk passes A's entry and goes on from the next slot - or,
+// before the first overflow, overwrites A's entry when the tag itself is due for sweeping.
+__device__ __forceinline__ void plan_follower(Plan &r, const Slot *tab, const u8 *buf, i64 pos, i64 tag, int a_flags,
+                                              int a_w2, i64 hmask, i64 hsize, i64 min_mask, int chain, i64 end, i64 last,
+                                              i64 w_lo, i64 w_hi) {
+    if (a_flags & F_COMPLEX) { r.flags |= F_COMPLEX; return; }
+    if (!(a_flags & F_INSERT)) return;                       // both lookup-only, nothing to find
+    if ((a_flags & F_W1) || chain == 1) { r.flags |= F_COMPLEX; return; }
+    {   // match_len(pos, pos - 1) must be < 31 (rzip.c:372-397); each direction capped at 31
+        int f = 0, b = 0;
+        while (f < MRZ_MIN_MATCH && pos + f < end && buf[pos + f] == buf[pos - 1 + f]) f++;
+        const i64 lo = last > 0 ? last : 0;
+        while (b < MRZ_MIN_MATCH && pos - b > lo && pos - 1 - b > 0 && buf[pos - 2 - b] == buf[pos - 1 - b]) b++;
+        if (f + b >= MRZ_MIN_MATCH) { r.flags |= F_COMPLEX; return; }
+    }
+    const i64 btm = (min_mask << 1) | 1;
+    const int myz = tz1(tag);
+    r.flags |= F_INSERT | F_FOLLOW;
+    r.rd_lo = (int)(tag & hmask);
+    if ((tag & btm) != btm) {
+        r.w2_slot = a_w2; r.rd_hi = a_w2; r.dcount = 0;
+    } else {
+        i64 h = (i64)a_w2 + 1;
+        const i64 hs = h;
+        int kind = -1;
+        for (;;) {
+            Slot e[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) e[q] = ld_slot(&tab[h + q]);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                if (kind >= 0) continue;
+                if (h + q >= hsize) { r.flags |= F_COMPLEX; return; }
+                if (slot_empty(e[q])) { kind = 0; h += q; }
+                else if (e[q].tag == tag) { r.flags |= F_COMPLEX; return; }
+                else if ((e[q].tag & btm) != btm) { kind = 1; h += q; }
+                else if (tz1(e[q].tag) < myz) { r.flags |= F_COMPLEX; return; }
+            }
+            if (kind >= 0) break;
+            h += 4;
+            if (h - hs > MAXWALK) { r.flags |= F_COMPLEX; return; }
+        }
+        r.w2_slot = (int)h; r.rd_hi = (int)h; r.dcount = kind == 0 ? 1 : 0;
+    }
+    if (r.rd_hi >= w_lo && r.rd_lo < w_hi) r.flags |= F_COMPLEX;
 }
 
 // Refill the ring of eligible slots (those clean_one_from_hash will zero next, in order) by a
@@ -522,7 +594,7 @@ __device__ __forceinline__ void sync_queue(Smem *S, int nlog) {
 
 // Runs the automaton over the current segment's candidate list (or to the end of the chunk).
 __global__ void __launch_bounds__(AT, 1)
-k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx, AutoState *st,
+k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restrict__ hidx, AutoState *st,
             const i64 *__restrict__ tile_off, const u32 *__restrict__ cand_pos,
             const i64 *__restrict__ cand_tag, Token *toks, i64 *dbg) {
     if (st->done || st->error) return;
@@ -548,7 +620,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
         S->li = 0; S->bmax = AT;
     }
     Warp w;   // used by warp 0 only
-    w.buf = buf; w.tab = tab; w.toks = toks; w.lane = lane;
+    w.buf = buf; w.tab = tab; w.filt = filt; w.toks = toks; w.lane = lane;
     w.n = n; w.end = end; w.hmask = hmask; w.hsize = hsize; w.limit = limit; w.tok_cap = st->tok_cap; w.chain = chain;
     w.wlog = S->wlog; w.nlog = 0; w.clean_hint = 0;
     __syncthreads();
@@ -572,7 +644,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
         // ---------------------------------------------------------------- gather the next candidates
         int nr = 0;
         i64 li = S->li;
-        const i64 p_now = S->run.p;
+        const i64 p_now = S->run.p, last_now = S->run.last;
         for (;;) {
             int room = bmax - nr;
             if (room <= 0 || li >= ncand) break;
@@ -596,14 +668,29 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
         tm[8] += nr; tm[9] += 1;
         // ---------------------------------------------------------------- phase A: plan
         Plan pl;
-        pl.flags = F_COMPLEX; pl.dcount = 0;
+        pl.flags = 0; pl.dcount = 0; pl.rd_lo = 1; pl.rd_hi = 0; pl.rd2_lo = -1; pl.rd2_hi = -1;
+        pl.w1_slot = -1; pl.w2_slot = -1; pl.w1_off = 0; pl.w1_tag = 0;
         i64 my_pos = 0, my_tag = 0;
+        bool follower = false;
         for (int q = tid; q < WH_CAP; q += AT) { S->wh_key[q] = -1; S->wh_val[q] = 0x7fffffff; }
         if (tid < nr) {
-            my_pos = seg_lo + (i64)S->b_rel[tid]; my_tag = S->b_tag[tid];
-            plan_op(pl, tab, my_tag, hmask, hsize, min_mask, ins_mask, chain, w_lo, w_hi);
+            const u32 rel = S->b_rel[tid];
+            my_pos = seg_lo + (i64)rel; my_tag = S->b_tag[tid];
+            // twin: same tag as the position just before, which is not itself the second of a pair
+            bool same = tid > 0 && S->b_rel[tid - 1] + 1 == rel && S->b_tag[tid - 1] == my_tag;
+            bool same_prev = tid > 1 && S->b_rel[tid - 2] + 2 == rel && S->b_tag[tid - 2] == my_tag;
+            follower = same && !same_prev;
+            if (!follower) {
+                if (filt_query(filt, my_tag)) pl.flags |= F_COMPLEX;          // an equal tag may exist
+                else if ((my_tag & ins_mask) == ins_mask)
+                    plan_op(pl, tab, my_tag, hmask, hsize, min_mask, chain, w_lo, w_hi);
+            }
+            S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;
         }
         __syncthreads();
+        if (follower)
+            plan_follower(pl, tab, buf, my_pos, my_tag, S->pl_fl[tid - 1], S->pl_w2[tid - 1], hmask, hsize, min_mask, chain,
+                          end, last_now, w_lo, w_hi);
         TICK(2);   // plan
         const bool planned_ins = tid < nr && (pl.flags & (F_COMPLEX | F_INSERT)) == F_INSERT;
         if (planned_ins) {
@@ -611,13 +698,16 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
             if (pl.flags & F_W1) wh_insert(S, pl.w1_slot, tid);
         }
         __syncthreads();
-        if (tid < nr && !(pl.flags & F_COMPLEX)) {
-            if (wh_range_hit(S, pl.rd_lo, pl.rd_hi, tid) ||
+        if (planned_ins) {   // a follower's plan builds on its leader's write: only older writes conflict
+            const int before = (pl.flags & F_FOLLOW) ? tid - 1 : tid;
+            if (wh_range_hit(S, pl.rd_lo, pl.rd_hi, before) ||
                 (pl.rd2_lo >= 0 && wh_range_hit(S, pl.rd2_lo, pl.rd2_hi, tid)))
                 pl.flags |= F_CONF;
         }
-        {   // inclusive prefix of (insert count, dcount) over ops that still hold a valid plan
-            int v = (tid < nr && (pl.flags & (F_COMPLEX | F_CONF | F_INSERT)) == F_INSERT) ? ((1 << 16) | pl.dcount) : 0;
+        {   // inclusive prefix over ops that still hold a valid plan: misses << 22 | inserts << 11 | dcount sum
+            int v = 0;
+            if (tid < nr && (pl.flags & (F_COMPLEX | F_CONF | F_INSERT)) == F_INSERT)
+                v = pl.dcount | (1 << 11) | ((pl.flags & F_FOLLOW) ? (1 << 22) : 0);
             int total;
             int ex = block_excl_scan(v, S->wsum, total);
             S->pre[tid] = ex + v;
@@ -637,7 +727,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
                 bool c = (pl.flags & (F_COMPLEX | F_CONF)) != 0;
                 c = c || (cur_len >= MRZ_MIN_MATCH && my_pos >= cur_p + MRZ_MIN_MATCH);   // an emission is due
                 if (!c && (pl.flags & F_INSERT) && pl.dcount == 1) {
-                    i64 T = cnt0 + ((S->pre[tid] - base) & 0xffff);
+                    i64 T = cnt0 + (((unsigned)S->pre[tid] - (unsigned)base) & 0x7ffu);
                     if (T > limit && (!steady || T - limit > avail)) c = true;             // needs a serial sweep step
                 }
                 if (c) cut = tid;
@@ -647,18 +737,20 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
             if (tid >= pos && tid < k && (pl.flags & F_INSERT)) {
                 if (pl.flags & F_W1) st_slot(&tab[pl.w1_slot], pl.w1_off, pl.w1_tag);
                 st_slot(&tab[pl.w2_slot], my_pos, my_tag);
+                filt_set(filt, my_tag);
             }
             int cleans = 0;
             if (k > pos) {
-                const int d = S->pre[k - 1] - base;
-                i64 T = cnt0 + (d & 0xffff);
+                const unsigned d = (unsigned)S->pre[k - 1] - (unsigned)base;
+                i64 T = cnt0 + (d & 0x7ffu);
                 cleans = T > limit ? (int)(T - limit) : 0;
                 if (tid < cleans) st_slot(&tab[S->E[(S->e_idx + tid) & (EQ_CAP - 1)]], 0, 0);
                 __syncthreads();   // everyone has read run.count / e_idx
                 if (tid == 0) {
                     Run &r = S->run;
                     r.count = T - cleans;
-                    r.inserts += d >> 16;
+                    r.inserts += (d >> 11) & 0x7ffu;
+                    r.misses += d >> 22;
                     r.nops += k - pos;
                     r.p = seg_lo + (i64)S->b_rel[k - 1];
                     if (cleans) {
@@ -738,7 +830,8 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
             __syncthreads();
             TICK(5);   // serial op
             if (S->ended) break;
-            // later plans that read a slot this op wrote are no longer valid
+            // later plans that read a slot this op wrote are no longer valid; nor is its twin's plan
+            if (tid == k + 1 && (pl.flags & F_FOLLOW)) pl.flags |= F_CONF;
             if (tid > k && tid < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
                 const int nl = S->nlog;
                 for (int q = 0; q < nl; q++) {
@@ -779,12 +872,12 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, const i64 *__restrict__ hidx,
     }
 }
 
-extern "C" void mrz_launch_automaton(const u8 *buf, Slot *tab, const i64 *hidx, AutoState *st, const i64 *tile_off,
+extern "C" void mrz_launch_automaton(const u8 *buf, Slot *tab, u64 *filt, const i64 *hidx, AutoState *st, const i64 *tile_off,
                                      const u32 *cand_pos, const i64 *cand_tag, Token *toks, i64 *dbg, cudaStream_t s) {
 #ifndef MRZ_CUSIM
     cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
+    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, tab, filt, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
 #else
-    MRZ_LAUNCH(k_automaton, 1, AT, s, buf, tab, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
+    MRZ_LAUNCH(k_automaton, 1, AT, s, buf, tab, filt, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
 #endif
 }

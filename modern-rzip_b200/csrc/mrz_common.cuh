@@ -16,6 +16,7 @@ typedef unsigned int u32;
 #define MRZ_MIN_MATCH 31      // rzip.c:49 MINIMUM_MATCH
 #define MRZ_GREAT_MATCH 1024  // rzip.c:48 GREAT_MATCH
 #define MRZ_PAD 256           // zero padding before and after the chunk in HBM
+#define MRZ_FILT_WORDS (1 << 24)   // tag filter: 2^24 64-bit words = 128 MiB (automaton.cu FILT_BITS)
 
 #define SCAN_THREADS 256
 #define SCAN_RUN 32                            // positions per thread
