@@ -688,9 +688,11 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restr
             S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;
         }
         __syncthreads();
-        if (follower)
+        if (follower) {
             plan_follower(pl, tab, buf, my_pos, my_tag, S->pl_fl[tid - 1], S->pl_w2[tid - 1], hmask, hsize, min_mask, chain,
                           end, last_now, w_lo, w_hi);
+            S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;    // its leader looks at this when committing
+        }
         TICK(2);   // plan
         const bool planned_ins = tid < nr && (pl.flags & (F_COMPLEX | F_INSERT)) == F_INSERT;
         if (planned_ins) {
@@ -736,7 +738,9 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restr
             // commit [pos, k)
             if (tid >= pos && tid < k && (pl.flags & F_INSERT)) {
                 if (pl.flags & F_W1) st_slot(&tab[pl.w1_slot], pl.w1_off, pl.w1_tag);
-                st_slot(&tab[pl.w2_slot], my_pos, my_tag);
+                // a twin that overwrites its leader's entry in the same commit must win the slot
+                const bool overwritten = tid + 1 < k && (S->pl_fl[tid + 1] & F_FOLLOW) && S->pl_w2[tid + 1] == pl.w2_slot;
+                if (!overwritten) st_slot(&tab[pl.w2_slot], my_pos, my_tag);
                 filt_set(filt, my_tag);
             }
             int cleans = 0;
