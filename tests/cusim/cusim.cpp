@@ -71,6 +71,9 @@ void launch(dim3 grid, dim3 block, const std::function<void()> &body) {
         fiber_pool = new Fiber[kMaxThreads];
         warp_pool = new WarpSlot[kMaxThreads / 32];
     }
+    static const char *seed_env = getenv("CUSIM_SEED");
+    static thread_local unsigned long long rng = seed_env ? strtoull(seed_env, nullptr, 10) * 2654435761ULL + 1 : 0;
+    const bool shuffle = seed_env != nullptr;
     Block saved = blk;
     Fiber *saved_cur = cur;
     blk.fib = fiber_pool;
@@ -97,7 +100,17 @@ void launch(dim3 grid, dim3 block, const std::function<void()> &body) {
                 }
                 while (blk.nlive > 0) {
                     bool progress = false;
-                    for (int i = 0; i < nthreads; i++) {
+                    // CUSIM_SEED set: visit the fibers in a different pseudo-random order on every pass, so that
+                    // code relying on threads running in index order (a data race on the GPU) fails here too
+                    unsigned start = 0, stride = 1;
+                    if (shuffle && (nthreads & (nthreads - 1)) == 0) {
+                        rng = rng * 6364136223846793005ULL + 1442695040888963407ULL;
+                        start = (unsigned)(rng >> 33) & (nthreads - 1);
+                        stride = ((unsigned)(rng >> 20) & (nthreads - 1)) | 1u;
+                    }
+                    for (int ii = 0; ii < nthreads; ii++) {
+                        int i = (int)((start + (unsigned)ii * stride) & (unsigned)(nthreads - 1));
+                        if (stride == 1 && start == 0) i = ii;
                         Fiber *f = &fiber_pool[i];
                         if (f->status == 3) continue;
                         if (f->status == 1 && f->bar_gen == blk.bar_gen) continue;
