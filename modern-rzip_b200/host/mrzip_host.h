@@ -59,6 +59,8 @@ typedef struct rzip_control {
     int device;                  /* CUDA device for the hot path */
     int n_devices;               /* >1: shard chunks over GPUs */
     struct mrz_ctx *gpu;
+    i64 gpu_cap, s0_cap, s1_cap;  /* device context capacity; pinned staging for the two streams */
+    uchar *pin_s0, *pin_s1;
     /* statistics as printed by rzip.c:1108-1115 */
     i64 matches, match_bytes, literals, literal_bytes, tag_hits, tag_misses, inserts;
     double gpu_ms, gpu_scan_ms, gpu_auto_ms, gpu_emit_ms;
@@ -110,6 +112,8 @@ bool compress_file(rzip_control *control);
 
 /* the hot path's outer entry (include/rzip.h:25) */
 void rzip_fd(rzip_control *control, int fd_in, int fd_out);
+void rzip_release_gpu(rzip_control *control);
+bool initialise_control(rzip_control *control); /* mrzip.c:1362 */
 
 /* MD5 (RFC 1321) — the reference gets it from libgcrypt (rzip.c:495, :829) */
 typedef struct {

@@ -318,3 +318,35 @@ def gen_motif(n, copies, motif_len=48, seed=7):
     for p in rng.integers(0, n - motif_len, copies):
         buf[p:p + motif_len] = motif
     return buf
+
+
+# ---------------------------------------------------------------- golden cases (tests/golden/make_golden.py)
+def survey_650():
+    """SURVEY.md §8(a) verified example: A(300) B(100) A[:200] C(50), Python random.seed(1)."""
+    import random
+    random.seed(1)
+    A = bytes(random.getrandbits(8) for _ in range(300))
+    B = bytes(random.getrandbits(8) for _ in range(100))
+    Cc = bytes(random.getrandbits(8) for _ in range(50))
+    return A + B + A[:200] + Cc
+
+
+def golden_cases():
+    """name -> (input bytes, extra mrzip flags).  All single-process, `-n -q -f`, MRZIP=NOCONFIG."""
+    pat = b"abcdefghijklmnopqrstuvwxyz012345"
+    cases = {"survey650": (survey_650(), ())}
+    for n in (0, 1, 30, 31, 32, 63, 64, 100):
+        cases["pattern%d" % n] = ((pat * 4)[:n], ())
+    cases["random100003"] = (gen_random(100003, seed=5), ())
+    cases["repeats1m"] = (gen_random_repeats(1 << 20, 12, lo=1024, hi=32768), ())
+    cases["motif_R1"] = (gen_motif(3 << 20, 3000), ("-R", "1"))
+    cases["vm_like_L9"] = (gen_vm_like(2 << 20, seed=19), ("-L", "9"))
+    cases["dense_R3"] = (gen_dense(2 << 20, seed=6), ("-R", "3"))
+    cases["tar_like"] = (gen_tar_like(4 << 20, seed=8), ())
+    return cases
+
+
+def load_golden():
+    import json
+    with open(os.path.join(GOLDEN, "reference_vectors.json")) as f:
+        return json.load(f)
