@@ -8,23 +8,29 @@
 // B200 design (not the reference's loop):
 //   * the per-byte loop is gone: candidates (positions whose tag passes the lookup gate) come from
 //     tag_scan.cu as a position-ordered list;
+//   * the table is stored as two arrays (tags[], offs[]) instead of the reference's 16-byte
+//     entries: walks only ever look at tags, so a probe step moves half the bytes;
 //   * BATCHED SPECULATION: the next <=1024 candidate ops are *planned* in parallel, one thread
-//     each, against the live table read-only (probe walk, insert target, one level of
-//     displacement).  Plans are then committed in order: a plan is valid as long as no earlier op
-//     of the batch wrote a slot inside its read ranges (checked exactly through a shared-memory
-//     hash of the batch's write slots), it met no equal tag (=> match_len needed), and it stays
-//     clear of the sweep window of clean_one_from_hash.  Everything else - typically <1 % of the
-//     ops - is executed by warp 0 on the live table with the reference semantics (32-slot probe,
-//     ballots for walk termination / equal-tag chains / the victim index, 256-byte-per-step
-//     match extension), after which later plans that read a slot it wrote are invalidated.
+//     each, against the live table read-only (insert walk, one level of displacement).  Plans are
+//     then committed in order: a plan is valid as long as no earlier op of the batch wrote a slot
+//     inside its read range (checked through a shared-memory hash of the batch's write slots)
+//     and it stays clear of the sweep window of clean_one_from_hash.  Everything else - a fraction
+//     of a percent of the ops - is executed by warp 0 on the live table with the reference
+//     semantics (32-slot probes, ballots for walk termination / equal-tag chains / the victim
+//     index, 256-byte-per-step match extension), after which later plans that read a slot it wrote
+//     are invalidated;
 //   * TAG FILTER: a blocked Bloom filter over every tag inserted in this chunk (one 64-bit word,
 //     three bits per tag, no false negatives).  A negative answer proves that no entry with an
 //     equal tag exists, so find_best_match's walk to the end of the probe cluster - hundreds of
-//     slots at high mask levels - is skipped altogether, and lookup-only ops touch no table slot.
-//   * TWINS: positions p and p+1 with equal tags (buf[p] == buf[p+31]) are planned as a pair.
+//     slots at high mask levels - is skipped altogether, and lookup-only ops touch no table slot;
+//   * GROUP SUMMARY: the insert walk looks for the first slot whose tag has fewer trailing one bits
+//     than `need` (empty, due for sweeping, or lesser than the new tag: rzip.c:264-277).  Shared
+//     memory holds, per group of 16 slots, a 4-bit lower bound of the minimum trailing-one count
+//     in the group, so a walk skips whole groups without touching them and reads one group;
+//   * TWINS: positions p and p+1 with equal tags (buf[p] == buf[p+31]) are planned as a pair;
 //   * the sweep of clean_one_from_hash is pre-resolved per batch: a parallel scan keeps a queue of
 //     the next eligible slots, so the n-th overflow of a batch zeroes the n-th queued slot.
-//   oracle/spec_model.c is the CPU model of exactly this scheme; tests/test_spec_model.py proves
+//   oracle/spec_model.c is the CPU model of the speculation rules; tests/test_spec_model.py proves
 //   it equivalent to the sequential restatement, tests/test_sim_parity.py runs this very file on
 //   the CPU emulator, tests/test_gpu_parity.py on the B200.
 #include "mrz_common.cuh"
@@ -32,9 +38,15 @@
 #define FULL 0xffffffffu
 #define AT 1024            // threads per CTA = ops per batch
 #define EQ_CAP 4096        // eligible-slot ring (power of two)
-#define WH_CAP 4096        // write-slot hash (power of two, >= 2 * AT)
-#define MAXWALK 4096       // longer probe walks are left to the serial path
+#define WH_CAP 4096        // write-slot hash (power of two)
+#define WH_PROBES 128      // longer probe sequences mean the hash is overfull: the batch goes serial
+#define MAXWALK 16384      // longer insert walks are left to the serial path
 #define WLOG_CAP 64
+#define GRP 16             // slots per summary group
+#define GRP_SHIFT 4
+#define EXACT_RANGE 48     // read ranges up to this many slots are checked slot by slot
+#define CGRP_SHIFT 6       // longer ones: 64-slot conflict groups for the middle part
+#define DUP_SALT 0x5bd1e9955bd1e995LL
 
 enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8, F_FOLLOW = 16 };
 
@@ -57,6 +69,31 @@ __device__ __forceinline__ void filt_set(u64 *F, i64 tag) {
     atomicOr((unsigned long long *)(F + w), (unsigned long long)b);
 }
 
+__device__ __forceinline__ int tz1c(i64 t) {   // trailing one bits, capped at 15 (summary nibble)
+    int z = tz1(t);
+    return z > 15 ? 15 : (z < 0 ? 15 : z);
+}
+__device__ __forceinline__ int nib_get(const u32 *gs, i64 g) { return (int)((gs[g >> 3] >> ((g & 7) * 4)) & 15u); }
+// plan phase only (no concurrent lowering): a lost update merely leaves a smaller, still valid, lower bound
+__device__ __forceinline__ void nib_raise(u32 *gs, i64 g, int v) {
+    u32 w = gs[g >> 3];
+    int sh = (int)(g & 7) * 4;
+    gs[g >> 3] = (w & ~(15u << sh)) | ((u32)v << sh);
+}
+// commit / serial phases: the group now holds a tag with v trailing ones (0 for a zeroed slot)
+__device__ __forceinline__ void nib_lower(u32 *gs, i64 g, int v) {
+    u32 *p = &gs[g >> 3];
+    int sh = (int)(g & 7) * 4;
+    u32 old = *p;
+    for (;;) {
+        if ((int)((old >> sh) & 15u) <= v) return;
+        u32 nw = (old & ~(15u << sh)) | ((u32)v << sh);
+        u32 seen = atomicCAS(p, old, nw);
+        if (seen == old) return;
+        old = seen;
+    }
+}
+
 // Running state of the automaton, shared by the whole CTA (rzip_state, mrzip_private.h:388-416).
 struct Run {
     i64 p, last, cur_p, cur_len, cur_ofs, min_mask, ins_mask, clean_ptr, count, vr;
@@ -67,8 +104,9 @@ struct Run {
 struct Warp {
     // constants
     const u8 *buf;
-    Slot *tab;
+    i64 *ttag, *toff;   // the table: tags and offsets (struct hash_entry, rzip.c:59-62, split in two arrays)
     u64 *filt;
+    u32 *gsum;          // group summary (shared memory)
     Token *toks;
     i64 n, end, hmask, hsize, limit, tok_cap;
     int chain, lane;
@@ -95,9 +133,16 @@ struct Warp {
             r.error = error;
         }
     }
-    __device__ __forceinline__ void log_write(i64 slot, int zeroed) {
-        if (nlog < WLOG_CAP && lane == 0) wlog[nlog] = (int)(slot << 1) | zeroed;
+    // table writes of the serial path: lane 0 stores, the write is logged, the summary follows
+    __device__ __forceinline__ void write_slot(i64 slot, i64 off, i64 tag) {
+        if (lane == 0) {
+            __stcg(toff + slot, off);
+            __stcg(ttag + slot, tag);
+            nib_lower(gsum, slot >> GRP_SHIFT, tag ? tz1c(tag) : 0);
+            if (nlog < WLOG_CAP) wlog[nlog] = (int)(slot << 1) | (tag ? 0 : 1);
+        }
         nlog++;
+        __syncwarp();
     }
 
     // rzip.c:372-397.  Returns total length (0 if < 31) and the backward part in rev.
@@ -149,16 +194,15 @@ struct Warp {
         i64 best = 0;
         i64 h = t & hmask;
         for (;;) {
-            Slot e = ld_slot(&tab[(h + lane) & hmask]);
-            bool empty = (e.off | e.tag) == 0;
-            unsigned em = __ballot_sync(FULL, empty);
+            i64 et = __ldcg(ttag + ((h + lane) & hmask));
+            unsigned em = __ballot_sync(FULL, et == 0);
             int fe = em ? (__ffs(em) - 1) : 32;
-            unsigned eq = __ballot_sync(FULL, !empty && e.tag == t);
+            unsigned eq = __ballot_sync(FULL, et == t);
             if (fe < 32) eq &= (1u << fe) - 1u;
             while (eq) {
                 int l = __ffs(eq) - 1;
                 eq &= eq - 1;
-                i64 off = __shfl_sync(FULL, e.off, l);
+                i64 off = __ldcg(toff + ((h + l) & hmask));
                 i64 rev;
                 i64 m = match_len(pp, off, rev);
                 if (m) {
@@ -182,13 +226,13 @@ struct Warp {
             i64 btm = (min_mask << 1) | 1;
             int ctz = tz1(ct);
             bool displaced = false;
-            i64 otag = 0, ooff = 0;
+            i64 otag = 0;
             for (;;) {
-                Slot e = ld_slot(&tab[(h + lane) & hmask]);
-                bool empty = (e.off | e.tag) == 0;
-                bool minbit = !empty && (e.tag & btm) != btm;
-                bool lesser = !empty && !minbit && tz1(e.tag) < ctz;
-                bool equal = !empty && !minbit && !lesser && e.tag == ct;
+                i64 et = __ldcg(ttag + ((h + lane) & hmask));
+                bool empty = et == 0;
+                bool minbit = !empty && (et & btm) != btm;
+                bool lesser = !empty && !minbit && tz1(et) < ctz;
+                bool equal = !empty && !minbit && !lesser && et == ct;
                 unsigned emm = __ballot_sync(FULL, empty);
                 unsigned mbm = __ballot_sync(FULL, minbit);
                 unsigned lsm = __ballot_sync(FULL, lesser);
@@ -216,8 +260,7 @@ struct Warp {
                     if ((mbm >> s) & 1u) count--;      // rzip.c:267-269: due for cleaning, overwrite
                     else if ((lsm >> s) & 1u) {        // rzip.c:275-277: re-insert the occupant first
                         displaced = true;
-                        otag = __shfl_sync(FULL, e.tag, s);
-                        ooff = __shfl_sync(FULL, e.off, s);
+                        otag = __shfl_sync(FULL, et, s);
                     }
                     break;
                 }
@@ -227,19 +270,16 @@ struct Warp {
                 if (sp >= 60) { error = 3; return; }
                 stk[3 * sp] = target; stk[3 * sp + 1] = ct; stk[3 * sp + 2] = coff;
                 sp++;
-                ct = otag; coff = ooff;
+                coff = __ldcg(toff + target);
+                ct = otag;
                 continue;
             }
-            if (lane == 0) st_slot(&tab[target], coff, ct);
-            log_write(target, 0);
-            __syncwarp();
+            write_slot(target, coff, ct);
             break;
         }
         while (sp > 0) {
             sp--;
-            if (lane == 0) st_slot(&tab[stk[3 * sp]], stk[3 * sp + 2], stk[3 * sp + 1]);
-            log_write(stk[3 * sp], 0);
-            __syncwarp();
+            write_slot(stk[3 * sp], stk[3 * sp + 2], stk[3 * sp + 1]);
         }
     }
 
@@ -253,16 +293,13 @@ struct Warp {
                 i64 idx = clean_ptr + lane;
                 bool elig = false;
                 if (idx < hsize) {
-                    Slot e = ld_slot(&tab[idx]);
-                    elig = (e.off | e.tag) != 0 && (e.tag & btm) != btm;
+                    i64 et = __ldcg(ttag + idx);
+                    elig = et != 0 && (et & btm) != btm;
                 }
                 unsigned m = __ballot_sync(FULL, elig);
                 if (m) {
-                    int l = __ffs(m) - 1;
-                    clean_ptr += l;
-                    if (lane == l) st_slot(&tab[idx], 0, 0);
-                    log_write(clean_ptr, 1);
-                    __syncwarp();
+                    clean_ptr += __ffs(m) - 1;
+                    write_slot(clean_ptr, 0, 0);
                     count--;
                     ins_mask = btm;
                     return;
@@ -279,12 +316,16 @@ struct Warp {
     __device__ __forceinline__ bool op(i64 pp, i64 t, i64 *stk) {
         nops++;
         i64 bofs = 0, brev = 0;
-        i64 best = filt_query(filt, t) ? lookup(t, pp, bofs, brev) : 0;   // negative: nothing to find
+        const bool maybe = filt_query(filt, t);                       // negative: nothing to find
+        i64 best = maybe ? lookup(t, pp, bofs, brev) : 0;
         if ((t & ins_mask) == ins_mask) {
             inserts++;
             count++;
             insert(t, pp, stk);
-            if (lane == 0) filt_set(filt, t);
+            if (lane == 0) {
+                filt_set(filt, t);
+                if (maybe) filt_set(filt, t ^ DUP_SALT);              // this tag may now be in the table twice
+            }
             __syncwarp();
             if (count > limit) clean_one();
         }
@@ -341,17 +382,18 @@ struct Smem {
     Run run;
     i64 e_scan;             // slots in [run.clean_ptr, e_scan) have been examined for the queue
     i64 li;                 // next candidate-list index
+    u32 gsum[(1 << 22) / GRP / 8];   // group summary: one nibble per 16 slots (128 KiB for the 64 MiB table)
     u32 b_rel[AT];          // batch: position of op j relative to seg_lo
     int b_li[AT];           // batch: candidate-list index of op j
     int pre[AT];            // inclusive prefix over planned ops: misses << 22 | inserts << 11 | dcount sum
     int pl_fl[AT], pl_w2[AT];   // plan flags / insert slot of op j, for its twin
     int E[EQ_CAP];          // ring of eligible slots, ascending
-    int wh_key[WH_CAP];     // write-slot hash: slot (or -1)
-    int wh_val[WH_CAP];     //                  smallest op index writing it
+    int wh_key[WH_CAP];     // write hash: slot, or (1 << 30) | (slot >> 6) for the 64-slot group; -1 empty
+    int wh_val[WH_CAP];     //             smallest op index writing it
     int wlog[WLOG_CAP];
     int wsum[40];
     unsigned e_idx, e_cnt;  // ring counters (monotonic)
-    int nr, pos, k, nlog, jumped, ended, bmax, red;
+    int nr, pos, k, nlog, jumped, ended, bmax, red, wh_over;
 };
 
 #ifdef MRZ_CUSIM
@@ -398,27 +440,48 @@ __device__ __forceinline__ int block_min(int v, int *red) {
     return *red;
 }
 
-__device__ __forceinline__ unsigned wh_hash(int slot) { return ((unsigned)slot * 2654435761u) >> 20; }  // 12 bits
+// ---- write hash: which earlier op of the batch writes a given slot / 64-slot group ------------------
+__device__ __forceinline__ unsigned wh_hash(int key) { return ((unsigned)key * 2654435761u) >> 20; }  // 12 bits
 
-__device__ __forceinline__ void wh_insert(Smem *S, int slot, int j) {
-    unsigned h = wh_hash(slot) & (WH_CAP - 1);
-    for (;;) {
-        int k = atomicCAS(&S->wh_key[h], -1, slot);
-        if (k == -1 || k == slot) { atomicMin(&S->wh_val[h], j); return; }
+__device__ __forceinline__ void wh_insert(Smem *S, int key, int j) {
+    unsigned h = wh_hash(key) & (WH_CAP - 1);
+    for (int n = 0; n < WH_PROBES; n++) {
+        int k = atomicCAS(&S->wh_key[h], -1, key);
+        if (k == -1 || k == key) { atomicMin(&S->wh_val[h], j); return; }
         h = (h + 1) & (WH_CAP - 1);
     }
+    S->wh_over = 1;
 }
-// true when some op with index < j writes a slot in [lo, hi]
-__device__ __forceinline__ bool wh_range_hit(const Smem *S, int lo, int hi, int j) {
-    for (int s = lo; s <= hi; s++) {
-        unsigned h = wh_hash(s) & (WH_CAP - 1);
-        for (;;) {
-            int k = S->wh_key[h];
-            if (k == -1) break;
-            if (k == s) { if (S->wh_val[h] < j) return true; break; }
-            h = (h + 1) & (WH_CAP - 1);
-        }
+__device__ __forceinline__ void wh_insert_slot(Smem *S, int slot, int j) {
+    wh_insert(S, slot, j);
+    wh_insert(S, (1 << 30) | (slot >> CGRP_SHIFT), j);
+}
+__device__ __forceinline__ bool wh_hit(const Smem *S, int key, int before) {
+    unsigned h = wh_hash(key) & (WH_CAP - 1);
+    for (int n = 0; n < WH_PROBES; n++) {
+        int k = S->wh_key[h];
+        if (k == -1) return false;
+        if (k == key) return S->wh_val[h] < before;
+        h = (h + 1) & (WH_CAP - 1);
     }
+    return true;
+}
+// true when some op with index < before writes a slot in [lo, hi] (conservative for long ranges: whole
+// 64-slot groups in the middle of the range are tested as groups)
+__device__ __forceinline__ bool wh_range_hit(const Smem *S, int lo, int hi, int before) {
+    if (hi - lo < EXACT_RANGE) {
+        for (int s = lo; s <= hi; s++)
+            if (wh_hit(S, s, before)) return true;
+        return false;
+    }
+    const int g_lo = (lo >> CGRP_SHIFT) + 1, g_hi = hi >> CGRP_SHIFT;   // full groups: [g_lo, g_hi)
+    for (int s = lo; s < (g_lo << CGRP_SHIFT) && s <= hi; s++)
+        if (wh_hit(S, s, before)) return true;
+    for (int g = g_lo; g < g_hi; g++)
+        if (wh_hit(S, (1 << 30) | g, before)) return true;
+    if (g_hi >= g_lo)
+        for (int s = g_hi << CGRP_SHIFT; s <= hi; s++)
+            if (wh_hit(S, s, before)) return true;
     return false;
 }
 
@@ -429,67 +492,87 @@ struct Plan {
     i64 w1_off, w1_tag;
 };
 
-__device__ __forceinline__ bool slot_empty(const Slot &e) { return (e.off | e.tag) == 0; }
-
-// Phase A: plan one op against the table without modifying anything (oracle/spec_model.c plan_op).
-// Only the insert walk is needed: the caller has established (tag filter) that no equal tag exists.
-__device__ __forceinline__ void plan_op(Plan &r, const Slot *tab, i64 tag, i64 hmask, i64 hsize, i64 min_mask,
-                                        int chain, i64 w_lo, i64 w_hi) {
-    const i64 btm = (min_mask << 1) | 1;
-    const int myz = tz1(tag);
-    const i64 h0 = tag & hmask;
-    i64 h = h0;
-    int kind = -1;           // 0: empty slot, 1: overwrite a due-for-sweep entry, 2: displace a lesser entry
-    i64 otag = 0, ooff = 0;
-    r.flags |= F_INSERT;
-    r.rd_lo = (int)h0;
-    for (;;) {
-        Slot e[4];
-#pragma unroll
-        for (int q = 0; q < 4; q++) e[q] = ld_slot(&tab[h + q]);   // the table has slack slots past hsize
-#pragma unroll
-        for (int q = 0; q < 4; q++) {
-            if (kind >= 0) continue;
-            if (h + q >= hsize) { r.flags |= F_COMPLEX; return; }
-            if (slot_empty(e[q])) { kind = 0; h += q; }
-            else if (e[q].tag == tag) { r.flags |= F_COMPLEX; return; }          // cannot happen with a sound filter
-            else if ((e[q].tag & btm) != btm) { kind = 1; h += q; }
-            else if (tz1(e[q].tag) < myz) { kind = 2; h += q; otag = e[q].tag; ooff = e[q].off; }
-        }
-        if (kind >= 0) break;
-        h += 4;
-        if (h - h0 > MAXWALK) { r.flags |= F_COMPLEX; return; }
+// First slot s >= h with tz1(tags[s]) < need (an empty slot has tag 0, i.e. zero trailing ones), or -1 when
+// the walk reaches the end of the table / gets too long.  Whole groups whose summary nibble is >= need are
+// skipped unseen; a group that is scanned completely without a hit has its nibble repaired.
+__device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int need, i64 hsize, i64 &stop_tag) {
+    if (h >= hsize) return -1;
+    const i64 h0 = h;
+    i64 g = h >> GRP_SHIFT;
+    i64 ngroups = hsize >> GRP_SHIFT;
+    {   // never look further than MAXWALK slots
+        i64 lim = ((h0 + MAXWALK) >> GRP_SHIFT) + 1;
+        if (lim < ngroups) ngroups = lim;
     }
-    r.w2_slot = (int)h; r.rd_hi = (int)h;
-    if (kind == 0) r.dcount = 1;
-    else if (kind == 1) r.dcount = 0;
-    else {
-        // one level of displacement (rzip.c:275-277): where does the occupant go?
-        const int oz = tz1(otag);
-        const i64 g0 = otag & hmask;
-        i64 g = g0;
-        int round = 0, d2 = 0;
-        bool done = false;
-        for (;;) {
-            Slot e[4];
+    bool whole = (h & (GRP - 1)) == 0;
+    for (;;) {
+        // scan the rest of group g from h, four tags per step
+        const i64 gend = (g + 1) << GRP_SHIFT;
+        int mn = 15;
+        while (h < gend) {
+            i64 t[4];
 #pragma unroll
-            for (int q = 0; q < 4; q++) e[q] = ld_slot(&tab[g + q]);
+            for (int q = 0; q < 4; q++) t[q] = __ldcg(ttag + h + q);   // the table has slack past hsize
 #pragma unroll
             for (int q = 0; q < 4; q++) {
-                if (done) continue;
-                if (g + q >= hsize) { r.flags |= F_COMPLEX; return; }
-                if (slot_empty(e[q])) { g += q; done = true; continue; }
-                if ((e[q].tag & btm) != btm) { d2 = -1; g += q; done = true; continue; }
-                if (tz1(e[q].tag) < oz) { r.flags |= F_COMPLEX; return; }
-                if (e[q].tag == otag && ++round == chain) { r.flags |= F_COMPLEX; return; }
+                if (h + q < gend) {
+                    int z = tz1(t[q]);
+                    if (z < 0) z = 64;
+                    if (z < need) { stop_tag = t[q]; return h + q; }
+                    int zc = z > 15 ? 15 : z;
+                    mn = zc < mn ? zc : mn;
+                }
             }
-            if (done) break;
-            g += 4;
-            if (g - g0 > MAXWALK) { r.flags |= F_COMPLEX; return; }
+            h += 4;
+        }
+        if (whole) nib_raise(gsum, g, mn);
+        // skip groups that cannot contain a stop
+        g++;
+        while (g < ngroups && nib_get(gsum, g) >= need) g++;
+        if (g >= ngroups) return -1;
+        h = g << GRP_SHIFT;
+        whole = true;
+    }
+}
+
+__device__ __forceinline__ void plan_init(Plan &r) {
+    r.flags = 0; r.dcount = 0; r.rd_lo = 1; r.rd_hi = 0; r.rd2_lo = -1; r.rd2_hi = -1;
+    r.w1_slot = -1; r.w2_slot = -1; r.w1_off = 0; r.w1_tag = 0;
+}
+
+// Phase A: plan the insert of (tag) against the table without modifying anything (oracle/spec_model.c
+// plan_op).  The caller has established through the tag filter that no equal tag exists.
+__device__ __forceinline__ void plan_op(Plan &r, const i64 *ttag, const i64 *toff, u32 *gsum, const u64 *filt, i64 tag,
+                                        i64 hmask, i64 hsize, i64 min_mask, int chain, i64 w_lo, i64 w_hi) {
+    const i64 btm = (min_mask << 1) | 1;
+    const int kb = __popcll((u64)btm);                 // entries with fewer trailing ones are due for sweeping
+    const int myz = tz1(tag);
+    const i64 h0 = tag & hmask;
+    r.flags |= F_INSERT;
+    r.rd_lo = (int)h0;
+    i64 st;
+    i64 s = find_stop(ttag, gsum, h0, myz > kb ? myz : kb, hsize, st);
+    if (s < 0) { r.flags |= F_COMPLEX; return; }
+    r.w2_slot = (int)s; r.rd_hi = (int)s;
+    if (st == 0) r.dcount = 1;                         // empty slot
+    else if ((st & btm) != btm) r.dcount = 0;          // rzip.c:267-269: overwrite an entry due for sweeping
+    else {
+        // rzip.c:275-277: the occupant is lesser; where does it go when re-inserted?  Only planned when the
+        // occupant's tag is unique in the table (no equal-tag chain to count) and nothing has to move further.
+        if (chain == 1 || filt_query(filt, st ^ DUP_SALT)) { r.flags |= F_COMPLEX; return; }
+        const int oz = tz1(st);
+        const i64 g0 = st & hmask;
+        i64 st2;
+        i64 g = find_stop(ttag, gsum, g0, oz > kb ? oz : kb, hsize, st2);
+        if (g < 0) { r.flags |= F_COMPLEX; return; }
+        int d2 = 0;
+        if (st2 != 0) {
+            if ((st2 & btm) != btm) d2 = -1;
+            else { r.flags |= F_COMPLEX; return; }     // a second displacement: serial
         }
         r.flags |= F_W1;
         r.rd2_lo = (int)g0; r.rd2_hi = (int)g;
-        r.w1_slot = (int)g; r.w1_off = ooff; r.w1_tag = otag;
+        r.w1_slot = (int)g; r.w1_off = __ldcg(toff + s); r.w1_tag = st;
         r.dcount = 1 + d2;
     }
     // anything touching the sweep window is left to the serial path
@@ -501,9 +584,9 @@ __device__ __forceinline__ void plan_op(Plan &r, const Slot *tab, i64 tag, i64 h
 // lookup meets exactly the entry A has just inserted and match_len(p+1, p) fails (tag_misses++) unless
 // the bytes form a genuine run; B's insert walk passes A's entry and goes on from the next slot - or,
 // before the first overflow, overwrites A's entry when the tag itself is due for sweeping.
-__device__ __forceinline__ void plan_follower(Plan &r, const Slot *tab, const u8 *buf, i64 pos, i64 tag, int a_flags,
-                                              int a_w2, i64 hmask, i64 hsize, i64 min_mask, int chain, i64 end, i64 last,
-                                              i64 w_lo, i64 w_hi) {
+__device__ __forceinline__ void plan_follower(Plan &r, const i64 *ttag, u32 *gsum, const u8 *buf, i64 pos, i64 tag,
+                                              int a_flags, int a_w2, i64 hmask, i64 hsize, i64 min_mask, int chain, i64 end,
+                                              i64 last, i64 w_lo, i64 w_hi) {
     if (a_flags & F_COMPLEX) { r.flags |= F_COMPLEX; return; }
     if (!(a_flags & F_INSERT)) return;                       // both lookup-only, nothing to find
     if ((a_flags & F_W1) || chain == 1) { r.flags |= F_COMPLEX; return; }
@@ -515,40 +598,25 @@ __device__ __forceinline__ void plan_follower(Plan &r, const Slot *tab, const u8
         if (f + b >= MRZ_MIN_MATCH) { r.flags |= F_COMPLEX; return; }
     }
     const i64 btm = (min_mask << 1) | 1;
+    const int kb = __popcll((u64)btm);
     const int myz = tz1(tag);
     r.flags |= F_INSERT | F_FOLLOW;
     r.rd_lo = (int)(tag & hmask);
     if ((tag & btm) != btm) {
         r.w2_slot = a_w2; r.rd_hi = a_w2; r.dcount = 0;
     } else {
-        i64 h = (i64)a_w2 + 1;
-        const i64 hs = h;
-        int kind = -1;
-        for (;;) {
-            Slot e[4];
-#pragma unroll
-            for (int q = 0; q < 4; q++) e[q] = ld_slot(&tab[h + q]);
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                if (kind >= 0) continue;
-                if (h + q >= hsize) { r.flags |= F_COMPLEX; return; }
-                if (slot_empty(e[q])) { kind = 0; h += q; }
-                else if (e[q].tag == tag) { r.flags |= F_COMPLEX; return; }
-                else if ((e[q].tag & btm) != btm) { kind = 1; h += q; }
-                else if (tz1(e[q].tag) < myz) { r.flags |= F_COMPLEX; return; }
-            }
-            if (kind >= 0) break;
-            h += 4;
-            if (h - hs > MAXWALK) { r.flags |= F_COMPLEX; return; }
-        }
-        r.w2_slot = (int)h; r.rd_hi = (int)h; r.dcount = kind == 0 ? 1 : 0;
+        i64 st;
+        i64 s = find_stop(ttag, gsum, (i64)a_w2 + 1, myz > kb ? myz : kb, hsize, st);
+        if (s < 0) { r.flags |= F_COMPLEX; return; }
+        if (st != 0 && (st & btm) == btm) { r.flags |= F_COMPLEX; return; }   // lesser occupant: displacement
+        r.w2_slot = (int)s; r.rd_hi = (int)s; r.dcount = st == 0 ? 1 : 0;
     }
     if (r.rd_hi >= w_lo && r.rd_lo < w_hi) r.flags |= F_COMPLEX;
 }
 
 // Refill the ring of eligible slots (those clean_one_from_hash will zero next, in order) by a
 // parallel scan of the table from e_scan; only meaningful once ins_mask == 2*min_mask+1.
-__device__ __forceinline__ void refill_queue(Smem *S, const Slot *tab, i64 hsize, int want) {
+__device__ __forceinline__ void refill_queue(Smem *S, const i64 *ttag, i64 hsize, int want) {
     const int tid = threadIdx.x;
     const i64 btm = (S->run.min_mask << 1) | 1;
     for (;;) {
@@ -559,8 +627,8 @@ __device__ __forceinline__ void refill_queue(Smem *S, const Slot *tab, i64 hsize
         // each thread examines two consecutive slots
         i64 s0 = scan + 2 * tid;
         bool g0 = false, g1 = false;
-        if (s0 < hsize) { Slot e = ld_slot(&tab[s0]); g0 = !slot_empty(e) && (e.tag & btm) != btm; }
-        if (s0 + 1 < hsize) { Slot e = ld_slot(&tab[s0 + 1]); g1 = !slot_empty(e) && (e.tag & btm) != btm; }
+        if (s0 < hsize) { i64 t = __ldcg(ttag + s0); g0 = t != 0 && (t & btm) != btm; }
+        if (s0 + 1 < hsize) { i64 t = __ldcg(ttag + s0 + 1); g1 = t != 0 && (t & btm) != btm; }
         int total;
         int ex = block_excl_scan((int)g0 + (int)g1, S->wsum, total);
         unsigned base = S->e_cnt + (unsigned)ex;
@@ -594,8 +662,8 @@ __device__ __forceinline__ void sync_queue(Smem *S, int nlog) {
 
 // Runs the automaton over the current segment's candidate list (or to the end of the chunk).
 __global__ void __launch_bounds__(AT, 1)
-k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restrict__ hidx, AutoState *st,
-            const i64 *__restrict__ tile_off, const u32 *__restrict__ cand_pos,
+k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum_global, const i64 *__restrict__ hidx,
+            AutoState *st, const i64 *__restrict__ tile_off, const u32 *__restrict__ cand_pos,
             const i64 *__restrict__ cand_tag, Token *toks, i64 *dbg) {
     if (st->done || st->error) return;
     MRZ_SMEM_PTR(Smem, S);
@@ -609,6 +677,8 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restr
     const i64 n = st->n, end = st->end, hmask = st->hmask, hsize = st->hsize, limit = st->limit;
     const int chain = st->chain;
     const i64 seg_lo = st->seg_lo, seg_hi = st->seg_hi, ncand = st->seg_ncand;
+    const int gwords = (int)(hsize >> (GRP_SHIFT + 3));          // summary words in use
+    for (int q = tid; q < gwords; q += AT) S->gsum[q] = gsum_global[q];
     if (tid == 0) {
         Run &r = S->run;
         r.p = st->p; r.last = st->last; r.cur_p = st->cur_p; r.cur_len = st->cur_len; r.cur_ofs = st->cur_ofs;
@@ -620,7 +690,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restr
         S->li = 0; S->bmax = AT;
     }
     Warp w;   // used by warp 0 only
-    w.buf = buf; w.tab = tab; w.filt = filt; w.toks = toks; w.lane = lane;
+    w.buf = buf; w.ttag = ttag; w.toff = toff; w.filt = filt; w.gsum = S->gsum; w.toks = toks; w.lane = lane;
     w.n = n; w.end = end; w.hmask = hmask; w.hsize = hsize; w.limit = limit; w.tok_cap = st->tok_cap; w.chain = chain;
     w.wlog = S->wlog; w.nlog = 0; w.clean_hint = 0;
     __syncthreads();
@@ -634,7 +704,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restr
         const int bmax = S->bmax;
         if (steady) {
             if (tid == 0 && S->e_scan < S->run.clean_ptr) S->e_scan = S->run.clean_ptr;
-            refill_queue(S, tab, hsize, bmax);
+            refill_queue(S, ttag, hsize, bmax);
         } else if (tid == 0) {
             S->e_idx = S->e_cnt = 0; S->e_scan = S->run.clean_ptr;
         }
@@ -668,11 +738,11 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restr
         tm[8] += nr; tm[9] += 1;
         // ---------------------------------------------------------------- phase A: plan
         Plan pl;
-        pl.flags = 0; pl.dcount = 0; pl.rd_lo = 1; pl.rd_hi = 0; pl.rd2_lo = -1; pl.rd2_hi = -1;
-        pl.w1_slot = -1; pl.w2_slot = -1; pl.w1_off = 0; pl.w1_tag = 0;
+        plan_init(pl);
         i64 my_pos = 0, my_tag = 0;
         bool follower = false;
         for (int q = tid; q < WH_CAP; q += AT) { S->wh_key[q] = -1; S->wh_val[q] = 0x7fffffff; }
+        if (tid == 0) S->wh_over = 0;
         if (tid < nr) {
             const u32 rel = S->b_rel[tid];
             my_pos = seg_lo + (i64)rel; my_tag = S->b_tag[tid];
@@ -683,26 +753,26 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restr
             if (!follower) {
                 if (filt_query(filt, my_tag)) pl.flags |= F_COMPLEX;          // an equal tag may exist
                 else if ((my_tag & ins_mask) == ins_mask)
-                    plan_op(pl, tab, my_tag, hmask, hsize, min_mask, chain, w_lo, w_hi);
+                    plan_op(pl, ttag, toff, S->gsum, filt, my_tag, hmask, hsize, min_mask, chain, w_lo, w_hi);
             }
             S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;
         }
         __syncthreads();
         if (follower) {
-            plan_follower(pl, tab, buf, my_pos, my_tag, S->pl_fl[tid - 1], S->pl_w2[tid - 1], hmask, hsize, min_mask, chain,
-                          end, last_now, w_lo, w_hi);
+            plan_follower(pl, ttag, S->gsum, buf, my_pos, my_tag, S->pl_fl[tid - 1], S->pl_w2[tid - 1], hmask, hsize, min_mask,
+                          chain, end, last_now, w_lo, w_hi);
             S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;    // its leader looks at this when committing
         }
         TICK(2);   // plan
         const bool planned_ins = tid < nr && (pl.flags & (F_COMPLEX | F_INSERT)) == F_INSERT;
         if (planned_ins) {
-            wh_insert(S, pl.w2_slot, tid);
-            if (pl.flags & F_W1) wh_insert(S, pl.w1_slot, tid);
+            wh_insert_slot(S, pl.w2_slot, tid);
+            if (pl.flags & F_W1) wh_insert_slot(S, pl.w1_slot, tid);
         }
         __syncthreads();
         if (planned_ins) {   // a follower's plan builds on its leader's write: only older writes conflict
             const int before = (pl.flags & F_FOLLOW) ? tid - 1 : tid;
-            if (wh_range_hit(S, pl.rd_lo, pl.rd_hi, before) ||
+            if ((S->wh_over && tid > 0) || wh_range_hit(S, pl.rd_lo, pl.rd_hi, before) ||
                 (pl.rd2_lo >= 0 && wh_range_hit(S, pl.rd2_lo, pl.rd2_hi, tid)))
                 pl.flags |= F_CONF;
         }
@@ -737,18 +807,32 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restr
             const int k = block_min(cut, &S->red);
             // commit [pos, k)
             if (tid >= pos && tid < k && (pl.flags & F_INSERT)) {
-                if (pl.flags & F_W1) st_slot(&tab[pl.w1_slot], pl.w1_off, pl.w1_tag);
+                if (pl.flags & F_W1) {
+                    __stcg(toff + pl.w1_slot, pl.w1_off);
+                    __stcg(ttag + pl.w1_slot, pl.w1_tag);
+                    nib_lower(S->gsum, pl.w1_slot >> GRP_SHIFT, tz1c(pl.w1_tag));
+                }
                 // a twin that overwrites its leader's entry in the same commit must win the slot
                 const bool overwritten = tid + 1 < k && (S->pl_fl[tid + 1] & F_FOLLOW) && S->pl_w2[tid + 1] == pl.w2_slot;
-                if (!overwritten) st_slot(&tab[pl.w2_slot], my_pos, my_tag);
+                if (!overwritten) {
+                    __stcg(toff + pl.w2_slot, my_pos);
+                    __stcg(ttag + pl.w2_slot, my_tag);
+                    nib_lower(S->gsum, pl.w2_slot >> GRP_SHIFT, tz1c(my_tag));
+                }
                 filt_set(filt, my_tag);
+                if (pl.flags & F_FOLLOW) filt_set(filt, my_tag ^ DUP_SALT);   // the tag is in the table twice now
             }
             int cleans = 0;
             if (k > pos) {
                 const unsigned d = (unsigned)S->pre[k - 1] - (unsigned)base;
                 i64 T = cnt0 + (d & 0x7ffu);
                 cleans = T > limit ? (int)(T - limit) : 0;
-                if (tid < cleans) st_slot(&tab[S->E[(S->e_idx + tid) & (EQ_CAP - 1)]], 0, 0);
+                if (tid < cleans) {
+                    const int sl = S->E[(S->e_idx + tid) & (EQ_CAP - 1)];
+                    __stcg(ttag + sl, (i64)0);
+                    __stcg(toff + sl, (i64)0);
+                    nib_lower(S->gsum, sl >> GRP_SHIFT, 0);
+                }
                 __syncthreads();   // everyone has read run.count / e_idx
                 if (tid == 0) {
                     Run &r = S->run;
@@ -862,6 +946,7 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restr
     if (tid == 0 && dbg)
         for (int q = 0; q < 12; q++) dbg[q] += tm[q];
     // segment exhausted (or chunk finished)
+    for (int q = tid; q < gwords; q += AT) gsum_global[q] = S->gsum[q];
     if (tid == 0) {
         const Run &r = S->run;
         i64 p = r.p;
@@ -876,12 +961,13 @@ k_automaton(const u8 *__restrict__ buf, Slot *tab, u64 *filt, const i64 *__restr
     }
 }
 
-extern "C" void mrz_launch_automaton(const u8 *buf, Slot *tab, u64 *filt, const i64 *hidx, AutoState *st, const i64 *tile_off,
-                                     const u32 *cand_pos, const i64 *cand_tag, Token *toks, i64 *dbg, cudaStream_t s) {
+extern "C" void mrz_launch_automaton(const u8 *buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum, const i64 *hidx, AutoState *st,
+                                     const i64 *tile_off, const u32 *cand_pos, const i64 *cand_tag, Token *toks, i64 *dbg,
+                                     cudaStream_t s) {
 #ifndef MRZ_CUSIM
     cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, tab, filt, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
+    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, ttag, toff, filt, gsum, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
 #else
-    MRZ_LAUNCH(k_automaton, 1, AT, s, buf, tab, filt, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
+    MRZ_LAUNCH(k_automaton, 1, AT, s, buf, ttag, toff, filt, gsum, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
 #endif
 }

@@ -15,8 +15,8 @@
 extern "C" {
 void mrz_launch_scan(const u8 *, const i64 *, AutoState *, int *, i64 *, u32 *, i64 *, int, cudaStream_t);
 void mrz_launch_debug_tags(const u8 *, const i64 *, i64, i64, i64 *, cudaStream_t);
-void mrz_launch_automaton(const u8 *, Slot *, u64 *, const i64 *, AutoState *, const i64 *, const u32 *, const i64 *,
-                          Token *, i64 *, cudaStream_t);
+void mrz_launch_automaton(const u8 *, i64 *, i64 *, u64 *, u32 *, const i64 *, AutoState *, const i64 *, const u32 *,
+                          const i64 *, Token *, i64 *, cudaStream_t);
 void mrz_crc_upload_consts(const void *);
 void mrz_launch_crc(const u8 *, i64, u32 *, u32 *, u32 *, cudaStream_t, int *);
 void mrz_launch_exclusive_scan(const i64 *, i64 *, i64, i64 *, i64 *, cudaStream_t, int *);
@@ -37,7 +37,8 @@ struct mrz_ctx {
     cudaEvent_t ev[4];
     // device buffers
     u8 *d_buf_alloc, *d_buf;  // chunk with MRZ_PAD slack on both sides
-    Slot *d_tab; i64 tab_slots;
+    i64 *d_tab; i64 tab_slots;   // tags[tab_slots + 32] then offs[tab_slots + 32]
+    u32 *d_gsum;         // group summary of the automaton, kept across its launches
     u64 *d_filt;         // tag filter of the automaton: MRZ_FILT_WORDS 64-bit words
     i64 *d_hidx;
     AutoState *d_st;
@@ -191,7 +192,7 @@ static int ensure_s0(mrz_ctx *ctx, i64 bytes) {
 extern "C" void mrz_ctx_destroy(mrz_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaFree(ctx->d_buf_alloc); cudaFree(ctx->d_tab); cudaFree(ctx->d_filt); cudaFree(ctx->d_hidx); cudaFree(ctx->d_st);
+    cudaFree(ctx->d_buf_alloc); cudaFree(ctx->d_tab); cudaFree(ctx->d_gsum); cudaFree(ctx->d_filt); cudaFree(ctx->d_hidx); cudaFree(ctx->d_st);
     cudaFree(ctx->d_tile_cnt); cudaFree(ctx->d_tile_off); cudaFree(ctx->d_cand_pos); cudaFree(ctx->d_cand_tag);
     cudaFree(ctx->d_toks); cudaFree(ctx->d_a0); cudaFree(ctx->d_a1); cudaFree(ctx->d_off0); cudaFree(ctx->d_off1);
     cudaFree(ctx->d_bsum); cudaFree(ctx->d_tot); cudaFree(ctx->d_dbg); cudaFree(ctx->d_s0); cudaFree(ctx->d_s1);
@@ -216,7 +217,8 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     ctx->d_buf = ctx->d_buf_alloc + MRZ_PAD;
     CK(cudaMemset(ctx->d_buf_alloc, 0, MRZ_PAD));
     ctx->tab_slots = (i64)64 * 65536;  // largest levels[].mb_used = 64 MiB
-    CK(cudaMalloc(&ctx->d_tab, (size_t)(ctx->tab_slots + 8) * sizeof(Slot)));  // + slack for 4-slot probe loads
+    CK(cudaMalloc(&ctx->d_tab, (size_t)(ctx->tab_slots + 32) * 16));  // + slack for 4-slot probe loads
+    CK(cudaMalloc(&ctx->d_gsum, (size_t)(ctx->tab_slots / 16 / 8) * 4));
     CK(cudaMalloc(&ctx->d_filt, (size_t)MRZ_FILT_WORDS * 8));
     CK(cudaMalloc(&ctx->d_hidx, 256 * 8));
     CK(cudaMalloc(&ctx->d_st, sizeof(AutoState)));
@@ -296,7 +298,8 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaEventRecord(ctx->ev[0], s));
     CK(cudaMemcpyAsync(ctx->d_hidx, prm->hash_index, 256 * 8, cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(ctx->d_st, &h, sizeof h, cudaMemcpyHostToDevice, s));
-    CK(cudaMemsetAsync(ctx->d_tab, 0, (size_t)(h.hsize + 8) * sizeof(Slot), s));  // rzip.c:518-519
+    CK(cudaMemsetAsync(ctx->d_tab, 0, (size_t)(ctx->tab_slots + 32) * 16, s));  // rzip.c:518-519
+    CK(cudaMemsetAsync(ctx->d_gsum, 0, (size_t)(ctx->tab_slots / 16 / 8) * 4, s));
     CK(cudaMemsetAsync(ctx->d_filt, 0, (size_t)MRZ_FILT_WORDS * 8, s));
     CK(cudaMemsetAsync(ctx->d_tot, 0, sizeof(EmitTotals), s));
     if (ctx->d_dbg) CK(cudaMemsetAsync(ctx->d_dbg, 0, 12 * 8, s));
@@ -316,7 +319,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
         mrz_launch_scan(ctx->d_buf, ctx->d_hidx, ctx->d_st, ctx->d_tile_cnt, ctx->d_tile_off, ctx->d_cand_pos,
                         ctx->d_cand_tag, tiles, s);
         CK(cudaEventRecord(ctx->ev[2], s));
-        mrz_launch_automaton(ctx->d_buf, ctx->d_tab, ctx->d_filt, ctx->d_hidx, ctx->d_st, ctx->d_tile_off, ctx->d_cand_pos,
+        mrz_launch_automaton(ctx->d_buf, ctx->d_tab, ctx->d_tab + ctx->tab_slots + 32, ctx->d_filt, ctx->d_gsum, ctx->d_hidx, ctx->d_st, ctx->d_tile_off, ctx->d_cand_pos,
                              ctx->d_cand_tag, ctx->d_toks, ctx->d_dbg, s);
         CK(cudaEventRecord(ctx->ev[3], s));
         launches += 4;
