@@ -44,8 +44,7 @@
 #define WLOG_CAP 64
 #define GRP 16             // slots per summary group
 #define GRP_SHIFT 4
-#define EXACT_RANGE 48     // read ranges up to this many slots are checked slot by slot
-#define CGRP_SHIFT 6       // longer ones: 64-slot conflict groups for the middle part
+#define CGRP_SHIFT 4       // conflict check: whole 16-slot groups inside a read range are tested as groups
 #define DUP_SALT 0x5bd1e9955bd1e995LL
 
 enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8, F_FOLLOW = 16 };
@@ -93,6 +92,8 @@ __device__ __forceinline__ void nib_lower(u32 *gs, i64 g, int v) {
         old = seen;
     }
 }
+
+__device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int need, i64 hsize, i64 &stop_tag);
 
 // Running state of the automaton, shared by the whole CTA (rzip_state, mrzip_private.h:388-416).
 struct Run {
@@ -321,7 +322,20 @@ struct Warp {
         if ((t & ins_mask) == ins_mask) {
             inserts++;
             count++;
-            insert(t, pp, stk);
+            bool placed = false;
+            if (!maybe) {   // no equal tag exists: the insert slot is the first empty / due-for-sweep / lesser entry
+                const i64 btm = (min_mask << 1) | 1;
+                const int kb = __popcll((u64)btm), myz = tz1(t);
+                i64 stg;
+                i64 sl = find_stop(ttag, gsum, t & hmask, myz > kb ? myz : kb, hsize, stg);
+                __syncwarp();                          // every lane has read the table before lane 0 writes it
+                if (sl >= 0 && (stg == 0 || (stg & btm) != btm)) {
+                    if (stg != 0) count--;             // rzip.c:267-269
+                    write_slot(sl, pp, t);
+                    placed = true;
+                }
+            }
+            if (!placed) insert(t, pp, stk);
             if (lane == 0) {
                 filt_set(filt, t);
                 if (maybe) filt_set(filt, t ^ DUP_SALT);              // this tag may now be in the table twice
@@ -393,6 +407,7 @@ struct Smem {
     int wlog[WLOG_CAP];
     int wsum[40];
     unsigned e_idx, e_cnt;  // ring counters (monotonic)
+    unsigned cutmask[AT / 32];
     int nr, pos, k, nlog, jumped, ended, bmax, red, wh_over;
 };
 
@@ -466,22 +481,21 @@ __device__ __forceinline__ bool wh_hit(const Smem *S, int key, int before) {
     }
     return true;
 }
-// true when some op with index < before writes a slot in [lo, hi] (conservative for long ranges: whole
-// 64-slot groups in the middle of the range are tested as groups)
+// true when some op with index < before writes a slot in [lo, hi].  Exact: the partial groups at either end
+// are tested slot by slot, the 16-slot groups lying wholly inside the range by their group key.
 __device__ __forceinline__ bool wh_range_hit(const Smem *S, int lo, int hi, int before) {
-    if (hi - lo < EXACT_RANGE) {
+    const int g_lo = (lo + (1 << CGRP_SHIFT) - 1) >> CGRP_SHIFT, g_hi = (hi + 1) >> CGRP_SHIFT;   // full groups: [g_lo, g_hi)
+    if (g_lo >= g_hi) {
         for (int s = lo; s <= hi; s++)
             if (wh_hit(S, s, before)) return true;
         return false;
     }
-    const int g_lo = (lo >> CGRP_SHIFT) + 1, g_hi = hi >> CGRP_SHIFT;   // full groups: [g_lo, g_hi)
-    for (int s = lo; s < (g_lo << CGRP_SHIFT) && s <= hi; s++)
+    for (int s = lo; s < (g_lo << CGRP_SHIFT); s++)
         if (wh_hit(S, s, before)) return true;
     for (int g = g_lo; g < g_hi; g++)
         if (wh_hit(S, (1 << 30) | g, before)) return true;
-    if (g_hi >= g_lo)
-        for (int s = g_hi << CGRP_SHIFT; s <= hi; s++)
-            if (wh_hit(S, s, before)) return true;
+    for (int s = g_hi << CGRP_SHIFT; s <= hi; s++)
+        if (wh_hit(S, s, before)) return true;
     return false;
 }
 
@@ -495,6 +509,7 @@ struct Plan {
 // First slot s >= h with tz1(tags[s]) < need (an empty slot has tag 0, i.e. zero trailing ones), or -1 when
 // the walk reaches the end of the table / gets too long.  Whole groups whose summary nibble is >= need are
 // skipped unseen; a group that is scanned completely without a hit has its nibble repaired.
+// Tags are read eight at a time (four 128-bit loads, two 32-byte sectors).
 __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int need, i64 hsize, i64 &stop_tag) {
     if (h >= hsize) return -1;
     const i64 h0 = h;
@@ -506,24 +521,23 @@ __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int 
     }
     bool whole = (h & (GRP - 1)) == 0;
     for (;;) {
-        // scan the rest of group g from h, four tags per step
         const i64 gend = (g + 1) << GRP_SHIFT;
         int mn = 15;
-        while (h < gend) {
-            i64 t[4];
+        for (i64 o = h & ~(i64)7; o < gend; o += 8) {
+            longlong2 v[4];
 #pragma unroll
-            for (int q = 0; q < 4; q++) t[q] = __ldcg(ttag + h + q);   // the table has slack past hsize
+            for (int q = 0; q < 4; q++) v[q] = __ldcg(reinterpret_cast<const longlong2 *>(ttag + o) + q);
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-                if (h + q < gend) {
-                    int z = tz1(t[q]);
+            for (int q = 0; q < 8; q++) {
+                const i64 t = (q & 1) ? v[q >> 1].y : v[q >> 1].x;
+                if (o + q >= h) {
+                    int z = tz1(t);
                     if (z < 0) z = 64;
-                    if (z < need) { stop_tag = t[q]; return h + q; }
+                    if (z < need) { stop_tag = t; return o + q; }
                     int zc = z > 15 ? 15 : z;
                     mn = zc < mn ? zc : mn;
                 }
             }
-            h += 4;
         }
         if (whole) nib_raise(gsum, g, mn);
         // skip groups that cannot contain a stop
@@ -616,9 +630,11 @@ __device__ __forceinline__ void plan_follower(Plan &r, const i64 *ttag, u32 *gsu
 
 // Refill the ring of eligible slots (those clean_one_from_hash will zero next, in order) by a
 // parallel scan of the table from e_scan; only meaningful once ins_mask == 2*min_mask+1.
-__device__ __forceinline__ void refill_queue(Smem *S, const i64 *ttag, i64 hsize, int want) {
+// The scan never goes past scan_end (the table end, or the window the current batch was planned with).
+__device__ __forceinline__ void refill_queue(Smem *S, const i64 *ttag, i64 scan_end, int want) {
     const int tid = threadIdx.x;
     const i64 btm = (S->run.min_mask << 1) | 1;
+    const i64 hsize = scan_end;
     for (;;) {
         __syncthreads();
         int avail = (int)(S->e_cnt - S->e_idx);
@@ -667,9 +683,9 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             const i64 *__restrict__ cand_tag, Token *toks, i64 *dbg) {
     if (st->done || st->error) return;
     MRZ_SMEM_PTR(Smem, S);
-    i64 tm[12];
+    i64 tm[20];
 #pragma unroll
-    for (int q = 0; q < 12; q++) tm[q] = 0;
+    for (int q = 0; q < 20; q++) tm[q] = 0;
     i64 t_prev = clock64();
 #define TICK(slot) do { i64 t_now = clock64(); tm[slot] += t_now - t_prev; t_prev = t_now; } while (0)
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -794,17 +810,26 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             const i64 cnt0 = S->run.count;
             const int avail = (int)(S->e_cnt - S->e_idx);
             const i64 cur_len = S->run.cur_len, cur_p = S->run.cur_p;
-            int cut = nr;
+            const unsigned e_idx0 = S->e_idx;
+            bool c = false;
             if (tid >= pos && tid < nr) {
-                bool c = (pl.flags & (F_COMPLEX | F_CONF)) != 0;
+                c = (pl.flags & (F_COMPLEX | F_CONF)) != 0;
                 c = c || (cur_len >= MRZ_MIN_MATCH && my_pos >= cur_p + MRZ_MIN_MATCH);   // an emission is due
                 if (!c && (pl.flags & F_INSERT) && pl.dcount == 1) {
                     i64 T = cnt0 + (((unsigned)S->pre[tid] - (unsigned)base) & 0x7ffu);
                     if (T > limit && (!steady || T - limit > avail)) c = true;             // needs a serial sweep step
                 }
-                if (c) cut = tid;
             }
-            const int k = block_min(cut, &S->red);
+            {
+                const unsigned bal = __ballot_sync(FULL, c);
+                if (lane == 0) S->cutmask[wid] = bal;
+            }
+            __syncthreads();   // every thread has read pos / count / queue state; the mask is complete
+            int k = nr;        // first op of [pos, nr) that cannot be committed from its plan
+            for (int wd = pos >> 5; wd < ((nr + 31) >> 5); wd++) {
+                const unsigned m = S->cutmask[wd];
+                if (m) { k = wd * 32 + __ffs(m) - 1; break; }
+            }
             // commit [pos, k)
             if (tid >= pos && tid < k && (pl.flags & F_INSERT)) {
                 if (pl.flags & F_W1) {
@@ -828,12 +853,11 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                 i64 T = cnt0 + (d & 0x7ffu);
                 cleans = T > limit ? (int)(T - limit) : 0;
                 if (tid < cleans) {
-                    const int sl = S->E[(S->e_idx + tid) & (EQ_CAP - 1)];
+                    const int sl = S->E[(e_idx0 + tid) & (EQ_CAP - 1)];
                     __stcg(ttag + sl, (i64)0);
                     __stcg(toff + sl, (i64)0);
                     nib_lower(S->gsum, sl >> GRP_SHIFT, 0);
                 }
-                __syncthreads();   // everyone has read run.count / e_idx
                 if (tid == 0) {
                     Run &r = S->run;
                     r.count = T - cleans;
@@ -851,6 +875,14 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             __syncthreads();
             TICK(4);   // cut search + commit
             tm[10] += 1;
+            if (tid == k) {   // why is this op serial?
+                int why = (pl.flags & F_COMPLEX) ? (follower ? 12 : ((pl.flags & F_INSERT) ? 13 : 11)) : (pl.flags & F_CONF) ? 14 : 15;
+                if (dbg) atomicAdd((unsigned long long *)&dbg[why], 1ULL);
+                if (dbg && why == 15) {
+                    int sub = (cur_len >= MRZ_MIN_MATCH && my_pos >= cur_p + MRZ_MIN_MATCH) ? 17 : (!steady ? 18 : 19);
+                    atomicAdd((unsigned long long *)&dbg[sub], 1ULL);
+                }
+            }
             // ---- op k on the live table, reference semantics (warp 0)
             if (wid == 0) {
                 w.load(S->run);
@@ -918,6 +950,9 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             __syncthreads();
             TICK(5);   // serial op
             if (S->ended) break;
+            // the op overwrote a queued slot and the queue was cut there: rebuild its tail, but only inside the
+            // window this batch was planned with
+            if (steady && S->e_scan < w_hi) refill_queue(S, ttag, w_hi, EQ_CAP);
             // later plans that read a slot this op wrote are no longer valid; nor is its twin's plan
             if (tid == k + 1 && (pl.flags & F_FOLLOW)) pl.flags |= F_CONF;
             if (tid > k && tid < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
@@ -926,6 +961,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                     int sl = S->wlog[q] >> 1;
                     if ((sl >= pl.rd_lo && sl <= pl.rd_hi) || (pl.rd2_lo >= 0 && sl >= pl.rd2_lo && sl <= pl.rd2_hi)) {
                         pl.flags |= F_CONF;
+                        if (dbg) atomicAdd((unsigned long long *)&dbg[16], 1ULL);
                         break;
                     }
                 }
@@ -944,7 +980,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
         TICK(7);
     }
     if (tid == 0 && dbg)
-        for (int q = 0; q < 12; q++) dbg[q] += tm[q];
+        for (int q = 0; q < 11; q++) dbg[q] += tm[q];
     // segment exhausted (or chunk finished)
     for (int q = tid; q < gwords; q += AT) gsum_global[q] = S->gsum[q];
     if (tid == 0) {

@@ -47,7 +47,7 @@ struct mrz_ctx {
     i64 *d_a0, *d_a1, *d_off0, *d_off1, *d_bsum; i64 item_cap;
     EmitTotals *d_tot;
     i64 *d_dbg;          // phase cycle counters of k_automaton (MRZ_PROFILE=1), else NULL
-    i64 h_dbg[12];
+    i64 h_dbg[20];
     u8 *d_s0; i64 s0_cap; u8 *d_s1; i64 s1_cap;
     u32 *d_crc_part, *d_crc_part2, *d_crc_misc;  // misc[0]=tail, misc[1]=final
     // host staging
@@ -227,7 +227,7 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     CK(cudaMalloc(&ctx->d_cand_pos, (size_t)(SEG_CAND_CAP + 64) * sizeof(u32)));
     CK(cudaMalloc(&ctx->d_cand_tag, (size_t)(SEG_CAND_CAP + 64) * sizeof(i64)));
     CK(cudaMalloc(&ctx->d_tot, sizeof(EmitTotals)));
-    if (getenv("MRZ_PROFILE")) CK(cudaMalloc(&ctx->d_dbg, 12 * 8));
+    if (getenv("MRZ_PROFILE")) CK(cudaMalloc(&ctx->d_dbg, 20 * 8));
     CK(cudaMalloc(&ctx->d_s1, (size_t)max_chunk + 64));
     ctx->s1_cap = max_chunk + 64;
     i64 nblk = max_chunk / 16384 + 1;
@@ -302,7 +302,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaMemsetAsync(ctx->d_gsum, 0, (size_t)(ctx->tab_slots / 16 / 8) * 4, s));
     CK(cudaMemsetAsync(ctx->d_filt, 0, (size_t)MRZ_FILT_WORDS * 8, s));
     CK(cudaMemsetAsync(ctx->d_tot, 0, sizeof(EmitTotals), s));
-    if (ctx->d_dbg) CK(cudaMemsetAsync(ctx->d_dbg, 0, 12 * 8, s));
+    if (ctx->d_dbg) CK(cudaMemsetAsync(ctx->d_dbg, 0, 20 * 8, s));
     launches += 2;
     // CRC of the chunk (independent of the automaton)
     mrz_launch_crc(ctx->d_buf, n, ctx->d_crc_part, ctx->d_crc_part2, ctx->d_crc_misc, s, &launches);
@@ -346,11 +346,14 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     }
 
     if (ctx->d_dbg) {
-        CK(cudaMemcpyAsync(ctx->h_dbg, ctx->d_dbg, 12 * 8, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(ctx->h_dbg, ctx->d_dbg, 20 * 8, cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
         static const char *nm[12] = {"refill", "gather", "plan", "conflict", "commit", "serial", "inval", "epilogue", "ops", "batches", "serial_ops", ""};
         fprintf(stderr, "[mrz profile] automaton cycles:");
         for (int q = 0; q < 11; q++) fprintf(stderr, " %s=%lld", nm[q], (long long)ctx->h_dbg[q]);
+        fprintf(stderr, " | serial because: filter+=%lld twin-complex=%lld insert-complex=%lld conflict=%lld emit/count=%lld [emit %lld, first overflow %lld, queue %lld] (dynamic invalidations %lld)",
+                (long long)ctx->h_dbg[11], (long long)ctx->h_dbg[12], (long long)ctx->h_dbg[13], (long long)ctx->h_dbg[14],
+                (long long)ctx->h_dbg[15], (long long)ctx->h_dbg[17], (long long)ctx->h_dbg[18], (long long)ctx->h_dbg[19], (long long)ctx->h_dbg[16]);
         fprintf(stderr, "\n");
     }
     // ---- emission ----

@@ -122,6 +122,13 @@ void launch(dim3 grid, dim3 block, const std::function<void()> &body) {
                     }
                     if (!progress && blk.nlive > 0) {
                         fprintf(stderr, "cusim: deadlock in block (%u,%u,%u): %d live threads all waiting\n", bx, by, bz, blk.nlive);
+                        int nb = 0, nw = 0;
+                        for (int i = 0; i < nthreads; i++) { nb += fiber_pool[i].status == 1; nw += fiber_pool[i].status == 2; }
+                        fprintf(stderr, "  %d at the block barrier, %d at a warp collective; warp-waiters:", nb, nw);
+                        for (int i = 0, c = 0; i < nthreads && c < 40; i++) if (fiber_pool[i].status == 2) { fprintf(stderr, " %d", i); c++; }
+                        fprintf(stderr, "\n  barrier-waiters:");
+                        for (int i = 0, c = 0; i < nthreads && c < 40; i++) if (fiber_pool[i].status == 1) { fprintf(stderr, " %d", i); c++; }
+                        fprintf(stderr, "\n");
                         abort();
                     }
                 }
