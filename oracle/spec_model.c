@@ -130,6 +130,14 @@ static int wcmp(const void *a, const void *b) {
     if (x->slot != y->slot) return x->slot < y->slot ? -1 : 1;
     return x->idx - y->idx;
 }
+/* exact-slot rule: some op with index < j writes exactly slot s */
+static int slot_hit(const wkey *w, int nw, i64 s, int j) {
+    int a = 0, b = nw;
+    while (a < b) { int m = (a + b) / 2; if (w[m].slot < s) a = m + 1; else b = m; }
+    for (; a < nw && w[a].slot == s; a++)
+        if (w[a].idx < j) return 1;
+    return 0;
+}
 static int range_hit(const wkey *w, int nw, i64 lo, i64 hi, int j) {
     int a = 0, b = nw;
     while (a < b) { int m = (a + b) / 2; if (w[m].slot < lo) a = m + 1; else b = m; }
@@ -157,6 +165,7 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
     c.s0 = s0; c.s1 = s1; c.s0_cap = s0_cap; c.s1_cap = s1_cap; c.cb = chunk_bytes;
     i64 wlog[256];
     c.wlog = wlog;
+    const int exact_rule = getenv("SPEC_RANGE") == NULL;
 
     i64 ins_mask = ((i64)1 << LEVELS[level].freq) - 1;
     c.min_mask = ins_mask;
@@ -221,7 +230,15 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
         for (int j = 0; j < nr; j++) {
             conf[j] = 0;
             if (R[j].flags & F_COMPLEX) { ss->complex_ops++; continue; }
-            if (range_hit(W, nw, R[j].rd_lo, R[j].rd_hi, (R[j].flags & F_FOLLOW) ? j - 1 : j) ||
+            int before = (R[j].flags & F_FOLLOW) ? j - 1 : j;
+            if (exact_rule && ins_mask == btm) {
+                /* steady state: an insert only ever raises the trailing-one count of the slot it writes, so a walk that
+                 * passed a slot still passes it; only a write to one of my own stop slots changes my plan */
+                if (!(R[j].flags & F_INSERT)) continue;
+                if (slot_hit(W, nw, R[j].w2_slot, before) || ((R[j].flags & F_W1) && slot_hit(W, nw, R[j].w1_slot, j))) { conf[j] = 1; ss->static_conflicts++; }
+                continue;
+            }
+            if (range_hit(W, nw, R[j].rd_lo, R[j].rd_hi, before) ||
                 (R[j].rd2_lo >= 0 && range_hit(W, nw, R[j].rd2_lo, R[j].rd2_hi, j))) { conf[j] = 1; ss->static_conflicts++; }
         }
         /* ---- phase B */
