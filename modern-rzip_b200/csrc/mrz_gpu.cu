@@ -17,6 +17,9 @@ void mrz_launch_scan(const u8 *, const i64 *, AutoState *, int *, i64 *, u32 *, 
 void mrz_launch_debug_tags(const u8 *, const i64 *, i64, i64, i64 *, cudaStream_t);
 void mrz_launch_automaton(const u8 *, i64 *, i64 *, u64 *, u32 *, const i64 *, AutoState *, const i64 *, const u32 *,
                           const i64 *, Token *, i64 *, cudaStream_t);
+size_t mrz_grid_state_bytes();
+int mrz_launch_automaton_grid(int, int, const u8 *, i64 *, i64 *, u64 *, u32 *, unsigned *, void *, const i64 *, AutoState *,
+                              const i64 *, const u32 *, const i64 *, Token *, i64 *, cudaStream_t);
 void mrz_crc_upload_consts(const void *);
 void mrz_launch_crc(const u8 *, i64, u32 *, u32 *, u32 *, cudaStream_t, int *);
 void mrz_launch_exclusive_scan(const i64 *, i64 *, i64, i64 *, i64 *, cudaStream_t, int *);
@@ -40,6 +43,9 @@ struct mrz_ctx {
     i64 *d_tab; i64 tab_slots;   // tags[tab_slots + 32] then offs[tab_slots + 32]
     u32 *d_gsum;         // group summary of the automaton, kept across its launches
     u64 *d_filt;         // tag filter of the automaton: MRZ_FILT_WORDS 64-bit words
+    unsigned *d_claim;   // grid automaton: per-slot claim of the current batch (automaton_grid.cu)
+    void *d_gstate;      // grid automaton: state shared by the CTAs
+    int grid_g, grid_t;  // grid automaton geometry (0 = the one-CTA automaton of automaton.cu)
     i64 *d_hidx;
     AutoState *d_st;
     int *d_tile_cnt; i64 *d_tile_off; u32 *d_cand_pos; i64 *d_cand_tag;
@@ -192,7 +198,7 @@ static int ensure_s0(mrz_ctx *ctx, i64 bytes) {
 extern "C" void mrz_ctx_destroy(mrz_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaFree(ctx->d_buf_alloc); cudaFree(ctx->d_tab); cudaFree(ctx->d_gsum); cudaFree(ctx->d_filt); cudaFree(ctx->d_hidx); cudaFree(ctx->d_st);
+    cudaFree(ctx->d_buf_alloc); cudaFree(ctx->d_tab); cudaFree(ctx->d_gsum); cudaFree(ctx->d_filt); cudaFree(ctx->d_claim); cudaFree(ctx->d_gstate); cudaFree(ctx->d_hidx); cudaFree(ctx->d_st);
     cudaFree(ctx->d_tile_cnt); cudaFree(ctx->d_tile_off); cudaFree(ctx->d_cand_pos); cudaFree(ctx->d_cand_tag);
     cudaFree(ctx->d_toks); cudaFree(ctx->d_a0); cudaFree(ctx->d_a1); cudaFree(ctx->d_off0); cudaFree(ctx->d_off1);
     cudaFree(ctx->d_bsum); cudaFree(ctx->d_tot); cudaFree(ctx->d_dbg); cudaFree(ctx->d_s0); cudaFree(ctx->d_s1);
@@ -220,6 +226,26 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     CK(cudaMalloc(&ctx->d_tab, (size_t)(ctx->tab_slots + 32) * 16));  // + slack for 4-slot probe loads
     CK(cudaMalloc(&ctx->d_gsum, (size_t)(ctx->tab_slots / 16 / 8) * 4));
     CK(cudaMalloc(&ctx->d_filt, (size_t)MRZ_FILT_WORDS * 8));
+    CK(cudaMalloc(&ctx->d_claim, (size_t)(ctx->tab_slots + 32) * 4));
+    CK(cudaMalloc(&ctx->d_gstate, mrz_grid_state_bytes()));
+    {   // geometry of the cooperative grid: G CTAs (the last one serves the sweep queue) x T threads
+        const char *a = getenv("MRZ_AUTOMATON"), *g = getenv("MRZ_G"), *t = getenv("MRZ_T");
+#ifdef MRZ_CUSIM
+        ctx->grid_g = 5; ctx->grid_t = 64;
+#else
+        ctx->grid_g = 33; ctx->grid_t = 32;
+#endif
+        if (g) ctx->grid_g = atoi(g);
+        if (t) ctx->grid_t = atoi(t);
+        if (!a || strcmp(a, "grid")) ctx->grid_g = 0;   // default: the one-CTA automaton (automaton.cu); MRZ_AUTOMATON=grid selects automaton_grid.cu
+        if (ctx->grid_g) {
+            if (ctx->grid_g < 2 || ctx->grid_g > 148 || ctx->grid_t < 32 || ctx->grid_t > 256 || (ctx->grid_t & 31) ||
+                (i64)(ctx->grid_g - 1) * ctx->grid_t > 8192) {
+                ctx->err = "bad MRZ_G / MRZ_T";
+                return MRZ_E_ARG;
+            }
+        }
+    }
     CK(cudaMalloc(&ctx->d_hidx, 256 * 8));
     CK(cudaMalloc(&ctx->d_st, sizeof(AutoState)));
     CK(cudaMalloc(&ctx->d_tile_cnt, (SEG_MAX_TILES + 1) * sizeof(int)));
@@ -301,6 +327,10 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaMemsetAsync(ctx->d_tab, 0, (size_t)(ctx->tab_slots + 32) * 16, s));  // rzip.c:518-519
     CK(cudaMemsetAsync(ctx->d_gsum, 0, (size_t)(ctx->tab_slots / 16 / 8) * 4, s));
     CK(cudaMemsetAsync(ctx->d_filt, 0, (size_t)MRZ_FILT_WORDS * 8, s));
+    if (ctx->grid_g) {
+        CK(cudaMemsetAsync(ctx->d_claim, 0xff, (size_t)(ctx->tab_slots + 32) * 4, s));
+        CK(cudaMemsetAsync(ctx->d_gstate, 0, mrz_grid_state_bytes(), s));
+    }
     CK(cudaMemsetAsync(ctx->d_tot, 0, sizeof(EmitTotals), s));
     if (ctx->d_dbg) CK(cudaMemsetAsync(ctx->d_dbg, 0, 20 * 8, s));
     launches += 2;
@@ -319,8 +349,14 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
         mrz_launch_scan(ctx->d_buf, ctx->d_hidx, ctx->d_st, ctx->d_tile_cnt, ctx->d_tile_off, ctx->d_cand_pos,
                         ctx->d_cand_tag, tiles, s);
         CK(cudaEventRecord(ctx->ev[2], s));
-        mrz_launch_automaton(ctx->d_buf, ctx->d_tab, ctx->d_tab + ctx->tab_slots + 32, ctx->d_filt, ctx->d_gsum, ctx->d_hidx, ctx->d_st, ctx->d_tile_off, ctx->d_cand_pos,
-                             ctx->d_cand_tag, ctx->d_toks, ctx->d_dbg, s);
+        if (ctx->grid_g) {
+            int lrc = mrz_launch_automaton_grid(ctx->grid_g, ctx->grid_t, ctx->d_buf, ctx->d_tab, ctx->d_tab + ctx->tab_slots + 32,
+                                                ctx->d_filt, ctx->d_gsum, ctx->d_claim, ctx->d_gstate, ctx->d_hidx, ctx->d_st,
+                                                ctx->d_tile_off, ctx->d_cand_pos, ctx->d_cand_tag, ctx->d_toks, ctx->d_dbg, s);
+            if (lrc) CK((cudaError_t)lrc);
+        } else
+            mrz_launch_automaton(ctx->d_buf, ctx->d_tab, ctx->d_tab + ctx->tab_slots + 32, ctx->d_filt, ctx->d_gsum, ctx->d_hidx, ctx->d_st,
+                                 ctx->d_tile_off, ctx->d_cand_pos, ctx->d_cand_tag, ctx->d_toks, ctx->d_dbg, s);
         CK(cudaEventRecord(ctx->ev[3], s));
         launches += 4;
         i64 prev_p = h.p;

@@ -30,6 +30,8 @@ typedef struct {
 } spec_stats;
 
 static int nonempty(const slot *s) { return (s->off | s->tag) != 0; }
+static int g_range_rule = 0;   /* SPEC_RANGE=1: the older, conservative read-range rules */
+static int in_win(i64 s, i64 w_lo, i64 w_hi) { return s >= w_lo && s < w_hi; }
 
 /* Tag filter: one 64-bit word per hash bucket, 3 bits per tag (blocked Bloom filter).  No false
  * negatives: every tag ever inserted into the table during this chunk has its bits set, so a
@@ -54,6 +56,7 @@ static void plan_op(const ctx *c, const u64 *F, rec *r, i64 pos, i64 tag, i64 in
     if ((tag & ins_mask) != ins_mask) return;         /* lookup only, and nothing to find */
     i64 h0 = tag & c->hmask, h, steps = 0;
     i64 btm = (c->min_mask << 1) | 1;
+    int w2_elig = 0, w1_elig = 0;   /* the stop slot holds an entry due for sweeping (it may sit in the sweep queue) */
     r->flags |= F_INSERT;
     r->rd_lo = h0;
     for (h = h0;; h++) {
@@ -61,7 +64,7 @@ static void plan_op(const ctx *c, const u64 *F, rec *r, i64 pos, i64 tag, i64 in
         const slot *o = &c->tab[h];
         if (!nonempty(o)) { r->w2_slot = h; r->dcount = 1; break; }
         if (o->tag == tag) { r->flags |= F_COMPLEX; return; }   /* cannot happen with a sound filter */
-        if ((o->tag & btm) != btm) { r->w2_slot = h; r->dcount = 0; break; }
+        if ((o->tag & btm) != btm) { r->w2_slot = h; r->dcount = 0; w2_elig = 1; break; }
         if (tz1(o->tag) < tz1(tag)) {
             /* one level of displacement (rzip.c:275-277) */
             i64 ot = o->tag, g = ot & c->hmask, round = 0, st2 = 0;
@@ -70,7 +73,7 @@ static void plan_op(const ctx *c, const u64 *F, rec *r, i64 pos, i64 tag, i64 in
                 if (g == c->hsize || ++st2 > MAXWALK) { r->flags |= F_COMPLEX; return; }
                 const slot *q = &c->tab[g];
                 if (!nonempty(q)) break;
-                if ((q->tag & btm) != btm) { d2 = -1; break; }
+                if ((q->tag & btm) != btm) { d2 = -1; w1_elig = 1; break; }
                 if (tz1(q->tag) < tz1(ot)) { r->flags |= F_COMPLEX; return; }
                 if (q->tag == ot && ++round == c->chain) { r->flags |= F_COMPLEX; return; }
             }
@@ -82,9 +85,16 @@ static void plan_op(const ctx *c, const u64 *F, rec *r, i64 pos, i64 tag, i64 in
         }
     }
     r->rd_hi = r->w2_slot;
-    /* anything touching the clean window is left to the serial path */
-    if (r->rd_hi >= w_lo && r->rd_lo < w_hi) r->flags |= F_COMPLEX;
-    if (r->rd2_lo >= 0 && r->rd2_hi >= w_lo && r->rd2_lo < w_hi) r->flags |= F_COMPLEX;
+    if (g_range_rule) {
+        /* anything touching the clean window is left to the serial path */
+        if (r->rd_hi >= w_lo && r->rd_lo < w_hi) r->flags |= F_COMPLEX;
+        if (r->rd2_lo >= 0 && r->rd2_hi >= w_lo && r->rd2_lo < w_hi) r->flags |= F_COMPLEX;
+    } else {
+        /* An entry due for sweeping stops every walk (its trailing-one count is below every op's need), so a slot of
+         * the sweep queue can only ever be a walk's STOP slot: only then does the order of sweeps and inserts matter. */
+        if (w2_elig && in_win(r->w2_slot, w_lo, w_hi)) r->flags |= F_COMPLEX;
+        if (w1_elig && in_win(r->w1_slot, w_lo, w_hi)) r->flags |= F_COMPLEX;
+    }
 }
 
 /* "Twin": position p+1 has the same tag as p (buf[p] == buf[p+31]) and both pass the gates.  The second op
@@ -117,10 +127,12 @@ static void plan_follower(const ctx *c, const rec *A, rec *B, i64 pos, i64 tag, 
         if (tz1(o->tag) < tz1(tag)) { B->flags |= F_COMPLEX; return; }
     }
     B->w2_slot = h; B->rd_hi = h;
-    if (B->rd_hi >= w_lo && B->rd_lo < w_hi) B->flags |= F_COMPLEX;
+    if (g_range_rule) { if (B->rd_hi >= w_lo && B->rd_lo < w_hi) B->flags |= F_COMPLEX; }
+    else if (B->dcount == 0 && in_win(h, w_lo, w_hi)) B->flags |= F_COMPLEX;
 }
 
 static int in_ranges(const rec *r, i64 s) {
+    if (!g_range_rule) return ((r->flags & F_INSERT) && s == r->w2_slot) || ((r->flags & F_W1) && s == r->w1_slot);
     return (s >= r->rd_lo && s <= r->rd_hi) || (r->rd2_lo >= 0 && s >= r->rd2_lo && s <= r->rd2_hi);
 }
 
@@ -166,6 +178,7 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
     i64 wlog[256];
     c.wlog = wlog;
     const int exact_rule = getenv("SPEC_RANGE") == NULL;
+    g_range_rule = !exact_rule;
 
     i64 ins_mask = ((i64)1 << LEVELS[level].freq) - 1;
     c.min_mask = ins_mask;
@@ -231,7 +244,7 @@ int orc_rzip_chunk_spec(const u8 *buf, i64 n, const i64 hash_index[256], int lev
             conf[j] = 0;
             if (R[j].flags & F_COMPLEX) { ss->complex_ops++; continue; }
             int before = (R[j].flags & F_FOLLOW) ? j - 1 : j;
-            if (exact_rule && ins_mask == btm) {
+            if (exact_rule) {
                 /* steady state: an insert only ever raises the trailing-one count of the slot it writes, so a walk that
                  * passed a slot still passes it; only a write to one of my own stop slots changes my plan */
                 if (!(R[j].flags & F_INSERT)) continue;

@@ -5,13 +5,18 @@
 
 namespace cusim {
 thread_local Fiber *cur = nullptr;
-thread_local Block blk;
+thread_local Block *blkp = nullptr;
 static thread_local void *sched_sp = nullptr;
 static thread_local char *stack_pool = nullptr;
 static thread_local Fiber *fiber_pool = nullptr;
 static thread_local WarpSlot *warp_pool = nullptr;
+static thread_local Block *block_pool = nullptr;
 static const size_t kStack = 128 * 1024;
-static const int kMaxThreads = 1024;
+static const int kMaxThreads = 1024;       // per block
+static const int kMaxFibers = 8192;        // all resident blocks of a cooperative launch
+static const int kMaxBlocks = 256;
+static thread_local int grid_arrived = 0, grid_blocks = 0;
+static thread_local unsigned grid_gen = 0;
 
 extern "C" void cusim_switch(void **save_sp, void *load_sp);
 asm(R"(
@@ -39,14 +44,22 @@ cusim_switch:
 
 void yield_to_scheduler() { cusim_switch(&cur->sp, sched_sp); }
 
-static void fiber_entry() {
-    (*blk.body)();
+void sync_grid() {
     Fiber *f = cur;
+    if (++grid_arrived == grid_blocks) { grid_arrived = 0; grid_gen++; return; }
+    f->status = 4; f->bar_gen = grid_gen;
+    yield_to_scheduler();
+}
+
+static void fiber_entry() {
+    (*blkp->body)();
+    Fiber *f = cur;
+    Block &b = *blkp;
     f->status = 3;
-    blk.nlive--;
-    if (blk.bar_arrived > 0 && blk.bar_arrived == blk.nlive) {  // exited threads do not take part in barriers
-        blk.bar_arrived = 0;
-        blk.bar_gen++;
+    b.nlive--;
+    if (b.bar_arrived > 0 && b.bar_arrived == b.nlive) {  // exited threads do not take part in barriers
+        b.bar_arrived = 0;
+        b.bar_gen++;
     }
     yield_to_scheduler();
     abort();
@@ -62,78 +75,114 @@ static void init_fiber(Fiber *f, int i) {
     f->status = 0;
 }
 
-void launch(dim3 grid, dim3 block, const std::function<void()> &body) {
-    int nthreads = (int)(block.x * block.y * block.z);
-    if (nthreads < 1 || nthreads > kMaxThreads) { fprintf(stderr, "cusim: bad block size %d\n", nthreads); abort(); }
-    if (!stack_pool) {
-        stack_pool = (char *)mmap(nullptr, kStack * kMaxThreads, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE, -1, 0);
-        if (stack_pool == MAP_FAILED) { perror("cusim mmap"); abort(); }
-        fiber_pool = new Fiber[kMaxThreads];
-        warp_pool = new WarpSlot[kMaxThreads / 32];
-    }
+static void ensure_pools() {
+    if (stack_pool) return;
+    stack_pool = (char *)mmap(nullptr, kStack * kMaxFibers, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE, -1, 0);
+    if (stack_pool == MAP_FAILED) { perror("cusim mmap"); abort(); }
+    fiber_pool = new Fiber[kMaxFibers];
+    warp_pool = new WarpSlot[kMaxFibers / 32 + kMaxBlocks];
+    block_pool = new Block[kMaxBlocks];
+}
+
+// Runs blocks [0, nblocks) of block_pool to completion, all resident at once.
+static void run_resident(int nblocks, int nthreads) {
     static const char *seed_env = getenv("CUSIM_SEED");
     static thread_local unsigned long long rng = seed_env ? strtoull(seed_env, nullptr, 10) * 2654435761ULL + 1 : 0;
     const bool shuffle = seed_env != nullptr;
-    Block saved = blk;
+    const int total = nblocks * nthreads;
+    const bool pow2 = (total & (total - 1)) == 0;
+    int live = total;
+    grid_arrived = 0; grid_blocks = nblocks; grid_gen = 0;
+    while (live > 0) {
+        bool progress = false;
+        // CUSIM_SEED set: visit the fibers in a different pseudo-random order on every pass, so that
+        // code relying on threads running in index order (a data race on the GPU) fails here too
+        unsigned start = 0, stride = 1;
+        if (shuffle && pow2) {
+            rng = rng * 6364136223846793005ULL + 1442695040888963407ULL;
+            start = (unsigned)(rng >> 33) & (total - 1);
+            stride = ((unsigned)(rng >> 20) & (total - 1)) | 1u;
+        }
+        for (int ii = 0; ii < total; ii++) {
+            int i = (stride == 1 && start == 0) ? ii : (int)((start + (unsigned)ii * stride) & (unsigned)(total - 1));
+            Fiber *f = &fiber_pool[i];
+            Block *b = &block_pool[f->block];
+            if (f->status == 3) continue;
+            if (f->status == 1 && f->bar_gen == b->bar_gen) continue;
+            if (f->status == 2 && f->warp_gen == b->warps[f->warp].gen) continue;
+            if (f->status == 4 && f->bar_gen == grid_gen) continue;
+            f->status = 0;
+            cur = f;
+            blkp = b;
+            cusim_switch(&sched_sp, f->sp);
+            if (f->status == 3) live--;
+            progress = true;
+        }
+        if (!progress && live > 0) {
+            fprintf(stderr, "cusim: deadlock: %d live threads all waiting (%d blocks)\n", live, nblocks);
+            int nb = 0, nw = 0, ng = 0;
+            for (int i = 0; i < total; i++) { nb += fiber_pool[i].status == 1; nw += fiber_pool[i].status == 2; ng += fiber_pool[i].status == 4; }
+            fprintf(stderr, "  %d at a block barrier, %d at a warp collective, %d at the grid barrier; warp-waiters:", nb, nw, ng);
+            for (int i = 0, c = 0; i < total && c < 40; i++) if (fiber_pool[i].status == 2) { fprintf(stderr, " %d", i); c++; }
+            fprintf(stderr, "\n  block-barrier-waiters:");
+            for (int i = 0, c = 0; i < total && c < 40; i++) if (fiber_pool[i].status == 1) { fprintf(stderr, " %d", i); c++; }
+            fprintf(stderr, "\n");
+            abort();
+        }
+    }
+}
+
+static void setup_block(Block *b, int bi, int first_fiber, uint3_ bid, dim3 grid, dim3 block, const std::function<void()> *body, void *smem) {
+    int nthreads = (int)(block.x * block.y * block.z);
+    int nwarps = (nthreads + 31) / 32;
+    b->fib = fiber_pool + first_fiber;
+    b->warps = warp_pool + (first_fiber / 32) + bi;   // disjoint even when nthreads is not a multiple of 32
+    b->bdim = block; b->gdim = grid; b->body = body; b->nthreads = nthreads;
+    b->bid = bid; b->nlive = nthreads; b->bar_arrived = 0; b->bar_gen = 0; b->smem = smem;
+    for (int w = 0; w < nwarps; w++) { b->warps[w].arrived = 0; b->warps[w].gen = 0; }
+    for (int i = 0; i < nthreads; i++) {
+        Fiber *f = &fiber_pool[first_fiber + i];
+        init_fiber(f, first_fiber + i);
+        f->block = bi;
+        f->tid = uint3_{(unsigned)i % block.x, ((unsigned)i / block.x) % block.y, (unsigned)i / (block.x * block.y)};
+        f->lane = i & 31;
+        f->warp = i >> 5;
+    }
+}
+
+void launch(dim3 grid, dim3 block, const std::function<void()> &body) {
+    int nthreads = (int)(block.x * block.y * block.z);
+    if (nthreads < 1 || nthreads > kMaxThreads) { fprintf(stderr, "cusim: bad block size %d\n", nthreads); abort(); }
+    ensure_pools();
+    Block *saved_blk = blkp;
     Fiber *saved_cur = cur;
-    blk.fib = fiber_pool;
-    blk.warps = warp_pool;
-    blk.bdim = block;
-    blk.gdim = grid;
-    blk.body = &body;
-    blk.nthreads = nthreads;
     for (unsigned bz = 0; bz < grid.z; bz++)
         for (unsigned by = 0; by < grid.y; by++)
             for (unsigned bx = 0; bx < grid.x; bx++) {
-                blk.bid = uint3_{bx, by, bz};
-                blk.nlive = nthreads;
-                blk.bar_arrived = 0;
-                blk.bar_gen = 0;
-                int nwarps = (nthreads + 31) / 32;
-                for (int w = 0; w < nwarps; w++) { warp_pool[w].arrived = 0; warp_pool[w].gen = 0; }
-                for (int i = 0; i < nthreads; i++) {
-                    Fiber *f = &fiber_pool[i];
-                    init_fiber(f, i);
-                    f->tid = uint3_{(unsigned)i % block.x, ((unsigned)i / block.x) % block.y, (unsigned)i / (block.x * block.y)};
-                    f->lane = i & 31;
-                    f->warp = i >> 5;
-                }
-                while (blk.nlive > 0) {
-                    bool progress = false;
-                    // CUSIM_SEED set: visit the fibers in a different pseudo-random order on every pass, so that
-                    // code relying on threads running in index order (a data race on the GPU) fails here too
-                    unsigned start = 0, stride = 1;
-                    if (shuffle && (nthreads & (nthreads - 1)) == 0) {
-                        rng = rng * 6364136223846793005ULL + 1442695040888963407ULL;
-                        start = (unsigned)(rng >> 33) & (nthreads - 1);
-                        stride = ((unsigned)(rng >> 20) & (nthreads - 1)) | 1u;
-                    }
-                    for (int ii = 0; ii < nthreads; ii++) {
-                        int i = (int)((start + (unsigned)ii * stride) & (unsigned)(nthreads - 1));
-                        if (stride == 1 && start == 0) i = ii;
-                        Fiber *f = &fiber_pool[i];
-                        if (f->status == 3) continue;
-                        if (f->status == 1 && f->bar_gen == blk.bar_gen) continue;
-                        if (f->status == 2 && f->warp_gen == warp_pool[f->warp].gen) continue;
-                        f->status = 0;
-                        cur = f;
-                        cusim_switch(&sched_sp, f->sp);
-                        progress = true;
-                    }
-                    if (!progress && blk.nlive > 0) {
-                        fprintf(stderr, "cusim: deadlock in block (%u,%u,%u): %d live threads all waiting\n", bx, by, bz, blk.nlive);
-                        int nb = 0, nw = 0;
-                        for (int i = 0; i < nthreads; i++) { nb += fiber_pool[i].status == 1; nw += fiber_pool[i].status == 2; }
-                        fprintf(stderr, "  %d at the block barrier, %d at a warp collective; warp-waiters:", nb, nw);
-                        for (int i = 0, c = 0; i < nthreads && c < 40; i++) if (fiber_pool[i].status == 2) { fprintf(stderr, " %d", i); c++; }
-                        fprintf(stderr, "\n  barrier-waiters:");
-                        for (int i = 0, c = 0; i < nthreads && c < 40; i++) if (fiber_pool[i].status == 1) { fprintf(stderr, " %d", i); c++; }
-                        fprintf(stderr, "\n");
-                        abort();
-                    }
-                }
+                setup_block(&block_pool[0], 0, 0, uint3_{bx, by, bz}, grid, block, &body, nullptr);
+                run_resident(1, nthreads);
             }
-    blk = saved;
+    blkp = saved_blk;
+    cur = saved_cur;
+}
+
+void launch_coop(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()> &body) {
+    int nthreads = (int)(block.x * block.y * block.z);
+    int nblocks = (int)(grid.x * grid.y * grid.z);
+    if (nthreads < 1 || nthreads > kMaxThreads || nblocks < 1 || nblocks > kMaxBlocks || nblocks * nthreads > kMaxFibers) {
+        fprintf(stderr, "cusim: bad cooperative launch %d x %d\n", nblocks, nthreads);
+        abort();
+    }
+    ensure_pools();
+    Block *saved_blk = blkp;
+    Fiber *saved_cur = cur;
+    char *smem = (char *)calloc((size_t)nblocks, smem_bytes + 64);
+    for (int b = 0; b < nblocks; b++)
+        setup_block(&block_pool[b], b, b * nthreads, uint3_{(unsigned)b % grid.x, ((unsigned)b / grid.x) % grid.y, (unsigned)b / (grid.x * grid.y)},
+                    grid, block, &body, smem + (size_t)b * (smem_bytes + 64));
+    run_resident(nblocks, nthreads);
+    free(smem);
+    blkp = saved_blk;
     cur = saved_cur;
 }
 }  // namespace cusim

@@ -81,7 +81,8 @@ namespace cusim {
 struct Fiber {
     void *sp;            // saved stack pointer
     char *stack;
-    int status;          // 0 runnable, 1 waiting at block barrier, 2 waiting at warp rendezvous, 3 done
+    int status;          // 0 runnable, 1 waiting at block barrier, 2 waiting at warp rendezvous, 3 done, 4 grid barrier
+    int block;           // index of its block (cooperative launches)
     unsigned bar_gen;    // generation waited for
     unsigned warp_gen;
     uint3_ tid;
@@ -100,22 +101,28 @@ struct Block {
     uint3_ bid;
     dim3 bdim, gdim;
     const std::function<void()> *body;
+    void *smem;          // dynamic shared memory of a cooperative launch (one per block)
 };
 extern thread_local Fiber *cur;
-extern thread_local Block blk;
+extern thread_local Block *blkp;     // block of the running fiber
 void yield_to_scheduler();
 void launch(dim3 grid, dim3 block, const std::function<void()> &body);
+// all blocks resident at once (cudaLaunchCooperativeKernel): grid-wide barriers become possible
+void launch_coop(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()> &body);
+void sync_grid();                    // called by ONE thread of every block
+static inline void *dyn_smem() { return blkp->smem; }
 
 static inline void sync_block() {
     Fiber *f = cur;
-    if (++blk.bar_arrived == blk.nlive) { blk.bar_arrived = 0; blk.bar_gen++; return; }
-    f->status = 1; f->bar_gen = blk.bar_gen;
+    Block &b = *blkp;
+    if (++b.bar_arrived == b.nlive) { b.bar_arrived = 0; b.bar_gen++; return; }
+    f->status = 1; f->bar_gen = b.bar_gen;
     yield_to_scheduler();
 }
 // Rendezvous of the lanes in `mask`; every lane contributes (v, p) and then sees all lanes' values.
 static inline WarpSlot &warp_exchange(unsigned mask, uint64_t v, int p) {
     Fiber *f = cur;
-    WarpSlot &w = blk.warps[f->warp];
+    WarpSlot &w = blkp->warps[f->warp];
     w.in[f->lane] = v; w.pin[f->lane] = p;
     w.arrived |= 1u << f->lane;
     if ((w.arrived & mask) == mask) {
@@ -137,9 +144,9 @@ static inline WarpSlot &warp_exchange(unsigned mask, uint64_t v, int p) {
 }  // namespace cusim
 
 #define threadIdx (cusim::cur->tid)
-#define blockIdx (cusim::blk.bid)
-#define blockDim (cusim::blk.bdim)
-#define gridDim (cusim::blk.gdim)
+#define blockIdx (cusim::blkp->bid)
+#define blockDim (cusim::blkp->bdim)
+#define gridDim (cusim::blkp->gdim)
 
 static inline void __syncthreads() { cusim::sync_block(); }
 static inline void __syncwarp(unsigned mask = 0xffffffffu) { cusim::warp_exchange(mask, 0, 0); }
@@ -198,3 +205,5 @@ template <class T> static inline T atomicCAS(T *p, T c, T v) { T o = *p; if (o =
 
 #define MRZ_LAUNCH(kernel, grid, block, stream, ...) \
     cusim::launch(dim3(grid), dim3(block), [=]() { kernel(__VA_ARGS__); })
+#define MRZ_LAUNCH_COOP(kernel, grid, block, smem, stream, ...) \
+    cusim::launch_coop(dim3(grid), dim3(block), (smem), [=]() { kernel(__VA_ARGS__); })
