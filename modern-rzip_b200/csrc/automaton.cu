@@ -38,8 +38,7 @@
 #define FULL 0xffffffffu
 #define AT 1024            // threads per CTA = ops per batch
 #define EQ_CAP 4096        // eligible-slot ring (power of two)
-#define WH_CAP 4096        // write-slot hash (power of two)
-#define WH_PROBES 128      // longer probe sequences mean the hash is overfull: the batch goes serial
+#define FWD_ITERS 6         // forwarding rounds per batch; later collisions go serial
 #define MAXWALK 16384      // longer insert walks are left to the serial path
 #define WLOG_CAP 64
 #define GRP 16             // slots per summary group
@@ -47,7 +46,10 @@
 #define CGRP_SHIFT 4       // conflict check: whole 16-slot groups inside a read range are tested as groups
 #define DUP_SALT 0x5bd1e9955bd1e995LL
 
-enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8, F_FOLLOW = 16 };
+enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8, F_FOLLOW = 16, F_W2ELIG = 32, F_W1ELIG = 64 };
+#define MAXDEP 3            // claimed slots a plan may walk past (forwarding)
+#define CLAIM_EPOCH_MAX 0x1FFFF0u
+__device__ __forceinline__ unsigned claim_key(unsigned epoch, int j, int is_w1) { return ((0x1FFFFFu - epoch) << 11) | ((unsigned)j << 1) | (unsigned)is_w1; }
 
 // Blocked Bloom filter over inserted tags: word index and 3-bit mask (oracle/spec_model.c filt_hash).
 #define FILT_BITS 24
@@ -402,13 +404,13 @@ struct Smem {
     int pre[AT];            // inclusive prefix over planned ops: misses << 22 | inserts << 11 | dcount sum
     int pl_fl[AT], pl_w2[AT];   // plan flags / insert slot of op j, for its twin
     int E[EQ_CAP];          // ring of eligible slots, ascending
-    int wh_key[WH_CAP];     // write hash: slot, or (1 << 30) | (slot >> 6) for the 64-slot group; -1 empty
-    int wh_val[WH_CAP];     //             smallest op index writing it
+    unsigned epoch;         // claim epoch (monotonic over the chunk; AutoState.pad1 between launches)
+    int changed[2];
     int wlog[WLOG_CAP];
     int wsum[40];
     unsigned e_idx, e_cnt;  // ring counters (monotonic)
     unsigned cutmask[AT / 32];
-    int nr, pos, k, nlog, jumped, ended, bmax, red, wh_over;
+    int nr, pos, k, nlog, jumped, ended, bmax, red;
 };
 
 #ifdef MRZ_CUSIM
@@ -455,55 +457,12 @@ __device__ __forceinline__ int block_min(int v, int *red) {
     return *red;
 }
 
-// ---- write hash: which earlier op of the batch writes a given slot / 64-slot group ------------------
-__device__ __forceinline__ unsigned wh_hash(int key) { return ((unsigned)key * 2654435761u) >> 20; }  // 12 bits
-
-__device__ __forceinline__ void wh_insert(Smem *S, int key, int j) {
-    unsigned h = wh_hash(key) & (WH_CAP - 1);
-    for (int n = 0; n < WH_PROBES; n++) {
-        int k = atomicCAS(&S->wh_key[h], -1, key);
-        if (k == -1 || k == key) { atomicMin(&S->wh_val[h], j); return; }
-        h = (h + 1) & (WH_CAP - 1);
-    }
-    S->wh_over = 1;
-}
-__device__ __forceinline__ void wh_insert_slot(Smem *S, int slot, int j) {
-    wh_insert(S, slot, j);
-    wh_insert(S, (1 << 30) | (slot >> CGRP_SHIFT), j);
-}
-__device__ __forceinline__ bool wh_hit(const Smem *S, int key, int before) {
-    unsigned h = wh_hash(key) & (WH_CAP - 1);
-    for (int n = 0; n < WH_PROBES; n++) {
-        int k = S->wh_key[h];
-        if (k == -1) return false;
-        if (k == key) return S->wh_val[h] < before;
-        h = (h + 1) & (WH_CAP - 1);
-    }
-    return true;
-}
-// true when some op with index < before writes a slot in [lo, hi].  Exact: the partial groups at either end
-// are tested slot by slot, the 16-slot groups lying wholly inside the range by their group key.
-__device__ __forceinline__ bool wh_range_hit(const Smem *S, int lo, int hi, int before) {
-    const int g_lo = (lo + (1 << CGRP_SHIFT) - 1) >> CGRP_SHIFT, g_hi = (hi + 1) >> CGRP_SHIFT;   // full groups: [g_lo, g_hi)
-    if (g_lo >= g_hi) {
-        for (int s = lo; s <= hi; s++)
-            if (wh_hit(S, s, before)) return true;
-        return false;
-    }
-    for (int s = lo; s < (g_lo << CGRP_SHIFT); s++)
-        if (wh_hit(S, s, before)) return true;
-    for (int g = g_lo; g < g_hi; g++)
-        if (wh_hit(S, (1 << 30) | g, before)) return true;
-    for (int s = g_hi << CGRP_SHIFT; s <= hi; s++)
-        if (wh_hit(S, s, before)) return true;
-    return false;
-}
-
 struct Plan {
     int flags, dcount;
-    int rd_lo, rd_hi, rd2_lo, rd2_hi;   // inclusive slot ranges read; rd2_lo < 0: none
     int w1_slot, w2_slot;               // displaced occupant's new home; where (tag, pos) goes
     i64 w1_off, w1_tag;
+    int ndep;                           // forwarding: slots this plan walked past because an EARLIER op of the batch
+    int dep_slot[MAXDEP], dep_own[MAXDEP];   // claims them with a tag that is no stop for this walk
 };
 
 // First slot s >= h with tz1(tags[s]) < need (an empty slot has tag 0, i.e. zero trailing ones), or -1 when
@@ -550,48 +509,42 @@ __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int 
 }
 
 __device__ __forceinline__ void plan_init(Plan &r) {
-    r.flags = 0; r.dcount = 0; r.rd_lo = 1; r.rd_hi = 0; r.rd2_lo = -1; r.rd2_hi = -1;
+    r.flags = 0; r.dcount = 0; r.ndep = 0;
     r.w1_slot = -1; r.w2_slot = -1; r.w1_off = 0; r.w1_tag = 0;
 }
 
 // Phase A: plan the insert of (tag) against the table without modifying anything (oracle/spec_model.c
-// plan_op).  The caller has established through the tag filter that no equal tag exists.
+// plan_op).  The caller has established through the tag filter that no equal tag exists.  The walk starts at
+// `start` (the tag's primary slot, or the slot after a claimed one when the plan is forwarded).
 __device__ __forceinline__ void plan_op(Plan &r, const i64 *ttag, const i64 *toff, u32 *gsum, const u64 *filt, i64 tag,
-                                        i64 hmask, i64 hsize, i64 min_mask, int chain, i64 w_lo, i64 w_hi) {
+                                        i64 start, i64 hmask, i64 hsize, i64 min_mask, int chain) {
     const i64 btm = (min_mask << 1) | 1;
     const int kb = __popcll((u64)btm);                 // entries with fewer trailing ones are due for sweeping
     const int myz = tz1(tag);
-    const i64 h0 = tag & hmask;
-    r.flags |= F_INSERT;
-    r.rd_lo = (int)h0;
+    r.flags = (r.flags & ~(F_W1 | F_W2ELIG | F_W1ELIG)) | F_INSERT;
     i64 st;
-    i64 s = find_stop(ttag, gsum, h0, myz > kb ? myz : kb, hsize, st);
+    i64 s = find_stop(ttag, gsum, start, myz > kb ? myz : kb, hsize, st);
     if (s < 0) { r.flags |= F_COMPLEX; return; }
-    r.w2_slot = (int)s; r.rd_hi = (int)s;
+    r.w2_slot = (int)s;
     if (st == 0) r.dcount = 1;                         // empty slot
-    else if ((st & btm) != btm) r.dcount = 0;          // rzip.c:267-269: overwrite an entry due for sweeping
+    else if ((st & btm) != btm) { r.dcount = 0; r.flags |= F_W2ELIG; }   // rzip.c:267-269: overwrite an entry due for sweeping
     else {
         // rzip.c:275-277: the occupant is lesser; where does it go when re-inserted?  Only planned when the
         // occupant's tag is unique in the table (no equal-tag chain to count) and nothing has to move further.
         if (chain == 1 || filt_query(filt, st ^ DUP_SALT)) { r.flags |= F_COMPLEX; return; }
         const int oz = tz1(st);
-        const i64 g0 = st & hmask;
         i64 st2;
-        i64 g = find_stop(ttag, gsum, g0, oz > kb ? oz : kb, hsize, st2);
+        i64 g = find_stop(ttag, gsum, st & hmask, oz > kb ? oz : kb, hsize, st2);
         if (g < 0) { r.flags |= F_COMPLEX; return; }
         int d2 = 0;
         if (st2 != 0) {
-            if ((st2 & btm) != btm) d2 = -1;
+            if ((st2 & btm) != btm) { d2 = -1; r.flags |= F_W1ELIG; }
             else { r.flags |= F_COMPLEX; return; }     // a second displacement: serial
         }
         r.flags |= F_W1;
-        r.rd2_lo = (int)g0; r.rd2_hi = (int)g;
         r.w1_slot = (int)g; r.w1_off = __ldcg(toff + s); r.w1_tag = st;
         r.dcount = 1 + d2;
     }
-    // anything touching the sweep window is left to the serial path
-    if (r.rd_hi >= w_lo && r.rd_lo < w_hi) r.flags |= F_COMPLEX;
-    if (r.rd2_lo >= 0 && r.rd2_hi >= w_lo && r.rd2_lo < w_hi) r.flags |= F_COMPLEX;
 }
 
 // "Twin" (oracle/spec_model.c plan_follower): position p+1 has the same tag as p and both insert.  B's
@@ -600,7 +553,7 @@ __device__ __forceinline__ void plan_op(Plan &r, const i64 *ttag, const i64 *tof
 // before the first overflow, overwrites A's entry when the tag itself is due for sweeping.
 __device__ __forceinline__ void plan_follower(Plan &r, const i64 *ttag, u32 *gsum, const u8 *buf, i64 pos, i64 tag,
                                               int a_flags, int a_w2, i64 hmask, i64 hsize, i64 min_mask, int chain, i64 end,
-                                              i64 last, i64 w_lo, i64 w_hi) {
+                                              i64 last) {
     if (a_flags & F_COMPLEX) { r.flags |= F_COMPLEX; return; }
     if (!(a_flags & F_INSERT)) return;                       // both lookup-only, nothing to find
     if ((a_flags & F_W1) || chain == 1) { r.flags |= F_COMPLEX; return; }
@@ -615,17 +568,16 @@ __device__ __forceinline__ void plan_follower(Plan &r, const i64 *ttag, u32 *gsu
     const int kb = __popcll((u64)btm);
     const int myz = tz1(tag);
     r.flags |= F_INSERT | F_FOLLOW;
-    r.rd_lo = (int)(tag & hmask);
     if ((tag & btm) != btm) {
-        r.w2_slot = a_w2; r.rd_hi = a_w2; r.dcount = 0;
+        r.w2_slot = a_w2; r.dcount = 0;
     } else {
         i64 st;
         i64 s = find_stop(ttag, gsum, (i64)a_w2 + 1, myz > kb ? myz : kb, hsize, st);
         if (s < 0) { r.flags |= F_COMPLEX; return; }
         if (st != 0 && (st & btm) == btm) { r.flags |= F_COMPLEX; return; }   // lesser occupant: displacement
-        r.w2_slot = (int)s; r.rd_hi = (int)s; r.dcount = st == 0 ? 1 : 0;
+        r.w2_slot = (int)s; r.dcount = st == 0 ? 1 : 0;
+        if (st != 0) r.flags |= F_W2ELIG;
     }
-    if (r.rd_hi >= w_lo && r.rd_lo < w_hi) r.flags |= F_COMPLEX;
 }
 
 // Refill the ring of eligible slots (those clean_one_from_hash will zero next, in order) by a
@@ -678,7 +630,7 @@ __device__ __forceinline__ void sync_queue(Smem *S, int nlog) {
 
 // Runs the automaton over the current segment's candidate list (or to the end of the chunk).
 __global__ void __launch_bounds__(AT, 1)
-k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum_global, const i64 *__restrict__ hidx,
+k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum_global, unsigned *claim, const i64 *__restrict__ hidx,
             AutoState *st, const i64 *__restrict__ tile_off, const u32 *__restrict__ cand_pos,
             const i64 *__restrict__ cand_tag, Token *toks, i64 *dbg) {
     if (st->done || st->error) return;
@@ -704,6 +656,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
         r.nops = st->n_ops; r.ntok = st->ntok; r.error = 0;
         S->e_idx = S->e_cnt = 0; S->e_scan = r.clean_ptr;
         S->li = 0; S->bmax = AT;
+        S->epoch = (unsigned)st->pad1; S->changed[0] = S->changed[1] = 0;
     }
     Warp w;   // used by warp 0 only
     w.buf = buf; w.ttag = ttag; w.toff = toff; w.filt = filt; w.gsum = S->gsum; w.toks = toks; w.lane = lane;
@@ -757,8 +710,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
         plan_init(pl);
         i64 my_pos = 0, my_tag = 0;
         bool follower = false;
-        for (int q = tid; q < WH_CAP; q += AT) { S->wh_key[q] = -1; S->wh_val[q] = 0x7fffffff; }
-        if (tid == 0) S->wh_over = 0;
+        int lead_w2 = -1;
         if (tid < nr) {
             const u32 rel = S->b_rel[tid];
             my_pos = seg_lo + (i64)rel; my_tag = S->b_tag[tid];
@@ -769,29 +721,88 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             if (!follower) {
                 if (filt_query(filt, my_tag)) pl.flags |= F_COMPLEX;          // an equal tag may exist
                 else if ((my_tag & ins_mask) == ins_mask)
-                    plan_op(pl, ttag, toff, S->gsum, filt, my_tag, hmask, hsize, min_mask, chain, w_lo, w_hi);
+                    plan_op(pl, ttag, toff, S->gsum, filt, my_tag, my_tag & hmask, hmask, hsize, min_mask, chain);
             }
             S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;
         }
         __syncthreads();
         if (follower) {
-            plan_follower(pl, ttag, S->gsum, buf, my_pos, my_tag, S->pl_fl[tid - 1], S->pl_w2[tid - 1], hmask, hsize, min_mask,
-                          chain, end, last_now, w_lo, w_hi);
-            S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;    // its leader looks at this when committing
+            lead_w2 = S->pl_w2[tid - 1];
+            plan_follower(pl, ttag, S->gsum, buf, my_pos, my_tag, S->pl_fl[tid - 1], lead_w2, hmask, hsize, min_mask,
+                          chain, end, last_now);
         }
         TICK(2);   // plan
+        // ---------------------------------------------------------------- conflicts: exact stop-slot claims with forwarding
+        // Every planned insert claims its stop slot(s) in claim[] (atomicMin of (epoch, op index)).  A plan whose stop slot
+        // is claimed by an EARLIER op either walks on from the next slot - when that op's tag is no stop for this walk,
+        // the claimed slot is remembered as a dependency - or gives up (F_CONF: serial).  Iterated to a fixed point.
         const bool planned_ins = tid < nr && (pl.flags & (F_COMPLEX | F_INSERT)) == F_INSERT;
-        if (planned_ins) {
-            wh_insert_slot(S, pl.w2_slot, tid);
-            if (pl.flags & F_W1) wh_insert_slot(S, pl.w1_slot, tid);
-        }
-        __syncthreads();
-        if (planned_ins) {   // a follower's plan builds on its leader's write: only older writes conflict
-            const int before = (pl.flags & F_FOLLOW) ? tid - 1 : tid;
-            if ((S->wh_over && tid > 0) || wh_range_hit(S, pl.rd_lo, pl.rd_hi, before) ||
-                (pl.rd2_lo >= 0 && wh_range_hit(S, pl.rd2_lo, pl.rd2_hi, tid)))
+        const int my_need = tz1(my_tag) > __popcll((u64)btm) ? tz1(my_tag) : __popcll((u64)btm);
+        for (int it = 0;; it++) {
+            if (S->epoch >= CLAIM_EPOCH_MAX) {   // claim keys exhausted: wipe the array, restart the epochs
+                __syncthreads();
+                for (i64 q = tid; q < hsize + 8; q += AT) claim[q] = 0xffffffffu;
+                __syncthreads();
+                if (tid == 0) S->epoch = 0;
+                __syncthreads();
+            }
+            const unsigned ep = S->epoch;
+            const unsigned ep_hi = claim_key(ep, 0, 0) >> 11;
+            bool live = planned_ins && !(pl.flags & (F_COMPLEX | F_CONF));
+            if (live && steady &&   // a stop slot that sits in the sweep queue: the order of sweeps and inserts matters
+                (((pl.flags & F_W2ELIG) && pl.w2_slot >= w_lo && pl.w2_slot < w_hi) ||
+                 ((pl.flags & F_W1ELIG) && pl.w1_slot >= w_lo && pl.w1_slot < w_hi))) {
                 pl.flags |= F_CONF;
+                live = false;
+            }
+            if (live) {
+                atomicMin(claim + pl.w2_slot, claim_key(ep, tid, 0));
+                if (pl.flags & F_W1) atomicMin(claim + pl.w1_slot, claim_key(ep, tid, 1));
+            }
+            __threadfence_block();
+            __syncthreads();
+            if (tid == 0) { S->epoch = ep + 1; S->changed[(it + 1) & 1] = 0; }
+            bool chg = false;
+            if (planned_ins && !live && it == 0) chg = false;
+            if (live) {
+                bool bad = false;
+                // a follower's plan builds on its leader's write: only older claims conflict, and the leader must not have moved
+                const int before = (pl.flags & F_FOLLOW) ? tid - 1 : tid;
+                if ((pl.flags & F_FOLLOW) && S->pl_w2[tid - 1] != lead_w2) bad = true;
+                for (int d = 0; d < pl.ndep && !bad; d++) {   // slots I walked past on the strength of an earlier op's claim
+                    const unsigned o = __ldcg(claim + pl.dep_slot[d]);
+                    const int oi = (int)((o >> 1) & 1023u);
+                    if ((o >> 11) != ep_hi || (o & 1u) || oi >= tid) { bad = true; break; }
+                    const i64 ot = S->b_tag[oi];
+                    if (tz1(ot) < my_need || (ot & btm) != btm || ot == my_tag) { bad = true; break; }
+                    pl.dep_own[d] = oi;
+                }
+                if (!bad) {
+                    const unsigned o = __ldcg(claim + pl.w2_slot);
+                    const int oi = (int)((o >> 1) & 1023u);
+                    if (oi < before) {   // my stop slot goes to an earlier op
+                        const i64 ot = S->b_tag[oi];
+                        if ((pl.flags & F_FOLLOW) || (o & 1u) || pl.ndep == MAXDEP || it >= FWD_ITERS || tz1(ot) < my_need ||
+                            (ot & btm) != btm || ot == my_tag)   // an equal tag: my lookup must meet its entry (serial)
+                            bad = true;
+                        else {           // its tag is no stop for my walk: go on from the next slot
+                            pl.dep_slot[pl.ndep] = pl.w2_slot; pl.dep_own[pl.ndep] = oi; pl.ndep++;
+                            plan_op(pl, ttag, toff, S->gsum, filt, my_tag, (i64)pl.w2_slot + 1, hmask, hsize, min_mask, chain);
+                            S->pl_w2[tid] = pl.w2_slot;
+                            chg = true;
+                            if (dbg) atomicAdd((unsigned long long *)&dbg[16], 1ULL);
+                        }
+                    } else if ((pl.flags & F_W1) && (int)((__ldcg(claim + pl.w1_slot) >> 1) & 1023u) < tid)
+                        bad = true;
+                }
+                if (bad) { pl.flags |= F_CONF; chg = true; }
+                if (chg) S->pl_fl[tid] = pl.flags;
+            }
+            if (chg) S->changed[it & 1] = 1;
+            __syncthreads();
+            if (!S->changed[it & 1]) break;
         }
+        if (tid < nr) { S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot; }
         {   // inclusive prefix over ops that still hold a valid plan: misses << 22 | inserts << 11 | dcount sum
             int v = 0;
             if (tid < nr && (pl.flags & (F_COMPLEX | F_CONF | F_INSERT)) == F_INSERT)
@@ -955,13 +966,17 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             if (steady && S->e_scan < w_hi) refill_queue(S, ttag, w_hi, EQ_CAP);
             // later plans that read a slot this op wrote are no longer valid; nor is its twin's plan
             if (tid == k + 1 && (pl.flags & F_FOLLOW)) pl.flags |= F_CONF;
+            if (tid > k && tid < nr)   // a plan forwarded over op k's claim assumed k's planned write
+                for (int d = 0; d < pl.ndep; d++)
+                    if (pl.dep_own[d] == k) pl.flags |= F_CONF;
             if (tid > k && tid < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
                 const int nl = S->nlog;
                 for (int q = 0; q < nl; q++) {
                     int sl = S->wlog[q] >> 1;
-                    if ((sl >= pl.rd_lo && sl <= pl.rd_hi) || (pl.rd2_lo >= 0 && sl >= pl.rd2_lo && sl <= pl.rd2_hi)) {
+                    bool hit = sl == pl.w2_slot || ((pl.flags & F_W1) && sl == pl.w1_slot);
+                    for (int d = 0; d < pl.ndep; d++) hit = hit || sl == pl.dep_slot[d];
+                    if (hit) {
                         pl.flags |= F_CONF;
-                        if (dbg) atomicAdd((unsigned long long *)&dbg[16], 1ULL);
                         break;
                     }
                 }
@@ -994,16 +1009,17 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
         st->n_ops = r.nops; st->ntok = r.ntok;
         if (r.error) st->error = r.error;
         if (p >= end) st->done = 1;
+        st->pad1 = (int)S->epoch;
     }
 }
 
-extern "C" void mrz_launch_automaton(const u8 *buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum, const i64 *hidx, AutoState *st,
+extern "C" void mrz_launch_automaton(const u8 *buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum, unsigned *claim, const i64 *hidx, AutoState *st,
                                      const i64 *tile_off, const u32 *cand_pos, const i64 *cand_tag, Token *toks, i64 *dbg,
                                      cudaStream_t s) {
 #ifndef MRZ_CUSIM
     cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, ttag, toff, filt, gsum, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
+    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, ttag, toff, filt, gsum, claim, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
 #else
-    MRZ_LAUNCH(k_automaton, 1, AT, s, buf, ttag, toff, filt, gsum, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
+    MRZ_LAUNCH(k_automaton, 1, AT, s, buf, ttag, toff, filt, gsum, claim, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
 #endif
 }

@@ -15,7 +15,7 @@
 extern "C" {
 void mrz_launch_scan(const u8 *, const i64 *, AutoState *, int *, i64 *, u32 *, i64 *, int, cudaStream_t);
 void mrz_launch_debug_tags(const u8 *, const i64 *, i64, i64, i64 *, cudaStream_t);
-void mrz_launch_automaton(const u8 *, i64 *, i64 *, u64 *, u32 *, const i64 *, AutoState *, const i64 *, const u32 *,
+void mrz_launch_automaton(const u8 *, i64 *, i64 *, u64 *, u32 *, unsigned *, const i64 *, AutoState *, const i64 *, const u32 *,
                           const i64 *, Token *, i64 *, cudaStream_t);
 size_t mrz_grid_state_bytes();
 int mrz_launch_automaton_grid(int, int, const u8 *, i64 *, i64 *, u64 *, u32 *, unsigned *, void *, const i64 *, AutoState *,
@@ -327,10 +327,8 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaMemsetAsync(ctx->d_tab, 0, (size_t)(ctx->tab_slots + 32) * 16, s));  // rzip.c:518-519
     CK(cudaMemsetAsync(ctx->d_gsum, 0, (size_t)(ctx->tab_slots / 16 / 8) * 4, s));
     CK(cudaMemsetAsync(ctx->d_filt, 0, (size_t)MRZ_FILT_WORDS * 8, s));
-    if (ctx->grid_g) {
-        CK(cudaMemsetAsync(ctx->d_claim, 0xff, (size_t)(ctx->tab_slots + 32) * 4, s));
-        CK(cudaMemsetAsync(ctx->d_gstate, 0, mrz_grid_state_bytes(), s));
-    }
+    CK(cudaMemsetAsync(ctx->d_claim, 0xff, (size_t)(ctx->tab_slots + 32) * 4, s));
+    if (ctx->grid_g) CK(cudaMemsetAsync(ctx->d_gstate, 0, mrz_grid_state_bytes(), s));
     CK(cudaMemsetAsync(ctx->d_tot, 0, sizeof(EmitTotals), s));
     if (ctx->d_dbg) CK(cudaMemsetAsync(ctx->d_dbg, 0, 20 * 8, s));
     launches += 2;
@@ -355,7 +353,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
                                                 ctx->d_tile_off, ctx->d_cand_pos, ctx->d_cand_tag, ctx->d_toks, ctx->d_dbg, s);
             if (lrc) CK((cudaError_t)lrc);
         } else
-            mrz_launch_automaton(ctx->d_buf, ctx->d_tab, ctx->d_tab + ctx->tab_slots + 32, ctx->d_filt, ctx->d_gsum, ctx->d_hidx, ctx->d_st,
+            mrz_launch_automaton(ctx->d_buf, ctx->d_tab, ctx->d_tab + ctx->tab_slots + 32, ctx->d_filt, ctx->d_gsum, ctx->d_claim, ctx->d_hidx, ctx->d_st,
                                  ctx->d_tile_off, ctx->d_cand_pos, ctx->d_cand_tag, ctx->d_toks, ctx->d_dbg, s);
         CK(cudaEventRecord(ctx->ev[3], s));
         launches += 4;
