@@ -38,6 +38,8 @@
 #define FULL 0xffffffffu
 #define AT 1024            // threads per CTA = ops per batch
 #define EQ_CAP 4096        // eligible-slot ring (power of two)
+#define LK_XCAP 2048       // a candidate still matching after this many bytes is extended by the whole CTA
+#define LK_CAP 256         // equal-tag entries the CTA-wide lookup collects; more: the warp walk
 #define FWD_ITERS 6         // forwarding rounds per batch; later collisions go serial
 #define MAXWALK 16384      // longer insert walks are left to the serial path
 #define WLOG_CAP 64
@@ -121,6 +123,7 @@ struct Warp {
     int *wlog;
     int nlog;
     i64 clean_hint;   // no eligible slot exists in [clean_ptr, clean_hint)
+    i64 *prof;        // MRZ_PROFILE: cycles / calls of the parts of a serial op (dbg[20..])
 
     __device__ __forceinline__ void load(const Run &r) {
         p = r.p; last = r.last; cur_p = r.cur_p; cur_len = r.cur_len; cur_ofs = r.cur_ofs;
@@ -149,73 +152,108 @@ struct Warp {
     }
 
     // rzip.c:372-397.  Returns total length (0 if < 31) and the backward part in rev.
+    // The first step compares 256 bytes (most candidates fail there); a match that survives it is extended 4 KiB per
+    // step - 16 independent 8-byte compares per lane in flight - so that long matches run at memory speed, not at
+    // one dependent round trip per 256 bytes.
+    __device__ __forceinline__ i64 extend(i64 a0, i64 b0, i64 maxlen, bool fwd) {
+        // fwd: longest common prefix of buf[a0..] and buf[b0..]; else longest common suffix of buf[..a0) and buf[..b0)
+        i64 f = 0;
+        int K = 1;
+        while (f < maxlen) {
+            int first = 0x7fffffff;            // (chunk index << 3 | byte) of my first mismatch in this step
+            for (int c = K - 1; c >= 0; c--) {
+                const i64 k = f + (i64)(c * 32 + lane) * 8;
+                u64 x = 0;
+                if (k < maxlen) x = fwd ? ld_u64_unaligned(buf, a0 + k) ^ ld_u64_unaligned(buf, b0 + k)
+                                        : ld_u64_unaligned(buf, a0 - 8 - k) ^ ld_u64_unaligned(buf, b0 - 8 - k);
+                if (x) {
+                    const int nb = fwd ? ((__ffsll((long long)x) - 1) >> 3) : (__clzll((long long)x) >> 3);
+                    first = ((c * 32 + lane) << 3) | nb;
+                }
+            }
+            for (int o = 16; o; o >>= 1) {
+                const int u = __shfl_xor_sync(FULL, first, o);
+                first = u < first ? u : first;
+            }
+            if (first != 0x7fffffff) {
+                f += (i64)(first >> 3) * 8 + (first & 7);
+                break;
+            }
+            f += (i64)K * 256;
+            K = 16;
+        }
+        return f > maxlen ? maxlen : f;
+    }
     __device__ __forceinline__ i64 match_len(i64 p0, i64 op, i64 &rev) {
         rev = 0;
         if (op >= p0) return 0;
-        i64 maxf = end - p0, f = 0;
-        while (f < maxf) {
-            i64 k = f + lane * 8;
-            u64 x = 0;
-            if (k < maxf) x = ld_u64_unaligned(buf, p0 + k) ^ ld_u64_unaligned(buf, op + k);
-            unsigned mm = __ballot_sync(FULL, x != 0);
-            if (mm) {
-                int l = __ffs(mm) - 1;
-                int nb = x ? ((__ffsll((long long)x) - 1) >> 3) : 8;
-                nb = __shfl_sync(FULL, nb, l);
-                f += l * 8 + nb;
-                break;
-            }
-            f += 256;
-        }
-        if (f > maxf) f = maxf;
-        i64 lo = last > 0 ? last : 0;
+        const i64 f = extend(p0, op, end - p0, true);
+        const i64 lo = last > 0 ? last : 0;
         i64 maxb = p0 - lo;
         if (op < maxb) maxb = op;
-        i64 r = 0;
-        while (r < maxb) {
-            i64 k = r + lane * 8;
-            u64 x = 0;
-            if (k < maxb) x = ld_u64_unaligned(buf, p0 - 8 - k) ^ ld_u64_unaligned(buf, op - 8 - k);
-            unsigned mm = __ballot_sync(FULL, x != 0);
-            if (mm) {
-                int l = __ffs(mm) - 1;
-                int nb = x ? (__clzll((long long)x) >> 3) : 8;
-                nb = __shfl_sync(FULL, nb, l);
-                r += l * 8 + nb;
-                break;
-            }
-            r += 256;
-        }
-        if (r > maxb) r = maxb;
+        const i64 r = extend(p0, op, maxb, false);
         rev = r;
-        i64 tot = f + r;
+        const i64 tot = f + r;
         return tot < MRZ_MIN_MATCH ? 0 : tot;
     }
 
-    // rzip.c:426-462
+    // rzip.c:426-462.  128 slots per step: every lane examines four consecutive slots.
     __device__ __forceinline__ i64 lookup(i64 t, i64 pp, i64 &bofs, i64 &brev) {
         i64 best = 0;
         i64 h = t & hmask;
         for (;;) {
-            i64 et = __ldcg(ttag + ((h + lane) & hmask));
-            unsigned em = __ballot_sync(FULL, et == 0);
-            int fe = em ? (__ffs(em) - 1) : 32;
-            unsigned eq = __ballot_sync(FULL, et == t);
-            if (fe < 32) eq &= (1u << fe) - 1u;
-            while (eq) {
-                int l = __ffs(eq) - 1;
-                eq &= eq - 1;
-                i64 off = __ldcg(toff + ((h + l) & hmask));
+            i64 et[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) et[q] = __ldcg(ttag + ((h + lane * 4 + q) & hmask));
+            unsigned em4 = 0, eq4 = 0;
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                if (et[q] == 0) em4 |= 1u << q;
+                if (et[q] == t) eq4 |= 1u << q;
+            }
+            const unsigned eml = __ballot_sync(FULL, em4 != 0);
+            int fe = 128;                       // position of the first empty slot in this window
+            if (eml) {
+                const int l = __ffs(eml) - 1;
+                const unsigned m = __shfl_sync(FULL, em4, l);
+                fe = l * 4 + (__ffs(m) - 1);
+            }
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                if (lane * 4 + q >= fe) eq4 &= ~(1u << q);
+            for (;;) {                          // equal tags before the first empty slot, in slot order
+                const unsigned ql = __ballot_sync(FULL, eq4 != 0);
+                if (!ql) break;
+                const int l = __ffs(ql) - 1;
+                const unsigned m = __shfl_sync(FULL, eq4, l);
+                const int q = __ffs(m) - 1;
+                if (lane == l) eq4 &= eq4 - 1;
+                i64 off = __ldcg(toff + ((h + l * 4 + q) & hmask));
                 i64 rev;
-                i64 m = match_len(pp, off, rev);
-                if (m) {
+                i64 mlen = match_len(pp, off, rev);
+                if (mlen) {
                     hits++;
-                    if (m > best) { best = m; bofs = off - rev; brev = rev; }
+                    if (mlen > best) { best = mlen; bofs = off - rev; brev = rev; }
                 } else
                     misses++;
             }
-            if (fe < 32) break;
-            h = (h + 32) & hmask;
+            if (fe < 128) break;
+            h = (h + 128) & hmask;
+        }
+        return best;
+    }
+
+    // The selection half of find_best_match (rzip.c:445-456) over candidates the CTA has already compared
+    // (k_automaton: every warp ran match_len for a share of the equal-tag slots; results in slot order).
+    __device__ __forceinline__ i64 lookup_pre(i64 &bofs, i64 &brev, int n, const i64 *len, const i64 *rv, const i64 *off) {
+        i64 best = 0;
+        for (int q = 0; q < n; q++) {
+            const i64 m = len[q];
+            if (m) {
+                hits++;
+                if (m > best) { best = m; bofs = off[q] - rv[q]; brev = rv[q]; }
+            } else
+                misses++;
         }
         return best;
     }
@@ -286,6 +324,40 @@ struct Warp {
         }
     }
 
+    // rzip.c:256-301 for a tag that has no equal entry in the table: every level of the displacement chain is a
+    // summary-accelerated find_stop walk (all walks see the table before any write, as the reference's recursion does).
+    // Returns false, having written nothing, when some level needs the general walk of insert().
+    __device__ __forceinline__ bool insert_fast(i64 t, i64 off, i64 *stk) {
+        const i64 btm = (min_mask << 1) | 1;
+        const int kb = __popcll((u64)btm);
+        int sp = 0;
+        i64 ct = t, coff = off;
+        for (;;) {
+            const int z = tz1(ct);
+            i64 stg;
+            const i64 sl = find_stop(ttag, gsum, ct & hmask, z > kb ? z : kb, hsize, stg);
+            if (sl < 0) return false;
+            if (stg == 0 || (stg & btm) != btm) {
+                __syncwarp();                          // every lane has read the table before lane 0 writes it
+                if (stg != 0) count--;                 // rzip.c:267-269
+                write_slot(sl, coff, ct);
+                while (sp > 0) {
+                    sp--;
+                    write_slot(stk[3 * sp], stk[3 * sp + 2], stk[3 * sp + 1]);
+                }
+                return true;
+            }
+            // rzip.c:275-277: a lesser occupant is re-inserted first; it must be unique (it meets only itself on its walk)
+            if (chain == 1 || sp >= 60 || filt_query(filt, stg ^ DUP_SALT)) return false;
+            __syncwarp();
+            if (lane == 0) { stk[3 * sp] = sl; stk[3 * sp + 1] = ct; stk[3 * sp + 2] = coff; }
+            __syncwarp();
+            sp++;
+            coff = __ldcg(toff + sl);
+            ct = stg;
+        }
+    }
+
     // rzip.c:305-328
     __device__ __forceinline__ void clean_one() {
         if (clean_ptr < clean_hint) clean_ptr = clean_hint;   // nothing eligible before the hint
@@ -316,34 +388,33 @@ struct Warp {
 
     // One position that passed the lookup gate (rzip.c:573-599).  Returns true when a match was
     // emitted (p jumped to last_match).
-    __device__ __forceinline__ bool op(i64 pp, i64 t, i64 *stk) {
+    // pre_n >= 0: the CTA has already walked the probe sequence and compared the pre_n equal-tag candidates
+    __device__ __noinline__ bool op(i64 pp, i64 t, i64 *stk, int pre_n = -1, const i64 *pre_len = nullptr, const i64 *pre_rev = nullptr,
+                                    const i64 *pre_off = nullptr) {
+#define PROF(slot, t0) do { if (prof && lane == 0) { prof[slot] += clock64() - (t0); prof[(slot) + 1] += 1; } } while (0)
         nops++;
         i64 bofs = 0, brev = 0;
+        i64 c0 = clock64();
         const bool maybe = filt_query(filt, t);                       // negative: nothing to find
-        i64 best = maybe ? lookup(t, pp, bofs, brev) : 0;
+        PROF(0, c0); c0 = clock64();
+        i64 best = 0;
+        if (maybe) best = pre_n >= 0 ? lookup_pre(bofs, brev, pre_n, pre_len, pre_rev, pre_off) : lookup(t, pp, bofs, brev);
+        if (maybe) PROF(2, c0);
         if ((t & ins_mask) == ins_mask) {
             inserts++;
             count++;
             bool placed = false;
-            if (!maybe) {   // no equal tag exists: the insert slot is the first empty / due-for-sweep / lesser entry
-                const i64 btm = (min_mask << 1) | 1;
-                const int kb = __popcll((u64)btm), myz = tz1(t);
-                i64 stg;
-                i64 sl = find_stop(ttag, gsum, t & hmask, myz > kb ? myz : kb, hsize, stg);
-                __syncwarp();                          // every lane has read the table before lane 0 writes it
-                if (sl >= 0 && (stg == 0 || (stg & btm) != btm)) {
-                    if (stg != 0) count--;             // rzip.c:267-269
-                    write_slot(sl, pp, t);
-                    placed = true;
-                }
-            }
-            if (!placed) insert(t, pp, stk);
+            c0 = clock64();
+            if (!maybe) { placed = insert_fast(t, pp, stk); PROF(4, c0); }   // no equal tag exists
+            c0 = clock64();
+            if (!placed) { insert(t, pp, stk); PROF(6, c0); }
             if (lane == 0) {
                 filt_set(filt, t);
                 if (maybe) filt_set(filt, t ^ DUP_SALT);              // this tag may now be in the table twice
             }
             __syncwarp();
-            if (count > limit) clean_one();
+            c0 = clock64();
+            if (count > limit) { clean_one(); PROF(8, c0); }
         }
         if (best > cur_len) { cur_p = pp - brev; cur_len = best; cur_ofs = bofs; }
         if ((cur_len >= MRZ_GREAT_MATCH || pp >= cur_p + MRZ_MIN_MATCH) && cur_len >= MRZ_MIN_MATCH) {
@@ -404,6 +475,10 @@ struct Smem {
     int pre[AT];            // inclusive prefix over planned ops: misses << 22 | inserts << 11 | dcount sum
     int pl_fl[AT], pl_w2[AT];   // plan flags / insert slot of op j, for its twin
     int E[EQ_CAP];          // ring of eligible slots, ascending
+    int lk_fe, lk_n;        // CTA-wide lookup: first empty position, equal-tag count
+    int lk_pos[LK_CAP];     //                  positions (relative to the primary slot) of equal tags, ascending
+    i64 lk_len[LK_CAP], lk_rev[LK_CAP], lk_off[LK_CAP];   // match_len results per candidate
+    i64 lk_f[LK_CAP], lk_r[LK_CAP];                       // capped forward / backward lengths (first pass)
     unsigned epoch;         // claim epoch (monotonic over the chunk; AutoState.pad1 between launches)
     int changed[2];
     int wlog[WLOG_CAP];
@@ -628,6 +703,36 @@ __device__ __forceinline__ void sync_queue(Smem *S, int nlog) {
     }
 }
 
+// Match extension by the whole CTA: longest common prefix of buf[a0..] / buf[b0..] (fwd) or longest common suffix of
+// buf[..a0) / buf[..b0), at most maxlen bytes; 32 KiB per step, four independent 8-byte compares per thread in flight.
+__device__ __forceinline__ i64 cta_extend(Smem *S, const u8 *buf, i64 a0, i64 b0, i64 maxlen, bool fwd) {
+    const int tid = threadIdx.x;
+    i64 f = 0;
+    while (f < maxlen) {
+        if (tid == 0) S->lk_fe = 0x7fffffff;
+        __syncthreads();
+        int first = 0x7fffffff;
+        for (int c = 3; c >= 0; c--) {
+            const int ci = c * AT + tid;
+            const i64 k = f + (i64)ci * 8;
+            u64 x = 0;
+            if (k < maxlen) x = fwd ? ld_u64_unaligned(buf, a0 + k) ^ ld_u64_unaligned(buf, b0 + k)
+                                    : ld_u64_unaligned(buf, a0 - 8 - k) ^ ld_u64_unaligned(buf, b0 - 8 - k);
+            if (x) first = (ci << 3) | (fwd ? ((__ffsll((long long)x) - 1) >> 3) : (__clzll((long long)x) >> 3));
+        }
+        if (first != 0x7fffffff) atomicMin(&S->lk_fe, first);
+        __syncthreads();
+        const int r = S->lk_fe;
+        __syncthreads();
+        if (r != 0x7fffffff) {
+            f += (i64)(r >> 3) * 8 + (r & 7);
+            break;
+        }
+        f += (i64)4 * AT * 8;
+    }
+    return f > maxlen ? maxlen : f;
+}
+
 // Runs the automaton over the current segment's candidate list (or to the end of the chunk).
 __global__ void __launch_bounds__(AT, 1)
 k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum_global, unsigned *claim, const i64 *__restrict__ hidx,
@@ -661,7 +766,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
     Warp w;   // used by warp 0 only
     w.buf = buf; w.ttag = ttag; w.toff = toff; w.filt = filt; w.gsum = S->gsum; w.toks = toks; w.lane = lane;
     w.n = n; w.end = end; w.hmask = hmask; w.hsize = hsize; w.limit = limit; w.tok_cap = st->tok_cap; w.chain = chain;
-    w.wlog = S->wlog; w.nlog = 0; w.clean_hint = 0;
+    w.wlog = S->wlog; w.nlog = 0; w.clean_hint = 0; w.prof = dbg ? dbg + 20 : nullptr;
     __syncthreads();
 
     for (;;) {
@@ -711,6 +816,8 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
         i64 my_pos = 0, my_tag = 0;
         bool follower = false;
         int lead_w2 = -1;
+        const i64 t_plan0 = clock64();
+        if (dbg && tid == 0) S->red = 0;
         if (tid < nr) {
             const u32 rel = S->b_rel[tid];
             my_pos = seg_lo + (i64)rel; my_tag = S->b_tag[tid];
@@ -724,8 +831,14 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                     plan_op(pl, ttag, toff, S->gsum, filt, my_tag, my_tag & hmask, hmask, hsize, min_mask, chain);
             }
             S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;
+            if (dbg) {   // per-op plan latency: mean and per-batch maximum (the barrier waits for the slowest walk)
+                const i64 dt = clock64() - t_plan0;
+                atomicAdd((unsigned long long *)&dbg[17], (unsigned long long)dt);
+                atomicMax(&S->red, (int)dt);
+            }
         }
         __syncthreads();
+        if (dbg && tid == 0) dbg[18] += S->red;
         if (follower) {
             lead_w2 = S->pl_w2[tid - 1];
             plan_follower(pl, ttag, S->gsum, buf, my_pos, my_tag, S->pl_fl[tid - 1], lead_w2, hmask, hsize, min_mask,
@@ -889,9 +1002,78 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             if (tid == k) {   // why is this op serial?
                 int why = (pl.flags & F_COMPLEX) ? (follower ? 12 : ((pl.flags & F_INSERT) ? 13 : 11)) : (pl.flags & F_CONF) ? 14 : 15;
                 if (dbg) atomicAdd((unsigned long long *)&dbg[why], 1ULL);
-                if (dbg && why == 15) {
-                    int sub = (cur_len >= MRZ_MIN_MATCH && my_pos >= cur_p + MRZ_MIN_MATCH) ? 17 : (!steady ? 18 : 19);
-                    atomicAdd((unsigned long long *)&dbg[sub], 1ULL);
+            }
+            // ---- the lookup of op k (find_best_match, rzip.c:426-462) by the whole CTA: the probe sequence is walked
+            // 4096 slots per step, equal tags are collected in slot order, and the 32 warps share the match_len calls
+            int pre_n = -1;
+            {
+                const i64 tk = S->b_tag[k], pk = seg_lo + (i64)S->b_rel[k];
+                if (filt_query(filt, tk)) {
+                    const i64 h = tk & hmask;
+                    if (tid == 0) S->lk_fe = 0x7fffffff;
+                    __syncthreads();
+                    int n_tot = 0;
+                    bool found = false;
+                    for (int base = 0;; base += AT * 4) {
+                        i64 et[4];
+#pragma unroll
+                        for (int q = 0; q < 4; q++) et[q] = __ldcg(ttag + ((h + base + tid * 4 + q) & hmask));
+                        unsigned eq4 = 0;
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            if (et[q] == 0) atomicMin(&S->lk_fe, base + tid * 4 + q);
+                            else if (et[q] == tk) eq4 |= 1u << q;
+                        }
+                        __syncthreads();
+                        const int fe = S->lk_fe;
+#pragma unroll
+                        for (int q = 0; q < 4; q++)
+                            if (base + tid * 4 + q >= fe) eq4 &= ~(1u << q);   // beyond the first empty slot: not on the walk
+                        int total;
+                        int ex = block_excl_scan(__popc(eq4), S->wsum, total);
+                        for (int q = 0; q < 4; q++)
+                            if ((eq4 >> q) & 1u) {
+                                if (n_tot + ex < LK_CAP) S->lk_pos[n_tot + ex] = base + tid * 4 + q;
+                                ex++;
+                            }
+                        n_tot += total;
+                        found = fe != 0x7fffffff;
+                        if (found || n_tot > LK_CAP || base + AT * 4 >= hsize) break;
+                    }
+                    __syncthreads();
+                    if (found && n_tot <= LK_CAP) {
+                        // single_match_len (rzip.c:372-397) per candidate: the warps share the candidates for the first
+                        // LK_XCAP bytes either side; whatever still matches there is extended by the whole CTA, 32 KiB per step
+                        w.last = S->run.last;
+                        const i64 lo = w.last > 0 ? w.last : 0;
+                        const i64 maxf = end - pk;
+                        for (int q = wid; q < n_tot; q += AT / 32) {
+                            const i64 off = __ldcg(toff + ((h + S->lk_pos[q]) & hmask));
+                            i64 f = 0, r = 0;
+                            if (off < pk) {
+                                i64 maxb = pk - lo;
+                                if (off < maxb) maxb = off;
+                                f = w.extend(pk, off, maxf < LK_XCAP ? maxf : LK_XCAP, true);
+                                r = w.extend(pk, off, maxb < LK_XCAP ? maxb : LK_XCAP, false);
+                            }
+                            if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; S->lk_off[q] = off; }
+                        }
+                        __syncthreads();
+                        for (int q = 0; q < n_tot; q++) {
+                            const i64 off = S->lk_off[q];
+                            i64 f = S->lk_f[q], r = S->lk_r[q], m = 0;
+                            if (off < pk) {
+                                i64 maxb = pk - lo;
+                                if (off < maxb) maxb = off;
+                                if (f == LK_XCAP && maxf > LK_XCAP) f += cta_extend(S, buf, pk + LK_XCAP, off + LK_XCAP, maxf - LK_XCAP, true);
+                                if (r == LK_XCAP && maxb > LK_XCAP) r += cta_extend(S, buf, pk - LK_XCAP, off - LK_XCAP, maxb - LK_XCAP, false);
+                                m = f + r < MRZ_MIN_MATCH ? 0 : f + r;
+                            }
+                            if (tid == 0) { S->lk_len[q] = m; S->lk_rev[q] = r; }
+                        }
+                        __syncthreads();
+                        pre_n = n_tot;
+                    }
                 }
             }
             // ---- op k on the live table, reference semantics (warp 0)
@@ -903,8 +1085,9 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                 w.clean_hint = hint;
                 const i64 pk = seg_lo + (i64)S->b_rel[k], tk = S->b_tag[k];
                 w.p = pk;
-                bool jumped = w.op(pk, tk, S->stk);
+                bool jumped = w.op(pk, tk, S->stk, pre_n, S->lk_len, S->lk_rev, S->lk_off);
                 w.clean_hint = 0;
+                const i64 c_dense = clock64();
                 if (jumped && !w.error) {
                     // dense-match regime: examine the next positions directly from the bytes until a
                     // window of 32 positions passes without an emission, then re-synchronise with the list
@@ -941,6 +1124,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                         nli = list_seek(cand_pos, tile_off[tile], tile_off[tile + 1], (u32)rel, lane);
                     }
                     if (lane == 0) S->li = nli;
+                    if (dbg && lane == 0) { dbg[30] += clock64() - c_dense; dbg[31] += 1; }
                 }
                 w.store(S->run);
                 if (lane == 0) {

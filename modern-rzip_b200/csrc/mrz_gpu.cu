@@ -53,7 +53,7 @@ struct mrz_ctx {
     i64 *d_a0, *d_a1, *d_off0, *d_off1, *d_bsum; i64 item_cap;
     EmitTotals *d_tot;
     i64 *d_dbg;          // phase cycle counters of k_automaton (MRZ_PROFILE=1), else NULL
-    i64 h_dbg[20];
+    i64 h_dbg[40];
     u8 *d_s0; i64 s0_cap; u8 *d_s1; i64 s1_cap;
     u32 *d_crc_part, *d_crc_part2, *d_crc_misc;  // misc[0]=tail, misc[1]=final
     // host staging
@@ -253,7 +253,7 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     CK(cudaMalloc(&ctx->d_cand_pos, (size_t)(SEG_CAND_CAP + 64) * sizeof(u32)));
     CK(cudaMalloc(&ctx->d_cand_tag, (size_t)(SEG_CAND_CAP + 64) * sizeof(i64)));
     CK(cudaMalloc(&ctx->d_tot, sizeof(EmitTotals)));
-    if (getenv("MRZ_PROFILE")) CK(cudaMalloc(&ctx->d_dbg, 20 * 8));
+    if (getenv("MRZ_PROFILE")) CK(cudaMalloc(&ctx->d_dbg, 40 * 8));
     CK(cudaMalloc(&ctx->d_s1, (size_t)max_chunk + 64));
     ctx->s1_cap = max_chunk + 64;
     i64 nblk = max_chunk / 16384 + 1;
@@ -330,7 +330,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaMemsetAsync(ctx->d_claim, 0xff, (size_t)(ctx->tab_slots + 32) * 4, s));
     if (ctx->grid_g) CK(cudaMemsetAsync(ctx->d_gstate, 0, mrz_grid_state_bytes(), s));
     CK(cudaMemsetAsync(ctx->d_tot, 0, sizeof(EmitTotals), s));
-    if (ctx->d_dbg) CK(cudaMemsetAsync(ctx->d_dbg, 0, 20 * 8, s));
+    if (ctx->d_dbg) CK(cudaMemsetAsync(ctx->d_dbg, 0, 40 * 8, s));
     launches += 2;
     // CRC of the chunk (independent of the automaton)
     mrz_launch_crc(ctx->d_buf, n, ctx->d_crc_part, ctx->d_crc_part2, ctx->d_crc_misc, s, &launches);
@@ -380,15 +380,19 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     }
 
     if (ctx->d_dbg) {
-        CK(cudaMemcpyAsync(ctx->h_dbg, ctx->d_dbg, 20 * 8, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(ctx->h_dbg, ctx->d_dbg, 40 * 8, cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
         static const char *nm[12] = {"refill", "gather", "plan", "conflict", "commit", "serial", "inval", "epilogue", "ops", "batches", "serial_ops", ""};
         fprintf(stderr, "[mrz profile] automaton cycles:");
         for (int q = 0; q < 11; q++) fprintf(stderr, " %s=%lld", nm[q], (long long)ctx->h_dbg[q]);
-        fprintf(stderr, " | serial because: filter+=%lld twin-complex=%lld insert-complex=%lld conflict=%lld emit/count=%lld [emit %lld, first overflow %lld, queue %lld] (dynamic invalidations %lld)",
+        fprintf(stderr, " | serial because: filter+=%lld twin-complex=%lld insert-complex=%lld conflict=%lld emit/count=%lld | forwarded=%lld | plan cycles per op: mean=%lld, mean of per-batch max=%lld",
                 (long long)ctx->h_dbg[11], (long long)ctx->h_dbg[12], (long long)ctx->h_dbg[13], (long long)ctx->h_dbg[14],
-                (long long)ctx->h_dbg[15], (long long)ctx->h_dbg[17], (long long)ctx->h_dbg[18], (long long)ctx->h_dbg[19], (long long)ctx->h_dbg[16]);
-        fprintf(stderr, "\n");
+                (long long)ctx->h_dbg[15], (long long)ctx->h_dbg[16], (long long)(ctx->h_dbg[17] / (ctx->h_dbg[8] ? ctx->h_dbg[8] : 1)),
+                (long long)(ctx->h_dbg[18] / (ctx->h_dbg[9] ? ctx->h_dbg[9] : 1)));
+        fprintf(stderr, "\n[mrz profile] serial op parts (cycles/calls): filter=%lld/%lld lookup=%lld/%lld insert_fast=%lld/%lld insert_slow=%lld/%lld clean=%lld/%lld dense-loop=%lld/%lld\n",
+                (long long)ctx->h_dbg[20], (long long)ctx->h_dbg[21], (long long)ctx->h_dbg[22], (long long)ctx->h_dbg[23],
+                (long long)ctx->h_dbg[24], (long long)ctx->h_dbg[25], (long long)ctx->h_dbg[26], (long long)ctx->h_dbg[27],
+                (long long)ctx->h_dbg[28], (long long)ctx->h_dbg[29], (long long)ctx->h_dbg[30], (long long)ctx->h_dbg[31]);
     }
     // ---- emission ----
     CK(cudaEventRecord(ctx->ev[1], s));
