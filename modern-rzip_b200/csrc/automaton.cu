@@ -76,25 +76,15 @@ __device__ __forceinline__ int tz1c(i64 t) {   // trailing one bits, capped at 1
     int z = tz1(t);
     return z > 15 ? 15 : (z < 0 ? 15 : z);
 }
-__device__ __forceinline__ int nib_get(const u32 *gs, i64 g) { return (int)((gs[g >> 3] >> ((g & 7) * 4)) & 15u); }
-// plan phase only (no concurrent lowering): a lost update merely leaves a smaller, still valid, lower bound
-__device__ __forceinline__ void nib_raise(u32 *gs, i64 g, int v) {
-    u32 w = gs[g >> 3];
-    int sh = (int)(g & 7) * 4;
-    gs[g >> 3] = (w & ~(15u << sh)) | ((u32)v << sh);
+// GROUP SUMMARY, in global memory (L2 resident, 512 KiB for the 64 MiB table): per group of 16 slots a 16-bit
+// thermometer - bit i set <=> every tag of the group has more than i trailing one bits (as far as is known: the
+// code is a lower bound, all-zero = nothing known).  Lowering is one atomicAnd, raising one atomicOr: both fire
+// and forget, so plans on any SM and commits on the main CTA maintain it without read-modify-write loops.
+__device__ __forceinline__ void sum_raise(u32 *gs, i64 g, int v) {      // plan phases: the whole group was seen, min = v
+    if (v > 0) atomicOr(gs + (g >> 1), (((1u << v) - 1u) & 0x7fffu) << ((g & 1) * 16));
 }
-// commit / serial phases: the group now holds a tag with v trailing ones (0 for a zeroed slot)
-__device__ __forceinline__ void nib_lower(u32 *gs, i64 g, int v) {
-    u32 *p = &gs[g >> 3];
-    int sh = (int)(g & 7) * 4;
-    u32 old = *p;
-    for (;;) {
-        if ((int)((old >> sh) & 15u) <= v) return;
-        u32 nw = (old & ~(15u << sh)) | ((u32)v << sh);
-        u32 seen = atomicCAS(p, old, nw);
-        if (seen == old) return;
-        old = seen;
-    }
+__device__ __forceinline__ void sum_lower(u32 *gs, i64 g, int v) {      // commit / serial phases: a tag with v trailing ones (0: zeroed)
+    atomicAnd(gs + (g >> 1), ~(0xffffu << ((g & 1) * 16)) | ((((1u << v) - 1u) & 0x7fffu) << ((g & 1) * 16)));
 }
 
 __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int need, i64 hsize, i64 &stop_tag);
@@ -111,7 +101,7 @@ struct Warp {
     const u8 *buf;
     i64 *ttag, *toff;   // the table: tags and offsets (struct hash_entry, rzip.c:59-62, split in two arrays)
     u64 *filt;
-    u32 *gsum;          // group summary (shared memory)
+    u32 *gsum;          // group summary (global memory)
     Token *toks;
     i64 n, end, hmask, hsize, limit, tok_cap;
     int chain, lane;
@@ -144,7 +134,7 @@ struct Warp {
         if (lane == 0) {
             __stcg(toff + slot, off);
             __stcg(ttag + slot, tag);
-            nib_lower(gsum, slot >> GRP_SHIFT, tag ? tz1c(tag) : 0);
+            sum_lower(gsum, slot >> GRP_SHIFT, tag ? tz1c(tag) : 0);
             if (nlog < WLOG_CAP) wlog[nlog] = (int)(slot << 1) | (tag ? 0 : 1);
         }
         nlog++;
@@ -469,7 +459,6 @@ struct Smem {
     Run run;
     i64 e_scan;             // slots in [run.clean_ptr, e_scan) have been examined for the queue
     i64 li;                 // next candidate-list index
-    u32 gsum[(1 << 22) / GRP / 8];   // group summary: one nibble per 16 slots (128 KiB for the 64 MiB table)
     u32 b_rel[AT];          // batch: position of op j relative to seg_lo
     int b_li[AT];           // batch: candidate-list index of op j
     int pre[AT];            // inclusive prefix over planned ops: misses << 22 | inserts << 11 | dcount sum
@@ -489,7 +478,7 @@ struct Smem {
 };
 
 #ifdef MRZ_CUSIM
-#define MRZ_SMEM_PTR(T, name) static T name##_storage; T *name = &name##_storage
+#define MRZ_SMEM_PTR(T, name) T *name = reinterpret_cast<T *>(cusim::dyn_smem())
 #else
 #define MRZ_SMEM_PTR(T, name) extern __shared__ __align__(16) unsigned char name##_raw[]; T *name = reinterpret_cast<T *>(name##_raw)
 #endif
@@ -541,9 +530,9 @@ struct Plan {
 };
 
 // First slot s >= h with tz1(tags[s]) < need (an empty slot has tag 0, i.e. zero trailing ones), or -1 when
-// the walk reaches the end of the table / gets too long.  Whole groups whose summary nibble is >= need are
-// skipped unseen; a group that is scanned completely without a hit has its nibble repaired.
-// Tags are read eight at a time (four 128-bit loads, two 32-byte sectors).
+// the walk reaches the end of the table / gets too long.  Whole groups whose summary says "every tag has >= need
+// trailing ones" are skipped unseen (one 128-bit load covers 8 groups = 128 slots); a group that is scanned
+// completely without a hit has its summary repaired.  Tags are read eight at a time (four 128-bit loads).
 __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int need, i64 hsize, i64 &stop_tag) {
     if (h >= hsize) return -1;
     const i64 h0 = h;
@@ -553,10 +542,17 @@ __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int 
         i64 lim = ((h0 + MAXWALK) >> GRP_SHIFT) + 1;
         if (lim < ngroups) ngroups = lim;
     }
+    const u32 pass_bit = 1u << ((need > 15 ? 15 : need) - 1);   // need >= 1: set <=> the group holds no stop for this walk
     bool whole = (h & (GRP - 1)) == 0;
     for (;;) {
         const i64 gend = (g + 1) << GRP_SHIFT;
         int mn = 15;
+        if ((h & (GRP - 1)) == GRP - 1) {   // the usual case at mask levels >= 4 (primary slots end in ...1111): one tag, one load
+            const i64 t = __ldcg(ttag + h);
+            int z = tz1(t);
+            if (z < 0) z = 64;
+            if (z < need) { stop_tag = t; return h; }
+        } else
         for (i64 o = h & ~(i64)7; o < gend; o += 8) {
             longlong2 v[4];
 #pragma unroll
@@ -573,11 +569,20 @@ __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int 
                 }
             }
         }
-        if (whole) nib_raise(gsum, g, mn);
+        if (whole) sum_raise(gsum, g, mn);
         // skip groups that cannot contain a stop
         g++;
-        while (g < ngroups && nib_get(gsum, g) >= need) g++;
-        if (g >= ngroups) return -1;
+        bool found = false;
+        while (g < ngroups && !found) {
+            const uint4 w4 = __ldcg(reinterpret_cast<const uint4 *>(gsum + ((g >> 3) << 2)));
+            const u32 wv[4] = {w4.x, w4.y, w4.z, w4.w};
+            for (;;) {
+                if (!((wv[(g & 7) >> 1] >> ((g & 1) * 16)) & pass_bit)) { found = true; break; }
+                g++;
+                if ((g & 7) == 0 || g >= ngroups) break;
+            }
+        }
+        if (!found) return -1;
         h = g << GRP_SHIFT;
         whole = true;
     }
@@ -703,6 +708,30 @@ __device__ __forceinline__ void sync_queue(Smem *S, int nlog) {
     }
 }
 
+// PLAN OFFLOAD.  The plan phase of a batch is bound by what one SM can issue (about one uncoalesced request per
+// cycle: ~20 k cycles for 1024 plans), so it is spread over H helper CTAs of the same cooperative grid: the main CTA
+// publishes the batch, every helper thread plans op (tid * H + helper) against the table - read-only, through L2 -
+// and writes the plan record; two flag hand-offs per batch, no grid barrier.  Commits, conflicts, sweeps and the
+// serial ops stay on the main CTA.
+struct PlanIO {
+    unsigned seq, done;       // batch number published by the main CTA / helper threads finished (both zeroed per launch)
+    int nr, chain;
+    i64 min_mask, ins_mask, last_now, hmask, hsize, end, seg_lo;
+    u32 rel[AT];
+    i64 tag[AT];
+    int flags[AT], dcount[AT], w1_slot[AT], w2_slot[AT];
+    i64 w1_off[AT], w1_tag[AT];
+};
+__device__ __forceinline__ unsigned wait_change(volatile unsigned *a, unsigned old) {
+#ifdef MRZ_CUSIM
+    return cusim::wait_change(a, old);
+#else
+    unsigned v;
+    while ((v = *a) == old) __nanosleep(40);
+    return v;
+#endif
+}
+
 // Match extension by the whole CTA: longest common prefix of buf[a0..] / buf[b0..] (fwd) or longest common suffix of
 // buf[..a0) / buf[..b0), at most maxlen bytes; 32 KiB per step, four independent 8-byte compares per thread in flight.
 __device__ __forceinline__ i64 cta_extend(Smem *S, const u8 *buf, i64 a0, i64 b0, i64 maxlen, bool fwd) {
@@ -737,8 +766,50 @@ __device__ __forceinline__ i64 cta_extend(Smem *S, const u8 *buf, i64 a0, i64 b0
 __global__ void __launch_bounds__(AT, 1)
 k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum_global, unsigned *claim, const i64 *__restrict__ hidx,
             AutoState *st, const i64 *__restrict__ tile_off, const u32 *__restrict__ cand_pos,
-            const i64 *__restrict__ cand_tag, Token *toks, i64 *dbg) {
+            const i64 *__restrict__ cand_tag, Token *toks, i64 *dbg, PlanIO *io) {
     if (st->done || st->error) return;
+    const int H = (int)gridDim.x - 1;             // helper CTAs (0: the main CTA plans by itself)
+    if (blockIdx.x > 0) {
+        // ------------------------------------------------------------ helper CTA: plans on request, touches nothing else
+        const int hid = (int)blockIdx.x - 1, per = AT / H;
+        if ((int)threadIdx.x >= per) return;
+        unsigned seen = 0;
+        for (;;) {
+            const unsigned sq = wait_change(&io->seq, seen);
+            if (sq == 0xffffffffu) return;
+            seen = sq;
+            __threadfence();
+            const int nr = *(volatile int *)&io->nr, chain = *(volatile int *)&io->chain;
+            const i64 min_mask = *(volatile i64 *)&io->min_mask, ins_mask = *(volatile i64 *)&io->ins_mask;
+            const i64 hmask = *(volatile i64 *)&io->hmask, hsize = *(volatile i64 *)&io->hsize;
+            const int j = (int)threadIdx.x * H + hid;
+            if (j < nr) {
+                const u32 rel = __ldcg(io->rel + j);
+                const i64 tag = __ldcg(io->tag + j);
+                const bool same = j > 0 && __ldcg(io->rel + j - 1) + 1 == rel && __ldcg(io->tag + j - 1) == tag;
+                const bool same_prev = j > 1 && __ldcg(io->rel + j - 2) + 2 == rel && __ldcg(io->tag + j - 2) == tag;
+                Plan pl;
+                plan_init(pl);
+                // a twin plans its leader's op itself: same tag, same table, same plan
+                if (filt_query(filt, tag)) pl.flags |= F_COMPLEX;
+                else if ((tag & ins_mask) == ins_mask)
+                    plan_op(pl, ttag, toff, gsum_global, filt, tag, tag & hmask, hmask, hsize, min_mask, chain);
+                if (same && !same_prev) {
+                    const int a_flags = pl.flags, a_w2 = pl.w2_slot;
+                    plan_init(pl);
+                    plan_follower(pl, ttag, gsum_global, buf, *(volatile i64 *)&io->seg_lo + (i64)rel, tag, a_flags, a_w2, hmask, hsize,
+                                  min_mask, chain, *(volatile i64 *)&io->end, *(volatile i64 *)&io->last_now);
+                }
+                __stcg(io->flags + j, pl.flags); __stcg(io->dcount + j, pl.dcount);
+                __stcg(io->w1_slot + j, pl.w1_slot); __stcg(io->w2_slot + j, pl.w2_slot);
+                __stcg(io->w1_off + j, pl.w1_off); __stcg(io->w1_tag + j, pl.w1_tag);
+            }
+            __threadfence();
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) atomicAdd(&io->done, 32u);
+        }
+    }
+    unsigned plan_seq = 0;
     MRZ_SMEM_PTR(Smem, S);
     i64 tm[20];
 #pragma unroll
@@ -750,8 +821,6 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
     const i64 n = st->n, end = st->end, hmask = st->hmask, hsize = st->hsize, limit = st->limit;
     const int chain = st->chain;
     const i64 seg_lo = st->seg_lo, seg_hi = st->seg_hi, ncand = st->seg_ncand;
-    const int gwords = (int)(hsize >> (GRP_SHIFT + 3));          // summary words in use
-    for (int q = tid; q < gwords; q += AT) S->gsum[q] = gsum_global[q];
     if (tid == 0) {
         Run &r = S->run;
         r.p = st->p; r.last = st->last; r.cur_p = st->cur_p; r.cur_len = st->cur_len; r.cur_ofs = st->cur_ofs;
@@ -764,7 +833,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
         S->epoch = (unsigned)st->pad1; S->changed[0] = S->changed[1] = 0;
     }
     Warp w;   // used by warp 0 only
-    w.buf = buf; w.ttag = ttag; w.toff = toff; w.filt = filt; w.gsum = S->gsum; w.toks = toks; w.lane = lane;
+    w.buf = buf; w.ttag = ttag; w.toff = toff; w.filt = filt; w.gsum = gsum_global; w.toks = toks; w.lane = lane;
     w.n = n; w.end = end; w.hmask = hmask; w.hsize = hsize; w.limit = limit; w.tok_cap = st->tok_cap; w.chain = chain;
     w.wlog = S->wlog; w.nlog = 0; w.clean_hint = 0; w.prof = dbg ? dbg + 20 : nullptr;
     __syncthreads();
@@ -818,6 +887,38 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
         int lead_w2 = -1;
         const i64 t_plan0 = clock64();
         if (dbg && tid == 0) S->red = 0;
+        if (H > 0) {
+            // publish the batch, wait for the helpers' plan records
+            if (tid < nr) { __stcg(io->rel + tid, S->b_rel[tid]); __stcg(io->tag + tid, S->b_tag[tid]); }
+            if (tid == 0) {
+                io->nr = nr; io->chain = chain; io->min_mask = min_mask; io->ins_mask = ins_mask; io->last_now = last_now;
+                io->hmask = hmask; io->hsize = hsize; io->end = end; io->seg_lo = seg_lo;
+            }
+            plan_seq++;
+            __syncthreads();
+            if (tid == 0) {
+                __threadfence();
+                *(volatile unsigned *)&io->seq = plan_seq;
+                const unsigned target = plan_seq * (unsigned)AT;
+                unsigned v = *(volatile unsigned *)&io->done;
+                while (v != target) v = wait_change(&io->done, v);
+                __threadfence();
+            }
+            __syncthreads();
+            if (tid < nr) {
+                const u32 rel = S->b_rel[tid];
+                my_pos = seg_lo + (i64)rel; my_tag = S->b_tag[tid];
+                bool same = tid > 0 && S->b_rel[tid - 1] + 1 == rel && S->b_tag[tid - 1] == my_tag;
+                bool same_prev = tid > 1 && S->b_rel[tid - 2] + 2 == rel && S->b_tag[tid - 2] == my_tag;
+                follower = same && !same_prev;
+                pl.flags = __ldcg(io->flags + tid); pl.dcount = __ldcg(io->dcount + tid);
+                pl.w1_slot = __ldcg(io->w1_slot + tid); pl.w2_slot = __ldcg(io->w2_slot + tid);
+                pl.w1_off = __ldcg(io->w1_off + tid); pl.w1_tag = __ldcg(io->w1_tag + tid);
+                S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;
+            }
+            __syncthreads();
+            if (follower) lead_w2 = S->pl_w2[tid - 1];
+        } else {
         if (tid < nr) {
             const u32 rel = S->b_rel[tid];
             my_pos = seg_lo + (i64)rel; my_tag = S->b_tag[tid];
@@ -828,7 +929,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             if (!follower) {
                 if (filt_query(filt, my_tag)) pl.flags |= F_COMPLEX;          // an equal tag may exist
                 else if ((my_tag & ins_mask) == ins_mask)
-                    plan_op(pl, ttag, toff, S->gsum, filt, my_tag, my_tag & hmask, hmask, hsize, min_mask, chain);
+                    plan_op(pl, ttag, toff, gsum_global, filt, my_tag, my_tag & hmask, hmask, hsize, min_mask, chain);
             }
             S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;
             if (dbg) {   // per-op plan latency: mean and per-batch maximum (the barrier waits for the slowest walk)
@@ -841,8 +942,9 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
         if (dbg && tid == 0) dbg[18] += S->red;
         if (follower) {
             lead_w2 = S->pl_w2[tid - 1];
-            plan_follower(pl, ttag, S->gsum, buf, my_pos, my_tag, S->pl_fl[tid - 1], lead_w2, hmask, hsize, min_mask,
+            plan_follower(pl, ttag, gsum_global, buf, my_pos, my_tag, S->pl_fl[tid - 1], lead_w2, hmask, hsize, min_mask,
                           chain, end, last_now);
+        }
         }
         TICK(2);   // plan
         // ---------------------------------------------------------------- conflicts: exact stop-slot claims with forwarding
@@ -900,7 +1002,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                             bad = true;
                         else {           // its tag is no stop for my walk: go on from the next slot
                             pl.dep_slot[pl.ndep] = pl.w2_slot; pl.dep_own[pl.ndep] = oi; pl.ndep++;
-                            plan_op(pl, ttag, toff, S->gsum, filt, my_tag, (i64)pl.w2_slot + 1, hmask, hsize, min_mask, chain);
+                            plan_op(pl, ttag, toff, gsum_global, filt, my_tag, (i64)pl.w2_slot + 1, hmask, hsize, min_mask, chain);
                             S->pl_w2[tid] = pl.w2_slot;
                             chg = true;
                             if (dbg) atomicAdd((unsigned long long *)&dbg[16], 1ULL);
@@ -959,14 +1061,14 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                 if (pl.flags & F_W1) {
                     __stcg(toff + pl.w1_slot, pl.w1_off);
                     __stcg(ttag + pl.w1_slot, pl.w1_tag);
-                    nib_lower(S->gsum, pl.w1_slot >> GRP_SHIFT, tz1c(pl.w1_tag));
+                    sum_lower(gsum_global, pl.w1_slot >> GRP_SHIFT, tz1c(pl.w1_tag));
                 }
                 // a twin that overwrites its leader's entry in the same commit must win the slot
                 const bool overwritten = tid + 1 < k && (S->pl_fl[tid + 1] & F_FOLLOW) && S->pl_w2[tid + 1] == pl.w2_slot;
                 if (!overwritten) {
                     __stcg(toff + pl.w2_slot, my_pos);
                     __stcg(ttag + pl.w2_slot, my_tag);
-                    nib_lower(S->gsum, pl.w2_slot >> GRP_SHIFT, tz1c(my_tag));
+                    sum_lower(gsum_global, pl.w2_slot >> GRP_SHIFT, tz1c(my_tag));
                 }
                 filt_set(filt, my_tag);
                 if (pl.flags & F_FOLLOW) filt_set(filt, my_tag ^ DUP_SALT);   // the tag is in the table twice now
@@ -980,7 +1082,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                     const int sl = S->E[(e_idx0 + tid) & (EQ_CAP - 1)];
                     __stcg(ttag + sl, (i64)0);
                     __stcg(toff + sl, (i64)0);
-                    nib_lower(S->gsum, sl >> GRP_SHIFT, 0);
+                    sum_lower(gsum_global, sl >> GRP_SHIFT, 0);
                 }
                 if (tid == 0) {
                     Run &r = S->run;
@@ -1180,8 +1282,11 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
     }
     if (tid == 0 && dbg)
         for (int q = 0; q < 11; q++) dbg[q] += tm[q];
+    if (tid == 0 && H > 0) {   // release the helper CTAs
+        __threadfence();
+        *(volatile unsigned *)&io->seq = 0xffffffffu;
+    }
     // segment exhausted (or chunk finished)
-    for (int q = tid; q < gwords; q += AT) gsum_global[q] = S->gsum[q];
     if (tid == 0) {
         const Run &r = S->run;
         i64 p = r.p;
@@ -1197,13 +1302,32 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
     }
 }
 
-extern "C" void mrz_launch_automaton(const u8 *buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum, unsigned *claim, const i64 *hidx, AutoState *st,
-                                     const i64 *tile_off, const u32 *cand_pos, const i64 *cand_tag, Token *toks, i64 *dbg,
-                                     cudaStream_t s) {
+extern "C" size_t mrz_planio_bytes() { return sizeof(PlanIO); }
+
+// helpers = number of plan-offload CTAs (0, or a power of two <= 32); > 0 needs a cooperative launch: the CTAs wait on one another.
+extern "C" int mrz_launch_automaton(const u8 *buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum, unsigned *claim, const i64 *hidx, AutoState *st,
+                                    const i64 *tile_off, const u32 *cand_pos, const i64 *cand_tag, Token *toks, i64 *dbg, int helpers,
+                                    void *planio, cudaStream_t s) {
+    PlanIO *io = (PlanIO *)planio;
 #ifndef MRZ_CUSIM
-    cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, ttag, toff, filt, gsum, claim, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
+    cudaError_t e = cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    if (e != cudaSuccess) return (int)e;
+    if (helpers > 0) {
+        e = cudaMemsetAsync(io, 0, 8, s);   // seq, done
+        if (e != cudaSuccess) return (int)e;
+        void *args[] = {(void *)&buf, (void *)&ttag, (void *)&toff, (void *)&filt, (void *)&gsum, (void *)&claim, (void *)&hidx, (void *)&st,
+                        (void *)&tile_off, (void *)&cand_pos, (void *)&cand_tag, (void *)&toks, (void *)&dbg, (void *)&io};
+        return (int)cudaLaunchCooperativeKernel((const void *)k_automaton, dim3(1 + helpers), dim3(AT), args, sizeof(Smem), s);
+    }
+    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, ttag, toff, filt, gsum, claim, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg, io);
+    return (int)cudaGetLastError();
 #else
-    MRZ_LAUNCH(k_automaton, 1, AT, s, buf, ttag, toff, filt, gsum, claim, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg);
+    if (helpers > 0) {
+        memset(io, 0, 8);
+        MRZ_LAUNCH_COOP(k_automaton, 1 + helpers, AT, sizeof(Smem), s, buf, ttag, toff, filt, gsum, claim, hidx, st, tile_off, cand_pos, cand_tag,
+                        toks, dbg, io);
+    } else
+        MRZ_LAUNCH_COOP(k_automaton, 1, AT, sizeof(Smem), s, buf, ttag, toff, filt, gsum, claim, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg, io);
+    return 0;
 #endif
 }

@@ -15,8 +15,9 @@
 extern "C" {
 void mrz_launch_scan(const u8 *, const i64 *, AutoState *, int *, i64 *, u32 *, i64 *, int, cudaStream_t);
 void mrz_launch_debug_tags(const u8 *, const i64 *, i64, i64, i64 *, cudaStream_t);
-void mrz_launch_automaton(const u8 *, i64 *, i64 *, u64 *, u32 *, unsigned *, const i64 *, AutoState *, const i64 *, const u32 *,
-                          const i64 *, Token *, i64 *, cudaStream_t);
+size_t mrz_planio_bytes();
+int mrz_launch_automaton(const u8 *, i64 *, i64 *, u64 *, u32 *, unsigned *, const i64 *, AutoState *, const i64 *, const u32 *,
+                         const i64 *, Token *, i64 *, int, void *, cudaStream_t);
 size_t mrz_grid_state_bytes();
 int mrz_launch_automaton_grid(int, int, const u8 *, i64 *, i64 *, u64 *, u32 *, unsigned *, void *, const i64 *, AutoState *,
                               const i64 *, const u32 *, const i64 *, Token *, i64 *, cudaStream_t);
@@ -46,6 +47,8 @@ struct mrz_ctx {
     unsigned *d_claim;   // grid automaton: per-slot claim of the current batch (automaton_grid.cu)
     void *d_gstate;      // grid automaton: state shared by the CTAs
     int grid_g, grid_t;  // grid automaton geometry (0 = the one-CTA automaton of automaton.cu)
+    void *d_planio;      // automaton.cu plan offload: batch + plan records
+    int helpers;         // plan-offload CTAs (MRZ_HELPERS)
     i64 *d_hidx;
     AutoState *d_st;
     int *d_tile_cnt; i64 *d_tile_off; u32 *d_cand_pos; i64 *d_cand_tag;
@@ -198,7 +201,7 @@ static int ensure_s0(mrz_ctx *ctx, i64 bytes) {
 extern "C" void mrz_ctx_destroy(mrz_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaFree(ctx->d_buf_alloc); cudaFree(ctx->d_tab); cudaFree(ctx->d_gsum); cudaFree(ctx->d_filt); cudaFree(ctx->d_claim); cudaFree(ctx->d_gstate); cudaFree(ctx->d_hidx); cudaFree(ctx->d_st);
+    cudaFree(ctx->d_buf_alloc); cudaFree(ctx->d_tab); cudaFree(ctx->d_gsum); cudaFree(ctx->d_filt); cudaFree(ctx->d_claim); cudaFree(ctx->d_planio); cudaFree(ctx->d_gstate); cudaFree(ctx->d_hidx); cudaFree(ctx->d_st);
     cudaFree(ctx->d_tile_cnt); cudaFree(ctx->d_tile_off); cudaFree(ctx->d_cand_pos); cudaFree(ctx->d_cand_tag);
     cudaFree(ctx->d_toks); cudaFree(ctx->d_a0); cudaFree(ctx->d_a1); cudaFree(ctx->d_off0); cudaFree(ctx->d_off1);
     cudaFree(ctx->d_bsum); cudaFree(ctx->d_tot); cudaFree(ctx->d_dbg); cudaFree(ctx->d_s0); cudaFree(ctx->d_s1);
@@ -224,10 +227,21 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     CK(cudaMemset(ctx->d_buf_alloc, 0, MRZ_PAD));
     ctx->tab_slots = (i64)64 * 65536;  // largest levels[].mb_used = 64 MiB
     CK(cudaMalloc(&ctx->d_tab, (size_t)(ctx->tab_slots + 32) * 16));  // + slack for 4-slot probe loads
-    CK(cudaMalloc(&ctx->d_gsum, (size_t)(ctx->tab_slots / 16 / 8) * 4));
+    CK(cudaMalloc(&ctx->d_gsum, (size_t)(ctx->tab_slots / 16 / 2 + 8) * 4));   // 16-bit thermometer per 16 slots
     CK(cudaMalloc(&ctx->d_filt, (size_t)MRZ_FILT_WORDS * 8));
     CK(cudaMalloc(&ctx->d_claim, (size_t)(ctx->tab_slots + 32) * 4));
     CK(cudaMalloc(&ctx->d_gstate, mrz_grid_state_bytes()));
+    CK(cudaMalloc(&ctx->d_planio, mrz_planio_bytes()));
+    {
+        const char *h = getenv("MRZ_HELPERS");
+#ifdef MRZ_CUSIM
+        ctx->helpers = 0;   // the emulator tests select helpers / the grid automaton per test (environment)
+#else
+        ctx->helpers = 0;   // measured on B200: the hand-off costs more than the plans it moves (profiles/r1_helpers_sweep.txt)
+#endif
+        if (h) ctx->helpers = atoi(h);
+        if (ctx->helpers < 0 || ctx->helpers > 32 || (ctx->helpers & (ctx->helpers - 1))) { ctx->err = "MRZ_HELPERS must be 0 or a power of two <= 32"; return MRZ_E_ARG; }
+    }
     {   // geometry of the cooperative grid: G CTAs (the last one serves the sweep queue) x T threads
         const char *a = getenv("MRZ_AUTOMATON"), *g = getenv("MRZ_G"), *t = getenv("MRZ_T");
 #ifdef MRZ_CUSIM
@@ -325,7 +339,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaMemcpyAsync(ctx->d_hidx, prm->hash_index, 256 * 8, cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(ctx->d_st, &h, sizeof h, cudaMemcpyHostToDevice, s));
     CK(cudaMemsetAsync(ctx->d_tab, 0, (size_t)(ctx->tab_slots + 32) * 16, s));  // rzip.c:518-519
-    CK(cudaMemsetAsync(ctx->d_gsum, 0, (size_t)(ctx->tab_slots / 16 / 8) * 4, s));
+    CK(cudaMemsetAsync(ctx->d_gsum, 0, (size_t)(ctx->tab_slots / 16 / 2 + 8) * 4, s));
     CK(cudaMemsetAsync(ctx->d_filt, 0, (size_t)MRZ_FILT_WORDS * 8, s));
     CK(cudaMemsetAsync(ctx->d_claim, 0xff, (size_t)(ctx->tab_slots + 32) * 4, s));
     if (ctx->grid_g) CK(cudaMemsetAsync(ctx->d_gstate, 0, mrz_grid_state_bytes(), s));
@@ -352,9 +366,12 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
                                                 ctx->d_filt, ctx->d_gsum, ctx->d_claim, ctx->d_gstate, ctx->d_hidx, ctx->d_st,
                                                 ctx->d_tile_off, ctx->d_cand_pos, ctx->d_cand_tag, ctx->d_toks, ctx->d_dbg, s);
             if (lrc) CK((cudaError_t)lrc);
-        } else
-            mrz_launch_automaton(ctx->d_buf, ctx->d_tab, ctx->d_tab + ctx->tab_slots + 32, ctx->d_filt, ctx->d_gsum, ctx->d_claim, ctx->d_hidx, ctx->d_st,
-                                 ctx->d_tile_off, ctx->d_cand_pos, ctx->d_cand_tag, ctx->d_toks, ctx->d_dbg, s);
+        } else {
+            int lrc = mrz_launch_automaton(ctx->d_buf, ctx->d_tab, ctx->d_tab + ctx->tab_slots + 32, ctx->d_filt, ctx->d_gsum, ctx->d_claim, ctx->d_hidx,
+                                           ctx->d_st, ctx->d_tile_off, ctx->d_cand_pos, ctx->d_cand_tag, ctx->d_toks, ctx->d_dbg, ctx->helpers,
+                                           ctx->d_planio, s);
+            if (lrc) CK((cudaError_t)lrc);
+        }
         CK(cudaEventRecord(ctx->ev[3], s));
         launches += 4;
         i64 prev_p = h.p;

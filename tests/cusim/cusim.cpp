@@ -13,7 +13,7 @@ static thread_local WarpSlot *warp_pool = nullptr;
 static thread_local Block *block_pool = nullptr;
 static const size_t kStack = 128 * 1024;
 static const int kMaxThreads = 1024;       // per block
-static const int kMaxFibers = 8192;        // all resident blocks of a cooperative launch
+static const int kMaxFibers = 16384;       // all resident blocks of a cooperative launch
 static const int kMaxBlocks = 256;
 static thread_local int grid_arrived = 0, grid_blocks = 0;
 static thread_local unsigned grid_gen = 0;
@@ -43,6 +43,15 @@ cusim_switch:
 )");
 
 void yield_to_scheduler() { cusim_switch(&cur->sp, sched_sp); }
+
+unsigned wait_change(volatile unsigned *addr, unsigned old) {
+    Fiber *f = cur;
+    while (*addr == old) {
+        f->status = 5; f->wait_addr = addr; f->wait_old = old;
+        yield_to_scheduler();
+    }
+    return *addr;
+}
 
 void sync_grid() {
     Fiber *f = cur;
@@ -111,6 +120,7 @@ static void run_resident(int nblocks, int nthreads) {
             if (f->status == 1 && f->bar_gen == b->bar_gen) continue;
             if (f->status == 2 && f->warp_gen == b->warps[f->warp].gen) continue;
             if (f->status == 4 && f->bar_gen == grid_gen) continue;
+            if (f->status == 5 && *f->wait_addr == f->wait_old) continue;
             f->status = 0;
             cur = f;
             blkp = b;

@@ -86,6 +86,7 @@ struct Fiber {
     int block;           // index of its block (cooperative launches)
     unsigned bar_gen;    // generation waited for
     unsigned warp_gen;
+    volatile unsigned *wait_addr; unsigned wait_old;   // status 5: waiting for *wait_addr != wait_old
     uint3_ tid;
     int lane, warp;
 };
@@ -111,6 +112,8 @@ void launch(dim3 grid, dim3 block, const std::function<void()> &body);
 // all blocks resident at once (cudaLaunchCooperativeKernel): grid-wide barriers become possible
 void launch_coop(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()> &body);
 void sync_grid();                    // called by ONE thread of every block
+// spin-wait of a cooperative kernel: the fiber sleeps until *addr != old (polled by the scheduler, no busy switching)
+unsigned wait_change(volatile unsigned *addr, unsigned old);
 static inline void *dyn_smem() { return blkp->smem; }
 
 static inline void sync_block() {
@@ -189,6 +192,7 @@ static inline int __clz(int x) { return x ? __builtin_clz((unsigned)x) : 32; }
 static inline int __clzll(long long x) { return x ? __builtin_clzll((unsigned long long)x) : 64; }
 template <class T> static inline T __ldg(const T *p) { return *p; }
 template <class T> static inline T __ldcg(const T *p) { return *(const volatile T *)p; }
+static inline uint4 __ldcg(const uint4 *p) { uint4 v; const volatile unsigned *q = (const volatile unsigned *)p; v.x = q[0]; v.y = q[1]; v.z = q[2]; v.w = q[3]; return v; }
 static inline longlong2 __ldcg(const longlong2 *p) { longlong2 v; v.x = ((const volatile long long *)p)[0]; v.y = ((const volatile long long *)p)[1]; return v; }
 template <class T> static inline void __stcg(T *p, T v) { *p = v; }
 static inline long long clock64() { return (long long)__builtin_ia32_rdtsc(); }

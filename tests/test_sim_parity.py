@@ -54,3 +54,35 @@ def test_degenerate(sim_ctx):
     check(sim_ctx, np.full(1 << 18, 255, dtype=np.uint8))
     check(sim_ctx, np.tile(np.arange(7, dtype=np.uint8), (1 << 18) // 7))
     check(sim_ctx, np.tile(H.gen_random(4099, seed=9), 100))
+
+
+def _ctx_with_env(env):
+    """A separate emulator context created under the given environment (the geometry is read at context creation)."""
+    import os
+    import mrz_py
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        lib = mrz_py.bind(os.path.join(os.path.dirname(os.path.abspath(__file__)), "cusim", "libmrz_sim.so"))
+        return mrz_py.Context(0, 1 << 24, library=lib)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+@pytest.mark.parametrize("env", [{"MRZ_HELPERS": "2"}, {"MRZ_AUTOMATON": "grid", "MRZ_G": "5", "MRZ_T": "64"}],
+                         ids=["plan-offload-2-helpers", "grid-automaton"])
+def test_other_automaton_geometries(sim_ctx, env):
+    """Plan offload to helper CTAs (cooperative launch) and the multi-CTA grid automaton, on inputs with matches,
+    sweeps, victims and twins."""
+    ctx = _ctx_with_env(env)
+    try:
+        check(ctx, H.gen_random_repeats(2 << 20, 30, lo=2048, hi=65536))
+        check(ctx, H.gen_motif(1 << 20, 2000), level=1)
+        check(ctx, H.gen_random(4 << 20, seed=21), level=2)
+        check(ctx, H.gen_vm_like(1 << 20, seed=13), level=6)
+    finally:
+        ctx.close()
