@@ -5,9 +5,11 @@
 
 A step = one pass of the hot path (hash_search, rzip.c:507-667) over one chunk of synthetic input.
 N=1 workload: BASELINE.json configs[1] — 4 GiB tar-like input, duplicate bodies at distances up to
-4 GiB, one chunk, rzip level 7.  N>1: every rank processes its own 4 GiB chunk of VM-image-like data
-(configs[2] sharded by chunk; weak scaling), victim_round carried across ranks by an all-gather of
-each chunk's victim_round map.
+4 GiB, one chunk, rzip level 7.  N>1: every rank processes its own 4 GiB VM-image-like input (configs[2]
+data, one chunk per GPU, each starting with victim_round = 0 exactly as N reference processes on N files
+would; weak scaling, no data-path collective).  `--one-file` instead treats the N chunks as consecutive
+chunks of ONE input and resolves the victim_round chain exactly (modern-rzip_b200/shard.py): chunks whose
+speculated carry was wrong are re-run inside the timed region.
 Prints ONE JSON line (rank 0).  `value` = device-resident throughput (CUDA events); `e2e` = the same
 through mrz_rzip_chunk() with pinned host buffers (H2D + kernels + D2H inside the timed region).
 """
@@ -28,6 +30,15 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 GIB = 1 << 30
 LEVEL = 7
+
+
+def measured_traffic():
+    """dram bytes per k_automaton launch from the committed ncu --set full capture (profiles/), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_final_traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return None
 
 
 def hbm_peak():
@@ -170,8 +181,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--size", type=int, default=4 * GIB, help="chunk bytes (default 4 GiB = configs[1])")
-    ap.add_argument("--cpu-sample", type=int, default=512 << 20, help="bytes of the workload given to the CPU baseline")
+    ap.add_argument("--cpu-sample", type=int, default=2048 << 20, help="bytes of the workload given to the CPU baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--one-file", action="store_true", help="N>1: the ranks' chunks are consecutive chunks of one input (exact carry)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -179,7 +191,9 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     n = args.size
     multi = world > 1
-    workload = ("configs[2]: VM-image-like, one %d-byte chunk per GPU, rzip level 7" % n) if multi else \
+    workload = ("configs[2]: VM-image-like, %s, one %d-byte chunk per GPU, rzip level 7"
+                % ("consecutive chunks of one input with the exact victim_round carry" if args.one_file else
+                   "one independent input per GPU", n)) if multi else \
         ("configs[1]: %.2f GiB tar-like, duplicate bodies at distances up to the chunk size, single chunk, rzip level 7"
          % (n / GIB))
     config = {"workload": workload, "chunk_bytes_per_gpu": n, "rzip_level": LEVEL,
@@ -200,7 +214,9 @@ def main():
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int64",
                 "data": "synthetic", "config": config,
                 "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": 1, "kind": "reference",
-                                 "sample": "first %d MiB of the workload generator, oracle/_ref/mrzip -n -L7 file->file "
+                                 "sample": "first %d MiB of the workload generator as one chunk (the reference does most of its table "
+                                           "work early in a chunk, so a prefix understates its whole-chunk rate), "
+                                           "oracle/_ref/mrzip -n -L7 file->file "
                                            "(1 hash_search thread + checksum/writer helpers), host has %d cores"
                                            % (sample_n >> 20, os.cpu_count())},
                 "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -237,10 +253,31 @@ def main():
     prm = mrz_py.make_params(LEVEL, cb, hidx, 0)
 
     clocks = ClockSampler(local_rank)
+    reruns_total = 0
+
+    def resident_step():
+        """One pass over this rank's chunk; with --one-file the victim_round chain across ranks is resolved exactly
+        (shard.py) and a chunk whose speculated carry was wrong runs again.  Returns (last result, summed timings)."""
+        nonlocal reruns_total
+        if not (multi and args.one_file):
+            r = ctx.run_resident(n, prm)
+            return r, (r.ms_kernels, r.ms_automaton, r.ms_tagscan, r.ms_emit, r.gpu_launches)
+        import shard
+        acc = [0.0, 0.0, 0.0, 0.0, 0]
+
+        def run(_chunk, vr_in):
+            r = ctx.run_resident(n, mrz_py.make_params(LEVEL, cb, hidx, vr_in))
+            for i, v in enumerate((r.ms_kernels, r.ms_automaton, r.ms_tagscan, r.ms_emit, r.gpu_launches)):
+                acc[i] += v
+            return int(r.victim_events), int(r.victim_round_out), r
+        results, _vr, reruns = shard.run_sharded([None] * world, run, rank, world, device="cuda")
+        reruns_total += reruns
+        return results[rank], tuple(acc)
+
     # device-resident timing (K)
     ctx.upload(data)
     for _ in range(args.warmup):
-        ctx.run_resident(n, prm)
+        resident_step()
     barrier()
     clocks.start()
     t0 = time.perf_counter()
@@ -248,12 +285,12 @@ def main():
     launches = 0
     res = None
     for _ in range(args.steps):
-        res = ctx.run_resident(n, prm)
-        ms_k += res.ms_kernels
-        ms_auto += res.ms_automaton
-        ms_scan += res.ms_tagscan
-        ms_emit += res.ms_emit
-        launches += res.gpu_launches
+        res, tms = resident_step()
+        ms_k += tms[0]
+        ms_auto += tms[1]
+        ms_scan += tms[2]
+        ms_emit += tms[3]
+        launches += tms[4]
     barrier()
     wall_k = time.perf_counter() - t0
     clk = clocks.stop()
@@ -269,6 +306,9 @@ def main():
     if multi:
         dist.all_reduce(tk, op=dist.ReduceOp.MAX)
     t_dev, t_wall, t_e2e = [float(x) for x in tk.tolist()]
+    if multi and args.one_file:
+        t_dev = t_wall   # the chain serialises re-runs across ranks: the critical path is the wall clock between the barriers
+        config["timing"] = "wall clock between barriers (victim_round chain across ranks); re-runs this rank: %d" % reruns_total
     total_bytes = n * world * args.steps
     value = total_bytes / t_dev / 1e9
     e2e = total_bytes / t_e2e / 1e9
@@ -284,7 +324,10 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clk,
             "roofline": {"bound": "hbm", "kernel": "k_automaton", "achieved": achieved, "peak": peak,
-                         "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": (measured_traffic() or {}).get("dram_bytes_per_launch"),
+                         "traffic_source": (measured_traffic() or {}).get("source"),
+                         "launches_per_step": None,
                          "algorithmic_bytes_per_step": int(b_alg),
                          "share_of_step": ms_auto / ms_k if ms_k else None,
                          "ms_per_step": {"tag_scan": ms_scan / args.steps, "automaton": ms_auto / args.steps,
@@ -298,8 +341,9 @@ def main():
         sample_n = min(args.cpu_sample, n)
         times = run_reference_sample(np.array(data[:sample_n]), 1, 0)
         line["cpu_baseline"] = {"value": sample_n / times[0] / 1e9, "unit": "GB/s", "cores": 1, "kind": "reference",
-                                "sample": "first %d MiB of the same input, oracle/_ref/mrzip -n -L7 file->file in "
-                                          "/dev/shm (1 hash_search thread + helpers); host has %d cores"
+                                "sample": "first %d MiB of the same input as one chunk (a prefix understates the reference's "
+                                          "whole-chunk rate: its table work is front-loaded), oracle/_ref/mrzip -n -L7 "
+                                          "file->file in /dev/shm (1 hash_search thread + helpers); host has %d cores"
                                           % (sample_n >> 20, os.cpu_count())}
     if rank == 0:
         print(json.dumps(line))
