@@ -5,9 +5,10 @@
 
 A step = one pass of the hot path (hash_search, rzip.c:507-667) over one chunk of synthetic input.
 N=1 workload: BASELINE.json configs[1] — 4 GiB tar-like input, duplicate bodies at distances up to
-4 GiB, one chunk, rzip level 7.  N>1: every rank processes its own 4 GiB VM-image-like input (configs[2]
-data, one chunk per GPU, each starting with victim_round = 0 exactly as N reference processes on N files
-would; weak scaling, no data-path collective).  `--one-file` instead treats the N chunks as consecutive
+4 GiB, one chunk, rzip level 7.  N>1 (weak scaling, no data-path collective): every rank processes its own
+4 GiB input of the SAME kind (seed 2 + rank), one chunk per GPU, each starting with victim_round = 0 exactly
+as N reference processes on N files would; `--workload vm` switches every rank (also N=1) to the VM-image-like
+data of configs[2].  `--one-file` instead treats the N chunks as consecutive
 chunks of ONE input and resolves the victim_round chain exactly (modern-rzip_b200/shard.py): chunks whose
 speculated carry was wrong are re-run inside the timed region.
 Prints ONE JSON line (rank 0).  `value` = device-resident throughput (CUDA events); `e2e` = the same
@@ -23,6 +24,8 @@ import threading
 import time
 
 import numpy as np
+
+os.environ.setdefault("NCCL_DEBUG", "WARN")   # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "modern-rzip_b200"))
@@ -181,8 +184,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--size", type=int, default=4 * GIB, help="chunk bytes (default 4 GiB = configs[1])")
-    ap.add_argument("--cpu-sample", type=int, default=2048 << 20, help="bytes of the workload given to the CPU baseline")
+    ap.add_argument("--cpu-sample", type=int, default=1024 << 20, help="bytes of the workload given to the CPU baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="tar", choices=["tar", "vm"], help="tar: configs[1] data; vm: configs[2] data")
     ap.add_argument("--one-file", action="store_true", help="N>1: the ranks' chunks are consecutive chunks of one input (exact carry)")
     args = ap.parse_args()
 
@@ -191,11 +195,12 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     n = args.size
     multi = world > 1
-    workload = ("configs[2]: VM-image-like, %s, one %d-byte chunk per GPU, rzip level 7"
-                % ("consecutive chunks of one input with the exact victim_round carry" if args.one_file else
-                   "one independent input per GPU", n)) if multi else \
-        ("configs[1]: %.2f GiB tar-like, duplicate bodies at distances up to the chunk size, single chunk, rzip level 7"
-         % (n / GIB))
+    kind = "configs[2]: VM-image-like (4 KiB blocks: zero / copies / random / text)" if args.workload == "vm" else \
+        "configs[1]: tar-like, duplicate bodies at distances up to the chunk size"
+    workload = "%s, %.2f GiB single chunk per GPU, rzip level 7" % (kind, n / GIB)
+    if multi:
+        workload += ", consecutive chunks of one input with the exact victim_round carry" if args.one_file else \
+            ", one independent input per GPU (seed 2 + rank)"
     config = {"workload": workload, "chunk_bytes_per_gpu": n, "rzip_level": LEVEL,
               "l2": "input (%.1f GiB) and 64 MiB table re-initialised every step; input larger than L2" % (n / GIB)}
 
@@ -203,9 +208,9 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return 0
-        gen = gen_vm_like if multi else gen_tar_like
+        gen = gen_vm_like if args.workload == "vm" else gen_tar_like
         sample_n = min(args.cpu_sample, n)
-        sample = gen(sample_n, seed=3 if multi else 2)
+        sample = gen(sample_n, seed=2)
         w = min(args.warmup, 1)
         times = run_reference_sample(sample, args.steps, w)
         gbs = sample_n / (sum(times) / len(times)) / 1e9
@@ -246,10 +251,7 @@ def main():
     pin_s0 = mrz_py.PinnedBuffer(n // 2 + 64)
     pin_s1 = mrz_py.PinnedBuffer(n + 16)
     data = pin_in.array
-    if multi:
-        gen_vm_like(n, seed=3 + rank, out=data)
-    else:
-        gen_tar_like(n, seed=2, out=data)
+    (gen_vm_like if args.workload == "vm" else gen_tar_like)(n, seed=2 + rank, out=data)
     prm = mrz_py.make_params(LEVEL, cb, hidx, 0)
 
     clocks = ClockSampler(local_rank)

@@ -317,7 +317,9 @@ struct Warp {
     // rzip.c:256-301 for a tag that has no equal entry in the table: every level of the displacement chain is a
     // summary-accelerated find_stop walk (all walks see the table before any write, as the reference's recursion does).
     // Returns false, having written nothing, when some level needs the general walk of insert().
-    __device__ __forceinline__ bool insert_fast(i64 t, i64 off, i64 *stk) {
+    // n_eq / eq_pos: the slots (relative to the primary slot, ascending) that hold a tag equal to t, as collected by the
+    // CTA-wide lookup; with them the equal-tag round counting and the victim choice of rzip.c:278-291 need no walk.
+    __device__ __forceinline__ bool insert_fast(i64 t, i64 off, i64 *stk, int n_eq, const int *eq_pos) {
         const i64 btm = (min_mask << 1) | 1;
         const int kb = __popcll((u64)btm);
         int sp = 0;
@@ -327,6 +329,21 @@ struct Warp {
             i64 stg;
             const i64 sl = find_stop(ttag, gsum, ct & hmask, z > kb ? z : kb, hsize, stg);
             if (sl < 0) return false;
+            if (sp == 0 && n_eq > 0) {
+                const i64 rel = sl - (t & hmask);
+                int ne = 0;                              // equal tags the walk meets before its stop slot
+                for (int q = lane; q < n_eq; q += 32) ne += eq_pos[q] < rel;
+                for (int o = 16; o; o >>= 1) ne += __shfl_xor_sync(FULL, ne, o);
+                if (ne >= chain) {                       // rzip.c:284-290: the chain is full, replace the victim_round-th entry
+                    const i64 target = ((t & hmask) + eq_pos[vr]) & hmask;
+                    __syncwarp();
+                    count--;
+                    vevents++;
+                    vr = (vr + 1 == chain) ? 0 : vr + 1;
+                    write_slot(target, off, t);
+                    return true;
+                }
+            }
             if (stg == 0 || (stg & btm) != btm) {
                 __syncwarp();                          // every lane has read the table before lane 0 writes it
                 if (stg != 0) count--;                 // rzip.c:267-269
@@ -380,7 +397,7 @@ struct Warp {
     // emitted (p jumped to last_match).
     // pre_n >= 0: the CTA has already walked the probe sequence and compared the pre_n equal-tag candidates
     __device__ __noinline__ bool op(i64 pp, i64 t, i64 *stk, int pre_n = -1, const i64 *pre_len = nullptr, const i64 *pre_rev = nullptr,
-                                    const i64 *pre_off = nullptr) {
+                                    const i64 *pre_off = nullptr, const int *pre_pos = nullptr) {
 #define PROF(slot, t0) do { if (prof && lane == 0) { prof[slot] += clock64() - (t0); prof[(slot) + 1] += 1; } } while (0)
         nops++;
         i64 bofs = 0, brev = 0;
@@ -395,7 +412,8 @@ struct Warp {
             count++;
             bool placed = false;
             c0 = clock64();
-            if (!maybe) { placed = insert_fast(t, pp, stk); PROF(4, c0); }   // no equal tag exists
+            if (!maybe) { placed = insert_fast(t, pp, stk, 0, nullptr); PROF(4, c0); }   // no equal tag exists
+            else if (pre_n >= 0) { placed = insert_fast(t, pp, stk, pre_n, pre_pos); PROF(4, c0); }   // all equal tags are known
             c0 = clock64();
             if (!placed) { insert(t, pp, stk); PROF(6, c0); }
             if (lane == 0) {
@@ -532,7 +550,7 @@ struct Plan {
 // First slot s >= h with tz1(tags[s]) < need (an empty slot has tag 0, i.e. zero trailing ones), or -1 when
 // the walk reaches the end of the table / gets too long.  Whole groups whose summary says "every tag has >= need
 // trailing ones" are skipped unseen (one 128-bit load covers 8 groups = 128 slots); a group that is scanned
-// completely without a hit has its summary repaired.  Tags are read eight at a time (four 128-bit loads).
+// completely without a hit has its summary repaired.  Tags are read eight at a time (two 256-bit loads).
 __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int need, i64 hsize, i64 &stop_tag) {
     if (h >= hsize) return -1;
     const i64 h0 = h;
@@ -554,12 +572,11 @@ __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int 
             if (z < need) { stop_tag = t; return h; }
         } else
         for (i64 o = h & ~(i64)7; o < gend; o += 8) {
-            longlong2 v[4];
-#pragma unroll
-            for (int q = 0; q < 4; q++) v[q] = __ldcg(reinterpret_cast<const longlong2 *>(ttag + o) + q);
+            i64 v[8];
+            ld_i64x8_cg(ttag + o, v);
 #pragma unroll
             for (int q = 0; q < 8; q++) {
-                const i64 t = (q & 1) ? v[q >> 1].y : v[q >> 1].x;
+                const i64 t = v[q];
                 if (o + q >= h) {
                     int z = tz1(t);
                     if (z < 0) z = 64;
@@ -969,6 +986,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                  ((pl.flags & F_W1ELIG) && pl.w1_slot >= w_lo && pl.w1_slot < w_hi))) {
                 pl.flags |= F_CONF;
                 live = false;
+                if (dbg) atomicAdd((unsigned long long *)&dbg[32], 1ULL);   // stop slot in the sweep queue
             }
             if (live) {
                 atomicMin(claim + pl.w2_slot, claim_key(ep, tid, 0));
@@ -983,13 +1001,14 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                 bool bad = false;
                 // a follower's plan builds on its leader's write: only older claims conflict, and the leader must not have moved
                 const int before = (pl.flags & F_FOLLOW) ? tid - 1 : tid;
-                if ((pl.flags & F_FOLLOW) && S->pl_w2[tid - 1] != lead_w2) bad = true;
+                int why = 0;
+                if ((pl.flags & F_FOLLOW) && S->pl_w2[tid - 1] != lead_w2) { bad = true; why = 33; }
                 for (int d = 0; d < pl.ndep && !bad; d++) {   // slots I walked past on the strength of an earlier op's claim
                     const unsigned o = __ldcg(claim + pl.dep_slot[d]);
                     const int oi = (int)((o >> 1) & 1023u);
-                    if ((o >> 11) != ep_hi || (o & 1u) || oi >= tid) { bad = true; break; }
+                    if ((o >> 11) != ep_hi || (o & 1u) || oi >= tid) { bad = true; why = 34; break; }
                     const i64 ot = S->b_tag[oi];
-                    if (tz1(ot) < my_need || (ot & btm) != btm || ot == my_tag) { bad = true; break; }
+                    if (tz1(ot) < my_need || (ot & btm) != btm || ot == my_tag) { bad = true; why = 34; break; }
                     pl.dep_own[d] = oi;
                 }
                 if (!bad) {
@@ -998,8 +1017,10 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                     if (oi < before) {   // my stop slot goes to an earlier op
                         const i64 ot = S->b_tag[oi];
                         if ((pl.flags & F_FOLLOW) || (o & 1u) || pl.ndep == MAXDEP || it >= FWD_ITERS || tz1(ot) < my_need ||
-                            (ot & btm) != btm || ot == my_tag)   // an equal tag: my lookup must meet its entry (serial)
+                            (ot & btm) != btm || ot == my_tag) {   // an equal tag: my lookup must meet its entry (serial)
                             bad = true;
+                            why = (pl.flags & F_FOLLOW) ? 33 : (o & 1u) ? 35 : ot == my_tag ? 36 : (tz1(ot) < my_need || (ot & btm) != btm) ? 37 : 38;
+                        }
                         else {           // its tag is no stop for my walk: go on from the next slot
                             pl.dep_slot[pl.ndep] = pl.w2_slot; pl.dep_own[pl.ndep] = oi; pl.ndep++;
                             plan_op(pl, ttag, toff, gsum_global, filt, my_tag, (i64)pl.w2_slot + 1, hmask, hsize, min_mask, chain);
@@ -1007,10 +1028,12 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                             chg = true;
                             if (dbg) atomicAdd((unsigned long long *)&dbg[16], 1ULL);
                         }
-                    } else if ((pl.flags & F_W1) && (int)((__ldcg(claim + pl.w1_slot) >> 1) & 1023u) < tid)
+                    } else if ((pl.flags & F_W1) && (int)((__ldcg(claim + pl.w1_slot) >> 1) & 1023u) < tid) {
                         bad = true;
+                        why = 39;
+                    }
                 }
-                if (bad) { pl.flags |= F_CONF; chg = true; }
+                if (bad) { pl.flags |= F_CONF; chg = true; if (dbg) atomicAdd((unsigned long long *)&dbg[why], 1ULL); }
                 if (chg) S->pl_fl[tid] = pl.flags;
             }
             if (chg) S->changed[it & 1] = 1;
@@ -1108,6 +1131,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             // ---- the lookup of op k (find_best_match, rzip.c:426-462) by the whole CTA: the probe sequence is walked
             // 4096 slots per step, equal tags are collected in slot order, and the 32 warps share the match_len calls
             int pre_n = -1;
+            const i64 c_lk0 = clock64();
             {
                 const i64 tk = S->b_tag[k], pk = seg_lo + (i64)S->b_rel[k];
                 if (filt_query(filt, tk)) {
@@ -1178,6 +1202,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                     }
                 }
             }
+            if (dbg && tid == 0) dbg[19] += clock64() - c_lk0;
             // ---- op k on the live table, reference semantics (warp 0)
             if (wid == 0) {
                 w.load(S->run);
@@ -1187,7 +1212,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                 w.clean_hint = hint;
                 const i64 pk = seg_lo + (i64)S->b_rel[k], tk = S->b_tag[k];
                 w.p = pk;
-                bool jumped = w.op(pk, tk, S->stk, pre_n, S->lk_len, S->lk_rev, S->lk_off);
+                bool jumped = w.op(pk, tk, S->stk, pre_n, S->lk_len, S->lk_rev, S->lk_off, S->lk_pos);
                 w.clean_hint = 0;
                 const i64 c_dense = clock64();
                 if (jumped && !w.error) {
@@ -1274,7 +1299,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
         if (tid == 0) {
             if (!S->ended) S->li = li;                       // whole batch consumed
             // batch size: small after an emission (the plans behind a jump are wasted), growing back
-            if (S->jumped) S->bmax = 64;
+            if (S->jumped) S->bmax = st->pad0 > 0 ? st->pad0 : AT;   // measured: restarting small after an emission only adds batches
             else if (S->bmax < AT) S->bmax *= 2;
         }
         __syncthreads();

@@ -86,6 +86,16 @@ __device__ __forceinline__ void st_slot(Slot *p, i64 off, i64 tag) {
     __stcg(reinterpret_cast<longlong2 *>(p), v);
 }
 
+// Eight consecutive i64 (64-byte aligned) with two 256-bit loads (LDG.E.256 on sm_100a), L2-coherent.
+__device__ __forceinline__ void ld_i64x8_cg(const i64 *p, i64 t[8]) {
+#ifdef MRZ_CUSIM
+    for (int q = 0; q < 8; q++) t[q] = ((const volatile i64 *)p)[q];
+#else
+    asm volatile("ld.global.cg.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(t[0]), "=l"(t[1]), "=l"(t[2]), "=l"(t[3]) : "l"(p));
+    asm volatile("ld.global.cg.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(t[4]), "=l"(t[5]), "=l"(t[6]), "=l"(t[7]) : "l"(p + 4));
+#endif
+}
+
 // 8 bytes starting at byte index idx (any alignment); buf has MRZ_PAD bytes of slack on both sides.
 __device__ __forceinline__ u64 ld_u64_unaligned(const u8 *buf, i64 idx) {
     const u8 *a = buf + idx;

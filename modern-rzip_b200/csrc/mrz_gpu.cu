@@ -331,6 +331,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     h.min_mask = h.ins_mask = ((i64)1 << kLevels[L].freq) - 1;  // rzip.c:509, :533
     h.victim_round = prm->victim_round_in;
     h.tok_cap = ctx->tok_cap;
+    { const char *bj = getenv("MRZ_BMAX_JUMP"); h.pad0 = bj ? atoi(bj) : 0; }   // batch size right after an emission (tuning)
     h.done = h.end <= 0 ? 1 : 0;
     int launches = 0;
     float ms_scan = 0, ms_auto = 0, ms_emit = 0, ms_total = 0;
@@ -410,6 +411,9 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
                 (long long)ctx->h_dbg[20], (long long)ctx->h_dbg[21], (long long)ctx->h_dbg[22], (long long)ctx->h_dbg[23],
                 (long long)ctx->h_dbg[24], (long long)ctx->h_dbg[25], (long long)ctx->h_dbg[26], (long long)ctx->h_dbg[27],
                 (long long)ctx->h_dbg[28], (long long)ctx->h_dbg[29], (long long)ctx->h_dbg[30], (long long)ctx->h_dbg[31]);
+        fprintf(stderr, "[mrz profile] CTA lookup phase cycles=%lld | plans given up: sweep-queue stop=%lld twin=%lld dependency=%lld owner-moves-occupant=%lld equal-tag=%lld owner-lesser=%lld limits=%lld w1-claimed=%lld\n",
+                (long long)ctx->h_dbg[19], (long long)ctx->h_dbg[32], (long long)ctx->h_dbg[33], (long long)ctx->h_dbg[34],
+                (long long)ctx->h_dbg[35], (long long)ctx->h_dbg[36], (long long)ctx->h_dbg[37], (long long)ctx->h_dbg[38], (long long)ctx->h_dbg[39]);
     }
     // ---- emission ----
     CK(cudaEventRecord(ctx->ev[1], s));
