@@ -113,6 +113,25 @@ def gen_vm_like(n, seed=3, out=None):
     return buf
 
 
+def gen_dense(n, seed=5, out=None, base=1 << 20, mutations=100):
+    """configs[4]: one random 1 MiB base block written over and over with 100 random point mutations per copy."""
+    rng = np.random.default_rng(seed)
+    buf = out if out is not None else np.zeros(n, dtype=np.uint8)
+    blk = rng.integers(0, 256, base, dtype=np.uint8)
+    for pos in range(0, n, base):
+        m = min(base, n - pos)
+        buf[pos:pos + m] = blk[:m]
+        idx = rng.integers(0, m, mutations)
+        buf[pos + idx] = rng.integers(0, 256, mutations, dtype=np.uint8)
+    return buf
+
+
+GENS = {"tar": gen_tar_like, "vm": gen_vm_like, "dense": gen_dense}
+KINDS = {"tar": "configs[1]: tar-like, duplicate bodies at distances up to the chunk size",
+         "vm": "configs[2]: VM-image-like (4 KiB blocks: zero / copies / random / text)",
+         "dense": "configs[4]: dense repeats (1 MiB base block, 100 point mutations per copy)"}
+
+
 # ------------------------------------------------------------------ clocks
 class ClockSampler:
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
@@ -157,7 +176,7 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------ reference CPU arm
-def run_reference_sample(sample, steps, warmup):
+def run_reference_sample(sample, steps, warmup, level=LEVEL):
     """Times the unmodified reference binary (oracle/_ref/mrzip -n) on a bounded sample."""
     import helpers as H
     if not H.have_ref():
@@ -170,7 +189,7 @@ def run_reference_sample(sample, steps, warmup):
         mflag = str(max(1, (sample.size * 3 // 2) // (100 * 1048576) + 2))  # ramsize so that one chunk holds it
         for i in range(warmup + steps):
             t0 = time.perf_counter()
-            H.run_reference(fin, fout, ("-m", mflag, "-p", "1", "-L", str(LEVEL)))
+            H.run_reference(fin, fout, ("-m", mflag, "-p", "1", "-L", str(level)))
             dt = time.perf_counter() - t0
             if i >= warmup:
                 times.append(dt)
@@ -186,7 +205,8 @@ def main():
     ap.add_argument("--size", type=int, default=4 * GIB, help="chunk bytes (default 4 GiB = configs[1])")
     ap.add_argument("--cpu-sample", type=int, default=1024 << 20, help="bytes of the workload given to the CPU baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="tar", choices=["tar", "vm"], help="tar: configs[1] data; vm: configs[2] data")
+    ap.add_argument("--workload", default="tar", choices=["tar", "vm", "dense"], help="tar: configs[1] data; vm: configs[2] data; dense: configs[4] data")
+    ap.add_argument("--level", type=int, default=LEVEL, help="rzip level (index into levels[], rzip.c:65-73)")
     ap.add_argument("--one-file", action="store_true", help="N>1: the ranks' chunks are consecutive chunks of one input (exact carry)")
     args = ap.parse_args()
 
@@ -195,24 +215,23 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     n = args.size
     multi = world > 1
-    kind = "configs[2]: VM-image-like (4 KiB blocks: zero / copies / random / text)" if args.workload == "vm" else \
-        "configs[1]: tar-like, duplicate bodies at distances up to the chunk size"
-    workload = "%s, %.2f GiB single chunk per GPU, rzip level 7" % (kind, n / GIB)
+    kind = KINDS[args.workload]
+    workload = "%s, %.2f GiB single chunk per GPU, rzip level %d" % (kind, n / GIB, args.level)
     if multi:
         workload += ", consecutive chunks of one input with the exact victim_round carry" if args.one_file else \
             ", one independent input per GPU (seed 2 + rank)"
-    config = {"workload": workload, "chunk_bytes_per_gpu": n, "rzip_level": LEVEL,
+    config = {"workload": workload, "chunk_bytes_per_gpu": n, "rzip_level": args.level,
               "l2": "input (%.1f GiB) and 64 MiB table re-initialised every step; input larger than L2" % (n / GIB)}
 
     # ---------------- reference arm: the reference's own CPU implementation on the host cores
     if args.impl == "reference":
         if rank != 0:
             return 0
-        gen = gen_vm_like if args.workload == "vm" else gen_tar_like
+        gen = GENS[args.workload]
         sample_n = min(args.cpu_sample, n)
         sample = gen(sample_n, seed=2)
         w = min(args.warmup, 1)
-        times = run_reference_sample(sample, args.steps, w)
+        times = run_reference_sample(sample, args.steps, w, args.level)
         gbs = sample_n / (sum(times) / len(times)) / 1e9
         line = {"impl": "reference", "metric": "rzip pre-process input GB/s", "value": gbs, "unit": "GB/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": w, "ms_per_step": 1e3 * sum(times) / len(times),
@@ -251,8 +270,8 @@ def main():
     pin_s0 = mrz_py.PinnedBuffer(n // 2 + 64)
     pin_s1 = mrz_py.PinnedBuffer(n + 16)
     data = pin_in.array
-    (gen_vm_like if args.workload == "vm" else gen_tar_like)(n, seed=2 + rank, out=data)
-    prm = mrz_py.make_params(LEVEL, cb, hidx, 0)
+    GENS[args.workload](n, seed=2 + rank, out=data)
+    prm = mrz_py.make_params(args.level, cb, hidx, 0)
 
     clocks = ClockSampler(local_rank)
     reruns_total = 0
@@ -268,7 +287,7 @@ def main():
         acc = [0.0, 0.0, 0.0, 0.0, 0]
 
         def run(_chunk, vr_in):
-            r = ctx.run_resident(n, mrz_py.make_params(LEVEL, cb, hidx, vr_in))
+            r = ctx.run_resident(n, mrz_py.make_params(args.level, cb, hidx, vr_in))
             for i, v in enumerate((r.ms_kernels, r.ms_automaton, r.ms_tagscan, r.ms_emit, r.gpu_launches)):
                 acc[i] += v
             return int(r.victim_events), int(r.victim_round_out), r
@@ -341,7 +360,7 @@ def main():
                        "victim_events": int(res.victim_events)}}
     if rank == 0 and not multi and not args.no_cpu_baseline:
         sample_n = min(args.cpu_sample, n)
-        times = run_reference_sample(np.array(data[:sample_n]), 1, 0)
+        times = run_reference_sample(np.array(data[:sample_n]), 1, 0, args.level)
         line["cpu_baseline"] = {"value": sample_n / times[0] / 1e9, "unit": "GB/s", "cores": 1, "kind": "reference",
                                 "sample": "first %d MiB of the same input as one chunk (a prefix understates the reference's "
                                           "whole-chunk rate: its table work is front-loaded), oracle/_ref/mrzip -n -L7 "

@@ -1259,13 +1259,25 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                     bool overflow = w.nlog > WLOG_CAP;
                     S->jumped = jumped;
                     S->nlog = overflow ? 0 : w.nlog;
-                    if (jumped || mask_changed || overflow || w.error) {
+                    int kp = nr;
+                    if (jumped && !mask_changed && !overflow && !w.error && w.p >= pk) {   // (a short match can end BEFORE op k: p goes back, rzip.c:597)
+                        // an emission skips the ops up to the end of the match; the plans beyond it stay good (only a
+                        // write to a plan's stop slot can spoil it): carry on with the first op past the jump
+                        int a = k + 1, b = nr;
+                        const i64 relp = w.p - seg_lo;
+                        while (a < b) {
+                            const int m = (a + b) >> 1;
+                            if ((i64)S->b_rel[m] <= relp) a = m + 1; else b = m;
+                        }
+                        kp = a;
+                    }
+                    if (mask_changed || overflow || w.error || (jumped && kp >= nr)) {
                         S->ended = 1;
                         S->e_idx = S->e_cnt = 0; S->e_scan = w.clean_ptr;    // rebuild the queue
                         if (!jumped) S->li = (i64)S->b_li[k] + 1;
                     } else {
                         if (steady) sync_queue(S, w.nlog);
-                        S->pos = k + 1;
+                        S->pos = jumped ? kp : k + 1;
                     }
                 }
             }
@@ -1276,11 +1288,12 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             // window this batch was planned with
             if (steady && S->e_scan < w_hi) refill_queue(S, ttag, w_hi, EQ_CAP);
             // later plans that read a slot this op wrote are no longer valid; nor is its twin's plan
-            if (tid == k + 1 && (pl.flags & F_FOLLOW)) pl.flags |= F_CONF;
-            if (tid > k && tid < nr)   // a plan forwarded over op k's claim assumed k's planned write
+            const int npos = S->pos;   // k + 1, or the first op past an emission's jump (the ops in between never run)
+            if (tid == npos && (pl.flags & F_FOLLOW)) pl.flags |= F_CONF;
+            if (tid >= npos && tid < nr)   // a plan forwarded over the claim of op k / of a skipped op assumed that op's planned write
                 for (int d = 0; d < pl.ndep; d++)
-                    if (pl.dep_own[d] == k) pl.flags |= F_CONF;
-            if (tid > k && tid < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
+                    if (pl.dep_own[d] >= k) pl.flags |= F_CONF;
+            if (tid >= npos && tid < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
                 const int nl = S->nlog;
                 for (int q = 0; q < nl; q++) {
                     int sl = S->wlog[q] >> 1;
