@@ -39,6 +39,7 @@
 #define AT 1024            // threads per CTA = ops per batch
 #define EQ_CAP 4096        // eligible-slot ring (power of two)
 #define LK_XCAP 2048       // a candidate still matching after this many bytes is extended by the whole CTA
+#define LK_XCAP2 (1 << 20)  // ... unless more than two candidates are that long: then the warps go on in parallel up to here
 #define LK_CAP 256         // equal-tag entries the CTA-wide lookup collects; more: the warp walk
 #define FWD_ITERS 6         // forwarding rounds per batch; later collisions go serial
 #define MAXWALK 16384      // longer insert walks are left to the serial path
@@ -1173,6 +1174,8 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                         w.last = S->run.last;
                         const i64 lo = w.last > 0 ? w.last : 0;
                         const i64 maxf = end - pk;
+                        if (tid == 0) S->lk_n = 0;      // candidates still matching at the cap
+                        __syncthreads();
                         for (int q = wid; q < n_tot; q += AT / 32) {
                             const i64 off = __ldcg(toff + ((h + S->lk_pos[q]) & hmask));
                             i64 f = 0, r = 0;
@@ -1181,18 +1184,36 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                                 if (off < maxb) maxb = off;
                                 f = w.extend(pk, off, maxf < LK_XCAP ? maxf : LK_XCAP, true);
                                 r = w.extend(pk, off, maxb < LK_XCAP ? maxb : LK_XCAP, false);
+                                if (lane == 0 && ((f == LK_XCAP && maxf > LK_XCAP) || (r == LK_XCAP && maxb > LK_XCAP))) atomicAdd(&S->lk_n, 1);
                             }
                             if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; S->lk_off[q] = off; }
                         }
                         __syncthreads();
+                        // many long candidates (dense repeats, deep chains): the warps carry on in parallel, one candidate
+                        // each, up to LK_XCAP2; the whole CTA then only extends what is still matching there
+                        const i64 cap = S->lk_n > 2 ? (i64)LK_XCAP2 : (i64)LK_XCAP;
+                        if (cap != LK_XCAP) {
+                            for (int q = wid; q < n_tot; q += AT / 32) {
+                                const i64 off = S->lk_off[q];
+                                if (off >= pk) continue;
+                                i64 f = S->lk_f[q], r = S->lk_r[q];
+                                i64 maxb = pk - lo;
+                                if (off < maxb) maxb = off;
+                                if (f == LK_XCAP && maxf > LK_XCAP) f += w.extend(pk + LK_XCAP, off + LK_XCAP, (maxf < cap ? maxf : cap) - LK_XCAP, true);
+                                if (r == LK_XCAP && maxb > LK_XCAP) r += w.extend(pk - LK_XCAP, off - LK_XCAP, (maxb < cap ? maxb : cap) - LK_XCAP, false);
+                                __syncwarp();
+                                if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; }
+                            }
+                            __syncthreads();
+                        }
                         for (int q = 0; q < n_tot; q++) {
                             const i64 off = S->lk_off[q];
                             i64 f = S->lk_f[q], r = S->lk_r[q], m = 0;
                             if (off < pk) {
                                 i64 maxb = pk - lo;
                                 if (off < maxb) maxb = off;
-                                if (f == LK_XCAP && maxf > LK_XCAP) f += cta_extend(S, buf, pk + LK_XCAP, off + LK_XCAP, maxf - LK_XCAP, true);
-                                if (r == LK_XCAP && maxb > LK_XCAP) r += cta_extend(S, buf, pk - LK_XCAP, off - LK_XCAP, maxb - LK_XCAP, false);
+                                if (f == cap && maxf > cap) f += cta_extend(S, buf, pk + cap, off + cap, maxf - cap, true);
+                                if (r == cap && maxb > cap) r += cta_extend(S, buf, pk - cap, off - cap, maxb - cap, false);
                                 m = f + r < MRZ_MIN_MATCH ? 0 : f + r;
                             }
                             if (tid == 0) { S->lk_len[q] = m; S->lk_rev[q] = r; }
@@ -1232,25 +1253,35 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                         i64 lo_v = __shfl_up_sync(FULL, P0, 1);
                         if (lane == 0) lo_v = 0;
                         i64 tq = (hi_i < 32 ? a0 : a1) ^ lo_v;
-                        bool again = false;
+                        bool again = false, bail = false;
                         int lim = (w.end - w.p) < 32 ? (int)(w.end - w.p) : 32;   // positions b0..min(b0+31,end)
                         for (int j = 0; j < lim; j++) {
                             i64 tj = __shfl_sync(FULL, tq, j);
                             if ((tj & w.min_mask) != w.min_mask) continue;
+                            if (filt_query(filt, tj)) {   // an equal tag may exist: its lookup belongs to the whole CTA (next cut op)
+                                w.p = b0 + j - 1;
+                                bail = true;
+                                break;
+                            }
                             w.p = b0 + j;
                             if (w.op(b0 + j, tj, S->stk)) { again = true; break; }
                         }
                         if (again) continue;
-                        w.p = b0 + lim - 1;
+                        if (!bail) w.p = b0 + lim - 1;
                         break;
                     }
-                    i64 nli = ncand;
-                    if (!w.error && w.p < w.end && w.p + 1 < seg_hi) {
-                        i64 rel = w.p + 1 - seg_lo;
-                        i64 tile = rel / SCAN_TILE;
-                        nli = list_seek(cand_pos, tile_off[tile], tile_off[tile + 1], (u32)rel, lane);
+                    // re-synchronise with the candidate list - unless the batch simply carries on past the jump (below)
+                    bool stay = !w.error && w.nlog <= WLOG_CAP && w.min_mask == min_mask && w.ins_mask == ins_mask && w.p >= pk &&
+                                (i64)S->b_rel[nr - 1] > w.p - seg_lo;
+                    if (!stay) {
+                        i64 nli = ncand;
+                        if (!w.error && w.p < w.end && w.p + 1 < seg_hi) {
+                            i64 rel = w.p + 1 - seg_lo;
+                            i64 tile = rel / SCAN_TILE;
+                            nli = list_seek(cand_pos, tile_off[tile], tile_off[tile + 1], (u32)rel, lane);
+                        }
+                        if (lane == 0) S->li = nli;
                     }
-                    if (lane == 0) S->li = nli;
                     if (dbg && lane == 0) { dbg[30] += clock64() - c_dense; dbg[31] += 1; }
                 }
                 w.store(S->run);
@@ -1292,7 +1323,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             if (tid == npos && (pl.flags & F_FOLLOW)) pl.flags |= F_CONF;
             if (tid >= npos && tid < nr)   // a plan forwarded over the claim of op k / of a skipped op assumed that op's planned write
                 for (int d = 0; d < pl.ndep; d++)
-                    if (pl.dep_own[d] >= k) pl.flags |= F_CONF;
+                    if (pl.dep_own[d] >= k && pl.dep_own[d] < npos) pl.flags |= F_CONF;
             if (tid >= npos && tid < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
                 const int nl = S->nlog;
                 for (int q = 0; q < nl; q++) {
