@@ -315,6 +315,77 @@ struct Warp {
         }
     }
 
+    // find_stop for the serial path, by one warp: the first probe and 32 summary quad-words (4096 slots of summary) are
+    // fetched in ONE round trip, the candidate group in a second (16 lanes, one tag each); a stale candidate is repaired
+    // and the next one taken from the summary already in registers.  Same result as find_stop.
+    __device__ __forceinline__ i64 find_stop_warp(i64 h, int need, i64 &stop_tag) {
+        if (h >= hsize) return -1;
+        const i64 ngroups_all = hsize >> GRP_SHIFT;
+        i64 ngroups = ((h + MAXWALK) >> GRP_SHIFT) + 1;
+        if (ngroups > ngroups_all) ngroups = ngroups_all;
+        const u32 pass_bit = 1u << ((need > 15 ? 15 : need) - 1);
+        const i64 g0 = h >> GRP_SHIFT;
+        // round trip 1: the rest of the first group (lanes 0..15) and the summary of the groups behind it (all lanes)
+        i64 wbase = (g0 + 1) >> 3;                       // first summary quad-word (8 groups each)
+        uint4 w4 = __ldcg(reinterpret_cast<const uint4 *>(gsum + ((wbase + lane) << 2)));
+        {
+            const i64 sl = (g0 << GRP_SHIFT) + (lane & 15);
+            const i64 tg = __ldcg(ttag + sl);
+            int z = tz1(tg);
+            if (z < 0) z = 64;
+            const unsigned m = __ballot_sync(FULL, lane < 16 && sl >= h && z < need);
+            if (m) {
+                const int l = __ffs(m) - 1;
+                stop_tag = __shfl_sync(FULL, tg, l);
+                return (g0 << GRP_SHIFT) + l;
+            }
+            if ((h & (GRP - 1)) == 0) {                  // the whole group was seen: repair its summary
+                int zc = lane < 16 ? (z > 15 ? 15 : z) : 15;
+                for (int o = 8; o; o >>= 1) { const int u = __shfl_xor_sync(FULL, zc, o); zc = u < zc ? u : zc; }
+                if (lane == 0) sum_raise(gsum, g0, zc);
+            }
+        }
+        i64 g = g0 + 1;
+        for (;;) {
+            if (g >= ngroups) return -1;
+            // candidate groups of my quad-word: bit q set <=> group (wbase + lane) * 8 + q may hold a stop
+            const u32 wv[4] = {w4.x, w4.y, w4.z, w4.w};
+            unsigned cand = 0;
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                const i64 gg = ((wbase + lane) << 3) + q;
+                if (gg >= g && gg < ngroups && !((wv[q >> 1] >> ((q & 1) * 16)) & pass_bit)) cand |= 1u << q;
+            }
+            const unsigned lm = __ballot_sync(FULL, cand != 0);
+            if (!lm) {                                   // nothing in these 4096 slots: next window of summary
+                g = (wbase + 32) << 3;
+                wbase += 32;
+                if (g >= ngroups) return -1;
+                w4 = __ldcg(reinterpret_cast<const uint4 *>(gsum + ((wbase + lane) << 2)));
+                continue;
+            }
+            const int ll = __ffs(lm) - 1;
+            const unsigned cm = __shfl_sync(FULL, cand, ll);
+            const i64 gc = ((wbase + ll) << 3) + (__ffs(cm) - 1);
+            // round trip 2: the candidate group, one tag per lane
+            const i64 sl = (gc << GRP_SHIFT) + (lane & 15);
+            const i64 tg = __ldcg(ttag + sl);
+            int z = tz1(tg);
+            if (z < 0) z = 64;
+            const unsigned m = __ballot_sync(FULL, lane < 16 && z < need);
+            if (m) {
+                const int l = __ffs(m) - 1;
+                stop_tag = __shfl_sync(FULL, tg, l);
+                return (gc << GRP_SHIFT) + l;
+            }
+            int zc = lane < 16 ? (z > 15 ? 15 : z) : 15;
+            for (int o = 8; o; o >>= 1) { const int u = __shfl_xor_sync(FULL, zc, o); zc = u < zc ? u : zc; }
+            zc = __shfl_sync(FULL, zc, 0);
+            if (lane == 0) sum_raise(gsum, gc, zc);      // stale summary: repair, go on behind this group
+            g = gc + 1;
+        }
+    }
+
     // rzip.c:256-301 for a tag that has no equal entry in the table: every level of the displacement chain is a
     // summary-accelerated find_stop walk (all walks see the table before any write, as the reference's recursion does).
     // Returns false, having written nothing, when some level needs the general walk of insert().
@@ -328,7 +399,7 @@ struct Warp {
         for (;;) {
             const int z = tz1(ct);
             i64 stg;
-            const i64 sl = find_stop(ttag, gsum, ct & hmask, z > kb ? z : kb, hsize, stg);
+            const i64 sl = find_stop_warp(ct & hmask, z > kb ? z : kb, stg);
             if (sl < 0) return false;
             if (sp == 0 && n_eq > 0) {
                 const i64 rel = sl - (t & hmask);
@@ -356,12 +427,14 @@ struct Warp {
                 return true;
             }
             // rzip.c:275-277: a lesser occupant is re-inserted first; it must be unique (it meets only itself on its walk)
-            if (chain == 1 || sp >= 60 || filt_query(filt, stg ^ DUP_SALT)) return false;
+            if (chain == 1 || sp >= 60) return false;
+            const i64 ooff = __ldcg(toff + sl);          // independent of the duplicate-filter word: one round trip for both
+            if (filt_query(filt, stg ^ DUP_SALT)) return false;
             __syncwarp();
             if (lane == 0) { stk[3 * sp] = sl; stk[3 * sp + 1] = ct; stk[3 * sp + 2] = coff; }
             __syncwarp();
             sp++;
-            coff = __ldcg(toff + sl);
+            coff = ooff;
             ct = stg;
         }
     }
