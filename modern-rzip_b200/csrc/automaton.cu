@@ -11,25 +11,34 @@
 //   * the table is stored as two arrays (tags[], offs[]) instead of the reference's 16-byte
 //     entries: walks only ever look at tags, so a probe step moves half the bytes;
 //   * BATCHED SPECULATION: the next <=1024 candidate ops are *planned* in parallel, one thread
-//     each, against the live table read-only (insert walk, one level of displacement).  Plans are
-//     then committed in order: a plan is valid as long as no earlier op of the batch wrote a slot
-//     inside its read range (checked through a shared-memory hash of the batch's write slots)
-//     and it stays clear of the sweep window of clean_one_from_hash.  Everything else - a fraction
-//     of a percent of the ops - is executed by warp 0 on the live table with the reference
-//     semantics (32-slot probes, ballots for walk termination / equal-tag chains / the victim
-//     index, 256-byte-per-step match extension), after which later plans that read a slot it wrote
-//     are invalidated;
+//     each, against the live table read-only (insert walk, one level of displacement), then
+//     committed in order; the first op that cannot commit from its plan cuts the batch, runs
+//     exactly (below), and the batch carries on behind it - also behind an emitted match;
+//   * EXACT CONFLICT RULE: an insert only ever RAISES the trailing-one count of the slot it writes
+//     (empty / due-for-sweep -> >= need, lesser -> greater), so a walk that passed a slot still
+//     passes it: only a write to a walk's own STOP slot can change its outcome, and an entry due for
+//     sweeping stops every walk, so a slot of the sweep queue can only be a stop slot too.  Plans
+//     CLAIM their stop slots with atomicMin((epoch, op index)) in a 16 MiB array (no hash, no
+//     clearing); a plan is invalid iff an earlier op claims one of its stop slots;
+//   * FORWARDING: when the earlier op's tag is no stop for the later walk (and not equal to its
+//     tag), the later plan walks on from the next slot, re-claims and remembers the dependency;
+//     iterated to a fixed point with __syncthreads rounds;
 //   * TAG FILTER: a blocked Bloom filter over every tag inserted in this chunk (one 64-bit word,
 //     three bits per tag, no false negatives).  A negative answer proves that no entry with an
 //     equal tag exists, so find_best_match's walk to the end of the probe cluster - hundreds of
 //     slots at high mask levels - is skipped altogether, and lookup-only ops touch no table slot;
 //   * GROUP SUMMARY: the insert walk looks for the first slot whose tag has fewer trailing one bits
-//     than `need` (empty, due for sweeping, or lesser than the new tag: rzip.c:264-277).  Shared
-//     memory holds, per group of 16 slots, a 4-bit lower bound of the minimum trailing-one count
-//     in the group, so a walk skips whole groups without touching them and reads one group;
+//     than `need` (empty, due for sweeping, or lesser than the new tag: rzip.c:264-277).  Global
+//     memory (L2) holds, per group of 16 slots, a 16-bit thermometer of the minimum trailing-one
+//     count; a walk skips 128 slots per 128-bit summary load and reads one group (256-bit loads);
+//     lowering is one atomicAnd, repair one atomicOr;
 //   * TWINS: positions p and p+1 with equal tags (buf[p] == buf[p+31]) are planned as a pair;
 //   * the sweep of clean_one_from_hash is pre-resolved per batch: a parallel scan keeps a queue of
-//     the next eligible slots, so the n-th overflow of a batch zeroes the n-th queued slot.
+//     the next eligible slots, so the n-th overflow of a batch zeroes the n-th queued slot;
+//   * SERIAL OPS USE THE WHOLE CTA: the probe sequence of find_best_match is walked 4096 slots per
+//     step, equal-tag candidates are compared by the 32 warps in parallel (__ballot_sync / __ffs
+//     memcmp), long matches are extended 32 KiB per step by all threads; the insert walks of the
+//     cut op are warp-cooperative (first probe + 4096 slots of summary in one round trip).
 //   oracle/spec_model.c is the CPU model of the speculation rules; tests/test_spec_model.py proves
 //   it equivalent to the sequential restatement, tests/test_sim_parity.py runs this very file on
 //   the CPU emulator, tests/test_gpu_parity.py on the B200.
@@ -46,7 +55,6 @@
 #define WLOG_CAP 64
 #define GRP 16             // slots per summary group
 #define GRP_SHIFT 4
-#define CGRP_SHIFT 4       // conflict check: whole 16-slot groups inside a read range are tested as groups
 #define DUP_SALT 0x5bd1e9955bd1e995LL
 
 enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8, F_FOLLOW = 16, F_W2ELIG = 32, F_W1ELIG = 64 };
