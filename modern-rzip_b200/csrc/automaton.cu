@@ -484,7 +484,7 @@ struct Warp {
         nops++;
         i64 bofs = 0, brev = 0;
         i64 c0 = clock64();
-        const bool maybe = filt_query(filt, t);                       // negative: nothing to find
+        const bool maybe = pre_n >= 0 ? true : pre_n == -2 ? false : filt_query(filt, t);   // negative: nothing to find
         PROF(0, c0); c0 = clock64();
         i64 best = 0;
         if (maybe) best = pre_n >= 0 ? lookup_pre(bofs, brev, pre_n, pre_len, pre_rev, pre_off) : lookup(t, pp, bofs, brev);
@@ -1212,11 +1212,12 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
             }
             // ---- the lookup of op k (find_best_match, rzip.c:426-462) by the whole CTA: the probe sequence is walked
             // 4096 slots per step, equal tags are collected in slot order, and the 32 warps share the match_len calls
-            int pre_n = -1;
+            int pre_n = -2;   // -2: the filter says no equal tag; -1: ask / walk on the warp; >= 0: candidates compared
             const i64 c_lk0 = clock64();
             {
                 const i64 tk = S->b_tag[k], pk = seg_lo + (i64)S->b_rel[k];
                 if (filt_query(filt, tk)) {
+                    pre_n = -1;
                     const i64 h = tk & hmask;
                     if (tid == 0) S->lk_fe = 0x7fffffff;
                     __syncthreads();
@@ -1263,8 +1264,31 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                             if (off < pk) {
                                 i64 maxb = pk - lo;
                                 if (off < maxb) maxb = off;
-                                f = w.extend(pk, off, maxf < LK_XCAP ? maxf : LK_XCAP, true);
-                                r = w.extend(pk, off, maxb < LK_XCAP ? maxb : LK_XCAP, false);
+                                const i64 mf = maxf < LK_XCAP ? maxf : LK_XCAP, mb = maxb < LK_XCAP ? maxb : LK_XCAP;
+                                {   // the first 256 bytes of both directions in one round trip
+                                    const i64 kk = lane * 8;
+                                    u64 xf = 0, xb = 0;
+                                    if (kk < mf) xf = ld_u64_unaligned(buf, pk + kk) ^ ld_u64_unaligned(buf, off + kk);
+                                    if (kk < mb) xb = ld_u64_unaligned(buf, pk - 8 - kk) ^ ld_u64_unaligned(buf, off - 8 - kk);
+                                    unsigned mm = __ballot_sync(FULL, xf != 0);
+                                    if (mm) {
+                                        const int l = __ffs(mm) - 1;
+                                        int nb = xf ? ((__ffsll((long long)xf) - 1) >> 3) : 8;
+                                        nb = __shfl_sync(FULL, nb, l);
+                                        f = l * 8 + nb;
+                                    } else
+                                        f = mf > 256 ? 256 + w.extend(pk + 256, off + 256, mf - 256, true) : mf;
+                                    if (f > mf) f = mf;
+                                    mm = __ballot_sync(FULL, xb != 0);
+                                    if (mm) {
+                                        const int l = __ffs(mm) - 1;
+                                        int nb = xb ? (__clzll((long long)xb) >> 3) : 8;
+                                        nb = __shfl_sync(FULL, nb, l);
+                                        r = l * 8 + nb;
+                                    } else
+                                        r = mb > 256 ? 256 + w.extend(pk - 256, off - 256, mb - 256, false) : mb;
+                                    if (r > mb) r = mb;
+                                }
                                 if (lane == 0 && ((f == LK_XCAP && maxf > LK_XCAP) || (r == LK_XCAP && maxb > LK_XCAP))) atomicAdd(&S->lk_n, 1);
                             }
                             if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; S->lk_off[q] = off; }
@@ -1336,10 +1360,12 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                         i64 tq = (hi_i < 32 ? a0 : a1) ^ lo_v;
                         bool again = false, bail = false;
                         int lim = (w.end - w.p) < 32 ? (int)(w.end - w.p) : 32;   // positions b0..min(b0+31,end)
+                        // one round trip for the 32 filter words (op() asks again: a tag inserted inside this window is seen there)
+                        const unsigned fmask = __ballot_sync(FULL, filt_query(filt, tq));
                         for (int j = 0; j < lim; j++) {
                             i64 tj = __shfl_sync(FULL, tq, j);
                             if ((tj & w.min_mask) != w.min_mask) continue;
-                            if (filt_query(filt, tj)) {   // an equal tag may exist: its lookup belongs to the whole CTA (next cut op)
+                            if ((fmask >> j) & 1u) {   // an equal tag may exist: its lookup belongs to the whole CTA (next cut op)
                                 w.p = b0 + j - 1;
                                 bail = true;
                                 break;
