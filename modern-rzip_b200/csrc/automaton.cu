@@ -50,6 +50,7 @@
 #define LK_XCAP 2048       // a candidate still matching after this many bytes is extended by the whole CTA
 #define LK_XCAP2 (1 << 20)  // ... unless more than two candidates are that long: then the warps go on in parallel up to here
 #define LK_CAP 256         // equal-tag entries the CTA-wide lookup collects; more: the warp walk
+#define DENSE_LOOP 0       // 1: after an emission warp 0 examines the next 32 positions from the bytes (measured slower than letting the batch carry on)
 #define FWD_ITERS 6         // forwarding rounds per batch; later collisions go serial
 #define MAXWALK 16384      // longer insert walks are left to the serial path
 #define WLOG_CAP 64
@@ -1344,7 +1345,7 @@ k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gs
                 if (jumped && !w.error) {
                     // dense-match regime: examine the next positions directly from the bytes until a
                     // window of 32 positions passes without an emission, then re-synchronise with the list
-                    for (;;) {
+                    for (; DENSE_LOOP;) {
                         if (w.error || w.p >= w.end) break;
                         i64 b0 = w.p + 1;                       // positions b0 + lane
                         i64 v0 = S->hx[__ldg(buf + b0 + lane)];
