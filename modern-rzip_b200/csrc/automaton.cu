@@ -60,7 +60,11 @@
 
 enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8, F_FOLLOW = 16, F_W2ELIG = 32, F_W1ELIG = 64 };
 #define MAXDEP 3            // claimed slots a plan may walk past (forwarding)
+#ifdef MRZ_CUSIM
+#define CLAIM_EPOCH_MAX 700u       // the CPU-emulator tests exercise the wrap-around (wipe + restart) path
+#else
 #define CLAIM_EPOCH_MAX 0x1FFFF0u
+#endif
 __device__ __forceinline__ unsigned claim_key(unsigned epoch, int j, int is_w1) { return ((0x1FFFFFu - epoch) << 11) | ((unsigned)j << 1) | (unsigned)is_w1; }
 
 // Blocked Bloom filter over inserted tags: word index and 3-bit mask (oracle/spec_model.c filt_hash).
