@@ -28,6 +28,8 @@ import numpy as np
 if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
     os.environ["NCCL_DEBUG"] = "WARN"     # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
 
+_REAL_STDOUT = 1
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "modern-rzip_b200"))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -197,7 +199,16 @@ def run_reference_sample(sample, steps, warmup, level=LEVEL):
     return times
 
 
+def emit_line(line):
+    """The ONE JSON line goes to the real stdout; anything libraries print to fd 1 (NCCL's banner) was sent to stderr."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)                         # library chatter on fd 1 -> stderr; emit_line() writes to the saved stdout
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=2)
@@ -245,7 +256,7 @@ def main():
                                            "(1 hash_search thread + checksum/writer helpers), host has %d cores"
                                            % (sample_n >> 20, os.cpu_count())},
                 "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit_line(line)
         return 0
 
     # ---------------- B200 arm
@@ -349,7 +360,7 @@ def main():
                          "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": (measured_traffic() or {}).get("dram_bytes_per_launch"),
                          "traffic_source": (measured_traffic() or {}).get("source"),
-                         "launches_per_step": None,
+                         "launches_per_step": int(launches) // max(1, args.steps),
                          "algorithmic_bytes_per_step": int(b_alg),
                          "share_of_step": ms_auto / ms_k if ms_k else None,
                          "ms_per_step": {"tag_scan": ms_scan / args.steps, "automaton": ms_auto / args.steps,
@@ -368,7 +379,7 @@ def main():
                                           "file->file in /dev/shm (1 hash_search thread + helpers); host has %d cores"
                                           % (sample_n >> 20, os.cpu_count())}
     if rank == 0:
-        print(json.dumps(line))
+        emit_line(line)
     ctx.close()
     if multi:
         dist.destroy_process_group()
