@@ -54,8 +54,8 @@
 #define FWD_ITERS 6         // forwarding rounds per batch; later collisions go serial
 #define MAXWALK 16384      // longer insert walks are left to the serial path
 #define WLOG_CAP 64
-#define GRP 16             // slots per summary group
-#define GRP_SHIFT 4
+#define GRP 8              // slots per summary group (= one 64-byte read of tags)
+#define GRP_SHIFT 3
 #define DUP_SALT 0x5bd1e9955bd1e995LL
 
 enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8, F_FOLLOW = 16, F_W2ELIG = 32, F_W1ELIG = 64 };
@@ -342,19 +342,19 @@ struct Warp {
         i64 wbase = (g0 + 1) >> 3;                       // first summary quad-word (8 groups each)
         uint4 w4 = __ldcg(reinterpret_cast<const uint4 *>(gsum + ((wbase + lane) << 2)));
         {
-            const i64 sl = (g0 << GRP_SHIFT) + (lane & 15);
+            const i64 sl = (g0 << GRP_SHIFT) + (lane & (GRP - 1));
             const i64 tg = __ldcg(ttag + sl);
             int z = tz1(tg);
             if (z < 0) z = 64;
-            const unsigned m = __ballot_sync(FULL, lane < 16 && sl >= h && z < need);
+            const unsigned m = __ballot_sync(FULL, lane < GRP && sl >= h && z < need);
             if (m) {
                 const int l = __ffs(m) - 1;
                 stop_tag = __shfl_sync(FULL, tg, l);
                 return (g0 << GRP_SHIFT) + l;
             }
             if ((h & (GRP - 1)) == 0) {                  // the whole group was seen: repair its summary
-                int zc = lane < 16 ? (z > 15 ? 15 : z) : 15;
-                for (int o = 8; o; o >>= 1) { const int u = __shfl_xor_sync(FULL, zc, o); zc = u < zc ? u : zc; }
+                int zc = lane < GRP ? (z > 15 ? 15 : z) : 15;
+                for (int o = GRP / 2; o; o >>= 1) { const int u = __shfl_xor_sync(FULL, zc, o); zc = u < zc ? u : zc; }
                 if (lane == 0) sum_raise(gsum, g0, zc);
             }
         }
@@ -381,18 +381,18 @@ struct Warp {
             const unsigned cm = __shfl_sync(FULL, cand, ll);
             const i64 gc = ((wbase + ll) << 3) + (__ffs(cm) - 1);
             // round trip 2: the candidate group, one tag per lane
-            const i64 sl = (gc << GRP_SHIFT) + (lane & 15);
+            const i64 sl = (gc << GRP_SHIFT) + (lane & (GRP - 1));
             const i64 tg = __ldcg(ttag + sl);
             int z = tz1(tg);
             if (z < 0) z = 64;
-            const unsigned m = __ballot_sync(FULL, lane < 16 && z < need);
+            const unsigned m = __ballot_sync(FULL, lane < GRP && z < need);
             if (m) {
                 const int l = __ffs(m) - 1;
                 stop_tag = __shfl_sync(FULL, tg, l);
                 return (gc << GRP_SHIFT) + l;
             }
-            int zc = lane < 16 ? (z > 15 ? 15 : z) : 15;
-            for (int o = 8; o; o >>= 1) { const int u = __shfl_xor_sync(FULL, zc, o); zc = u < zc ? u : zc; }
+            int zc = lane < GRP ? (z > 15 ? 15 : z) : 15;
+            for (int o = GRP / 2; o; o >>= 1) { const int u = __shfl_xor_sync(FULL, zc, o); zc = u < zc ? u : zc; }
             zc = __shfl_sync(FULL, zc, 0);
             if (lane == 0) sum_raise(gsum, gc, zc);      // stale summary: repair, go on behind this group
             g = gc + 1;

@@ -227,7 +227,7 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     CK(cudaMemset(ctx->d_buf_alloc, 0, MRZ_PAD));
     ctx->tab_slots = (i64)64 * 65536;  // largest levels[].mb_used = 64 MiB
     CK(cudaMalloc(&ctx->d_tab, (size_t)(ctx->tab_slots + 32) * 16));  // + slack for 4-slot probe loads
-    CK(cudaMalloc(&ctx->d_gsum, (size_t)(ctx->tab_slots / 16 / 2 + 1024) * 4));   // 16-bit thermometer per 16 slots
+    CK(cudaMalloc(&ctx->d_gsum, (size_t)(ctx->tab_slots / 8 / 2 + 1024) * 4));   // 16-bit thermometer per 8 slots (automaton.cu GRP)
     CK(cudaMalloc(&ctx->d_filt, (size_t)MRZ_FILT_WORDS * 8));
     CK(cudaMalloc(&ctx->d_claim, (size_t)(ctx->tab_slots + 32) * 4));
     CK(cudaMalloc(&ctx->d_gstate, mrz_grid_state_bytes()));
@@ -340,7 +340,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaMemcpyAsync(ctx->d_hidx, prm->hash_index, 256 * 8, cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(ctx->d_st, &h, sizeof h, cudaMemcpyHostToDevice, s));
     CK(cudaMemsetAsync(ctx->d_tab, 0, (size_t)(ctx->tab_slots + 32) * 16, s));  // rzip.c:518-519
-    CK(cudaMemsetAsync(ctx->d_gsum, 0, (size_t)(ctx->tab_slots / 16 / 2 + 1024) * 4, s));
+    CK(cudaMemsetAsync(ctx->d_gsum, 0, (size_t)(ctx->tab_slots / 8 / 2 + 1024) * 4, s));
     CK(cudaMemsetAsync(ctx->d_filt, 0, (size_t)MRZ_FILT_WORDS * 8, s));
     CK(cudaMemsetAsync(ctx->d_claim, 0xff, (size_t)(ctx->tab_slots + 32) * 4, s));
     if (ctx->grid_g) CK(cudaMemsetAsync(ctx->d_gstate, 0, mrz_grid_state_bytes(), s));
