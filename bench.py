@@ -204,6 +204,132 @@ def emit_line(line):
     os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
 
 
+CHAIN = [1, 2, 2, 2, 3, 4, 6, 16, 32, 128]     # levels[].max_chain_len, rzip.c:65-73
+
+
+def variants_bench(args, rank, world, local_rank, config, barrier):
+    """One input of world x chunks_per_gpu chunks (chunk k -> rank k mod world).  Every chunk is resident on its GPU and
+    its automaton runs for all max_chain_len values of victim_round_in concurrently (one CTA + one table each); the
+    chunks of a rank run concurrently too (one host thread each).  The chain is resolved with one all-gather
+    (shard.run_sharded_variants) and only the chosen variant of each chunk is emitted.  Timed by the wall clock between
+    barriers (the critical path includes the host threads and the all-gather); max over ranks."""
+    import torch
+    import mrz_py
+    import helpers as H
+    import shard
+    multi = world > 1
+    if multi:
+        import torch.distributed as dist
+    n, C_, V = args.size, args.chunks_per_gpu, CHAIN[args.level]
+    n_chunks = world * C_
+    hidx, cb = H.hash_index(), H.chunk_bytes(n)
+    prm = mrz_py.make_params(args.level, cb, hidx, 0)
+    sets, pins = [], []
+    for c in range(C_):
+        k = c * world + rank
+        vs = mrz_py.VariantSet(local_rank, n, V)
+        pin = mrz_py.PinnedBuffer(n)
+        GENS[args.workload](n, seed=2 + k, out=pin.array)
+        sets.append(vs)
+        pins.append(pin)
+    pin_s0 = mrz_py.PinnedBuffer(n // 2 + 64)
+    pin_s1 = mrz_py.PinnedBuffer(n + 16)
+    chunks = [None] * n_chunks
+    launches = 0
+    last = {}
+
+    def step(with_copies):
+        nonlocal launches
+        outs = [None] * C_
+
+        def work(c):
+            if with_copies:
+                sets[c].upload(pins[c].array)
+            outs[c] = sets[c].run(n, prm)
+        th = [threading.Thread(target=work, args=(c,)) for c in range(1, C_)]
+        for t in th:
+            t.start()
+        work(0)
+        for t in th:
+            t.join()
+        it = iter(range(C_))
+        chosen, vr = shard.run_sharded_variants(
+            chunks, lambda _c: [r.victim_round_out for r in outs[next(it)]], V, rank, world, device="cuda")
+        b_alg = 0
+        for c in range(C_):
+            v = chosen[c * world + rank]
+            launches += sum(int(r.gpu_launches) for r in outs[c])
+            if with_copies:
+                r, s0, s1 = sets[c].emit(v, pin_s0.array, pin_s1.array)
+            else:
+                r = sets[c].ctxs[v].run_emit()
+            launches += int(r.gpu_launches) - int(outs[c][v].gpu_launches)
+            b_alg += n + r.s0_len + r.s1_len
+            last[c] = (r, v, max(float(x.ms_automaton) for x in outs[c]), float(outs[c][v].ms_automaton))
+        return b_alg, vr
+
+    for c in range(C_):
+        sets[c].upload(pins[c].array)
+    for _ in range(args.warmup):
+        step(False)
+    clocks = ClockSampler(local_rank)
+    barrier()
+    clocks.start()
+    launches = 0
+    t0 = time.perf_counter()
+    b_alg = 0
+    for _ in range(args.steps):
+        b, vr_final = step(False)
+        b_alg += b
+    barrier()
+    wall_k = time.perf_counter() - t0
+    clk = clocks.stop()
+    barrier()
+    t0 = time.perf_counter()
+    d2h = 0
+    for _ in range(args.steps):
+        step(True)
+    barrier()
+    wall_e = time.perf_counter() - t0
+    tk = torch.tensor([wall_k, wall_e, float(b_alg)], dtype=torch.float64, device="cuda")
+    if multi:
+        tmax = tk.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tk, op=dist.ReduceOp.SUM)
+        t_k, t_e, b_all = float(tmax[0]), float(tmax[1]), float(tk[2])
+    else:
+        t_k, t_e, b_all = [float(x) for x in tk.tolist()]
+    total_bytes = n * n_chunks * args.steps
+    peak, peak_kind = hbm_peak()
+    config["workload"] = "%s, ONE input of %d chunks x %.2f GiB (chunk k on GPU k mod %d, %d chunk(s) resident per GPU), " \
+        "rzip level %d, all %d victim_round_in variants of every chunk run side by side, chain resolved by one all-gather" % (
+            KINDS[args.workload], n_chunks, n / GIB, world, C_, args.level, V)
+    config["timing"] = "wall clock between barriers, max over ranks"
+    config["automata_per_gpu"] = C_ * V
+    line = {"metric": "rzip pre-process input GB/s", "value": total_bytes / t_k / 1e9, "unit": "GB/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_k / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int64",
+            "data": "synthetic", "config": config,
+            "e2e": {"value": total_bytes / t_e / 1e9, "unit": "GB/s", "h2d_bytes_per_step": n * C_,
+                    "d2h_bytes_per_step": int(sum(int(last[c][0].s0_len + last[c][0].s1_len) for c in range(C_)))},
+            "gpu_launches": int(launches), "clocks": clk,
+            "roofline": {"bound": "hbm", "kernel": "k_automaton x %d concurrent" % (C_ * V),
+                         "achieved": b_all / t_k / 1e9 / world, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
+                         "frac": b_all / t_k / 1e9 / world / peak, "traffic": None,
+                         "note": "algorithmic bytes of the CHOSEN variants of one GPU's chunks / wall time of the step"},
+            "variants": {"per_chunk": V, "final_victim_round": int(vr_final),
+                         "chosen": {str(c * world + rank): int(last[c][1]) for c in range(C_)},
+                         "ms_automaton_slowest_variant": {str(c * world + rank): last[c][2] for c in range(C_)},
+                         "ms_automaton_chosen_variant": {str(c * world + rank): last[c][3] for c in range(C_)}}}
+    if rank == 0:
+        emit_line(line)
+    for vs in sets:
+        vs.close()
+    if multi:
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     global _REAL_STDOUT
     sys.stdout.flush()
@@ -220,6 +346,10 @@ def main():
     ap.add_argument("--workload", default="tar", choices=["tar", "vm", "dense"], help="tar: configs[1] data; vm: configs[2] data; dense: configs[4] data")
     ap.add_argument("--level", type=int, default=LEVEL, help="rzip level (index into levels[], rzip.c:65-73)")
     ap.add_argument("--one-file", action="store_true", help="N>1: the ranks' chunks are consecutive chunks of one input (exact carry)")
+    ap.add_argument("--variants", action="store_true",
+                    help="chunks of ONE input, chunk k on rank k mod N, every chunk run for all max_chain_len values of "
+                         "victim_round_in side by side (mrz_run_variants); one all-gather resolves the chain, no re-runs")
+    ap.add_argument("--chunks-per-gpu", type=int, default=1, help="--variants: chunks resident and running concurrently per GPU")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -274,6 +404,9 @@ def main():
         if multi:
             dist.barrier()
         torch.cuda.synchronize()
+
+    if args.variants:
+        return variants_bench(args, rank, world, local_rank, config, barrier)
 
     hidx = H.hash_index()
     cb = H.chunk_bytes(n)

@@ -72,6 +72,24 @@ int mrz_upload(mrz_ctx *ctx, const uint8_t *chunk, int64_t n);                 /
 int mrz_run_resident(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result *res); /* kernels only */
 int mrz_download(mrz_ctx *ctx, uint8_t *s0, int64_t s0_cap, uint8_t *s1, int64_t s1_cap); /* D2H */
 
+/* Variant-parallel chunks (the multi-GPU / multi-chunk answer to the one scalar that links chunks: the
+ * function-local `static victim_round` of insert_hash, rzip.c:259, which enters the next chunk and is
+ * output-relevant as soon as that chunk evicts a victim, rzip.c:278-291).  Instead of waiting for the previous
+ * chunk's value, the automaton of a resident chunk is run for EVERY possible victim_round_in (0 .. max_chain_len-1,
+ * levels[] rzip.c:65-73) side by side — one CTA, one hash table and one token list per variant; the automaton uses
+ * 1 of 148 SMs — and the caller keeps the variant the chain selects.
+ *   mrz_ctx_create_variant: a context that shares the parent's chunk bytes and stream-1 buffer and owns its own
+ *                           table / filter / claims / candidate lists / tokens (≈ 0.3 GB + 0.1 x max_chunk).
+ *   mrz_run_automaton:      hash_search up to the token list (no streams): counters, victim_round_out, n_ops.
+ *   mrz_run_emit:           put_literal/put_match/CRC (rzip.c:161-227, :617-666) for the tokens of the last
+ *                           mrz_run_automaton of this context; then mrz_download from the same context.
+ *   mrz_run_variants:       ctxs[v] runs with victim_round_in = v (prm->victim_round_in is ignored), all nvar
+ *                           concurrently on the device; res[v] as mrz_run_automaton.  ctxs[0] may be the parent. */
+int mrz_ctx_create_variant(mrz_ctx *parent, mrz_ctx **out);
+int mrz_run_automaton(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result *res);
+int mrz_run_emit(mrz_ctx *ctx, mrz_result *res);
+int mrz_run_variants(mrz_ctx *const *ctxs, int nvar, int64_t n, const mrz_params *prm, mrz_result *res);
+
 /* Pinned host memory for the e2e path (cudaHostAlloc); optional. */
 void *mrz_host_alloc(int64_t bytes);
 void mrz_host_free(void *p);

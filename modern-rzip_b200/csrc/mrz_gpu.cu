@@ -8,6 +8,10 @@
 #include <stdlib.h>
 #include <string.h>
 #include <string>
+#ifndef MRZ_CUSIM
+#include <thread>
+#endif
+#include <vector>
 
 #include "../../include/mrz_gpu.h"
 #include "mrz_common.cuh"
@@ -38,7 +42,8 @@ struct mrz_ctx {
     int device;
     i64 max_chunk;
     cudaStream_t stream;
-    cudaEvent_t ev[4];
+    cudaEvent_t ev[6];
+    mrz_ctx *parent;     // variant context (mrz_ctx_create_variant): d_buf and d_s1 belong to the parent
     // device buffers
     u8 *d_buf_alloc, *d_buf;  // chunk with MRZ_PAD slack on both sides
     i64 *d_tab; i64 tab_slots;   // tags[tab_slots + 32] then offs[tab_slots + 32]
@@ -63,6 +68,9 @@ struct mrz_ctx {
     u32 *h_crc; i64 h_crc_cap;
     // last run
     i64 last_n, last_s0, last_s1, last_ntok;
+    // between mrz_run_automaton and mrz_run_emit
+    AutoState last_state; int last_cb; bool have_tokens;
+    float ms_scan, ms_auto, ms_phase_a; int launches;
     std::string err;
 };
 
@@ -201,6 +209,7 @@ static int ensure_s0(mrz_ctx *ctx, i64 bytes) {
 extern "C" void mrz_ctx_destroy(mrz_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
+    if (ctx->parent) ctx->d_buf_alloc = nullptr, ctx->d_s1 = nullptr;   // borrowed from the parent
     cudaFree(ctx->d_buf_alloc); cudaFree(ctx->d_tab); cudaFree(ctx->d_gsum); cudaFree(ctx->d_filt); cudaFree(ctx->d_claim); cudaFree(ctx->d_planio); cudaFree(ctx->d_gstate); cudaFree(ctx->d_hidx); cudaFree(ctx->d_st);
     cudaFree(ctx->d_tile_cnt); cudaFree(ctx->d_tile_off); cudaFree(ctx->d_cand_pos); cudaFree(ctx->d_cand_tag);
     cudaFree(ctx->d_toks); cudaFree(ctx->d_a0); cudaFree(ctx->d_a1); cudaFree(ctx->d_off0); cudaFree(ctx->d_off1);
@@ -213,8 +222,9 @@ extern "C" void mrz_ctx_destroy(mrz_ctx *ctx) {
     delete ctx;
 }
 
-static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
+static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk, mrz_ctx *parent) {
     CK(cudaSetDevice(device));
+    ctx->parent = parent;
     crc_host_init();
     mrz_crc_upload_consts(&g_crc);
     CK(cudaGetLastError());
@@ -222,9 +232,14 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     ctx->max_chunk = max_chunk;
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     for (auto &e : ctx->ev) CK(cudaEventCreate(&e));
-    CK(cudaMalloc(&ctx->d_buf_alloc, (size_t)max_chunk + 2 * MRZ_PAD + 64));
-    ctx->d_buf = ctx->d_buf_alloc + MRZ_PAD;
-    CK(cudaMemset(ctx->d_buf_alloc, 0, MRZ_PAD));
+    if (parent) {
+        ctx->d_buf_alloc = parent->d_buf_alloc;
+        ctx->d_buf = parent->d_buf;
+    } else {
+        CK(cudaMalloc(&ctx->d_buf_alloc, (size_t)max_chunk + 2 * MRZ_PAD + 64));
+        ctx->d_buf = ctx->d_buf_alloc + MRZ_PAD;
+        CK(cudaMemset(ctx->d_buf_alloc, 0, MRZ_PAD));
+    }
     ctx->tab_slots = (i64)64 * 65536;  // largest levels[].mb_used = 64 MiB
     CK(cudaMalloc(&ctx->d_tab, (size_t)(ctx->tab_slots + 32) * 16));  // + slack for 4-slot probe loads
     CK(cudaMalloc(&ctx->d_gsum, (size_t)(ctx->tab_slots / 8 / 2 + 1024) * 4));   // 16-bit thermometer per 8 slots (automaton.cu GRP)
@@ -268,7 +283,11 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     CK(cudaMalloc(&ctx->d_cand_tag, (size_t)(SEG_CAND_CAP + 64) * sizeof(i64)));
     CK(cudaMalloc(&ctx->d_tot, sizeof(EmitTotals)));
     if (getenv("MRZ_PROFILE")) CK(cudaMalloc(&ctx->d_dbg, 40 * 8));
-    CK(cudaMalloc(&ctx->d_s1, (size_t)max_chunk + 64));
+    if (parent) {
+        ctx->d_s1 = parent->d_s1;
+    } else {
+        CK(cudaMalloc(&ctx->d_s1, (size_t)max_chunk + 64));
+    }
     ctx->s1_cap = max_chunk + 64;
     i64 nblk = max_chunk / 16384 + 1;
     CK(cudaMalloc(&ctx->d_crc_part, (size_t)nblk * 4));
@@ -279,6 +298,7 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk) {
     if (!ctx->h_crc) return MRZ_E_NOMEM;
     int rc;
     if ((rc = ensure_tokens(ctx, max_chunk / 256 + 1024))) return rc;
+    if (parent) return 0;   // a variant allocates its emission buffers only if it is the one chosen to emit
     if ((rc = ensure_items(ctx, max_chunk / 256 + 1024))) return rc;
     if ((rc = ensure_s0(ctx, max_chunk / 32 + 4096))) return rc;
     return 0;
@@ -294,7 +314,21 @@ extern "C" int mrz_ctx_create(int device, int64_t max_chunk, mrz_ctx **out) {
     }
     if (device < 0 || device >= n) { g_err = "bad device index"; return MRZ_E_ARG; }
     mrz_ctx *ctx = new mrz_ctx();
-    int rc = ctx_create_impl(ctx, device, max_chunk);
+    int rc = ctx_create_impl(ctx, device, max_chunk, nullptr);
+    if (rc) {
+        g_err = ctx->err;
+        mrz_ctx_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return 0;
+}
+
+extern "C" int mrz_ctx_create_variant(mrz_ctx *parent, mrz_ctx **out) {
+    if (!out || !parent || parent->parent) return MRZ_E_ARG;
+    *out = nullptr;
+    mrz_ctx *ctx = new mrz_ctx();
+    int rc = ctx_create_impl(ctx, parent->device, parent->max_chunk, parent);
     if (rc) {
         g_err = ctx->err;
         mrz_ctx_destroy(ctx);
@@ -314,8 +348,9 @@ extern "C" int mrz_upload(mrz_ctx *ctx, const uint8_t *chunk, int64_t n) {
 }
 
 // One attempt with the current token capacity.  Returns 1 when the token buffer overflowed.
-static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res) {
+static int run_phase_a(mrz_ctx *ctx, i64 n, const mrz_params *prm) {
     cudaStream_t s = ctx->stream;
+    ctx->have_tokens = false;
     const int L = prm->level;
     AutoState h;
     memset(&h, 0, sizeof h);
@@ -334,7 +369,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     { const char *bj = getenv("MRZ_BMAX_JUMP"); h.pad0 = bj ? atoi(bj) : 0; }   // batch size right after an emission (tuning)
     h.done = h.end <= 0 ? 1 : 0;
     int launches = 0;
-    float ms_scan = 0, ms_auto = 0, ms_emit = 0, ms_total = 0;
+    float ms_scan = 0, ms_auto = 0;
 
     CK(cudaEventRecord(ctx->ev[0], s));
     CK(cudaMemcpyAsync(ctx->d_hidx, prm->hash_index, 256 * 8, cudaMemcpyHostToDevice, s));
@@ -344,7 +379,6 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaMemsetAsync(ctx->d_filt, 0, (size_t)MRZ_FILT_WORDS * 8, s));
     CK(cudaMemsetAsync(ctx->d_claim, 0xff, (size_t)(ctx->tab_slots + 32) * 4, s));
     if (ctx->grid_g) CK(cudaMemsetAsync(ctx->d_gstate, 0, mrz_grid_state_bytes(), s));
-    CK(cudaMemsetAsync(ctx->d_tot, 0, sizeof(EmitTotals), s));
     if (ctx->d_dbg) CK(cudaMemsetAsync(ctx->d_dbg, 0, 40 * 8, s));
     launches += 2;
     // CRC of the chunk (independent of the automaton)
@@ -415,12 +449,51 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
                 (long long)ctx->h_dbg[19], (long long)ctx->h_dbg[32], (long long)ctx->h_dbg[33], (long long)ctx->h_dbg[34],
                 (long long)ctx->h_dbg[35], (long long)ctx->h_dbg[36], (long long)ctx->h_dbg[37], (long long)ctx->h_dbg[38], (long long)ctx->h_dbg[39]);
     }
+    CK(cudaEventRecord(ctx->ev[4], s));
+    CK(cudaStreamSynchronize(s));
+    cudaEventElapsedTime(&ctx->ms_phase_a, ctx->ev[0], ctx->ev[4]);
+    ctx->last_state = h;
+    ctx->last_cb = prm->chunk_bytes;
+    ctx->last_n = n; ctx->last_ntok = h.ntok; ctx->last_s0 = ctx->last_s1 = 0;
+    ctx->ms_scan = ms_scan; ctx->ms_auto = ms_auto; ctx->launches = launches;
+    ctx->have_tokens = true;
+    return 0;
+}
+
+// Counters of a chunk whose automaton has run (everything but the stream lengths and the CRC).
+static void fill_automaton_result(const mrz_ctx *ctx, mrz_result *res) {
+    const AutoState &h = ctx->last_state;
+    memset(res, 0, sizeof *res);
+    res->tag_hits = h.tag_hits;
+    res->tag_misses = h.tag_misses;
+    res->inserts = h.inserts;
+    res->matches = h.ntok;            // un-split matches; the emission reports rzip.c's split count
+    res->victim_round_out = h.victim_round;
+    res->victim_events = h.victim_events;
+    res->final_min_mask = h.min_mask;
+    res->n_ops = h.n_ops;
+    res->ms_kernels = ctx->ms_phase_a;
+    res->ms_tagscan = ctx->ms_scan;
+    res->ms_automaton = ctx->ms_auto;
+    res->gpu_launches = ctx->launches;
+}
+
+// Emission of the tokens the last run_phase_a of this context left behind.
+static int run_phase_b(mrz_ctx *ctx, mrz_result *res) {
+    cudaStream_t s = ctx->stream;
+    if (!ctx->have_tokens) { ctx->err = "mrz_run_emit without a preceding automaton run"; return MRZ_E_ARG; }
+    const AutoState &h = ctx->last_state;
+    const i64 n = ctx->last_n;
+    const int chunk_bytes = ctx->last_cb;
+    int launches = ctx->launches;
+    float ms_emit = 0;
     // ---- emission ----
     CK(cudaEventRecord(ctx->ev[1], s));
+    CK(cudaMemsetAsync(ctx->d_tot, 0, sizeof(EmitTotals), s));
     i64 m = h.ntok, items = m + 1;
     int rc;
     if ((rc = ensure_items(ctx, items))) return rc;
-    mrz_launch_item_sizes(ctx->d_toks, m, n, prm->chunk_bytes, ctx->d_a0, ctx->d_a1, ctx->d_tot, s);
+    mrz_launch_item_sizes(ctx->d_toks, m, n, chunk_bytes, ctx->d_a0, ctx->d_a1, ctx->d_tot, s);
     launches++;
     mrz_launch_exclusive_scan(ctx->d_a0, ctx->d_off0, items, ctx->d_bsum, ctx->d_off0 + items, s, &launches);
     mrz_launch_exclusive_scan(ctx->d_a1, ctx->d_off1, items, ctx->d_bsum, ctx->d_off1 + items, s, &launches);
@@ -448,7 +521,7 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     u32 crc = raw ^ crc_shift(0xFFFFFFFFu, (u64)n) ^ 0xFFFFFFFFu;
     CK(cudaMemcpyAsync(ctx->d_crc_misc + 1, &crc, 4, cudaMemcpyHostToDevice, s));
     if ((rc = ensure_s0(ctx, totals[0]))) return rc;
-    mrz_launch_emit(ctx->d_buf, ctx->d_toks, m, n, prm->chunk_bytes, ctx->d_off0, ctx->d_off1, totals[1], ctx->d_s0,
+    mrz_launch_emit(ctx->d_buf, ctx->d_toks, m, n, chunk_bytes, ctx->d_off0, ctx->d_off1, totals[1], ctx->d_s0,
                     ctx->d_s1, ctx->d_crc_misc + 1, s, &launches);
     EmitTotals tot;
     CK(cudaMemcpyAsync(&tot, ctx->d_tot, sizeof tot, cudaMemcpyDeviceToHost, s));
@@ -456,47 +529,89 @@ static int run_once(mrz_ctx *ctx, i64 n, const mrz_params *prm, mrz_result *res)
     CK(cudaStreamSynchronize(s));
     CK(cudaGetLastError());
     cudaEventElapsedTime(&ms_emit, ctx->ev[1], ctx->ev[2]);
-    cudaEventElapsedTime(&ms_total, ctx->ev[0], ctx->ev[2]);
 
-    memset(res, 0, sizeof *res);
+    fill_automaton_result(ctx, res);
     res->s0_len = totals[0];
     res->s1_len = totals[1];
     res->matches = tot.matches;
     res->match_bytes = tot.match_bytes;
     res->literals = tot.literals;
     res->literal_bytes = totals[1];
-    res->tag_hits = h.tag_hits;
-    res->tag_misses = h.tag_misses;
-    res->inserts = h.inserts;
-    res->victim_round_out = h.victim_round;
-    res->victim_events = h.victim_events;
-    res->final_min_mask = h.min_mask;
-    res->n_ops = h.n_ops;
     res->crc32 = crc;
-    res->ms_kernels = ms_total;
-    res->ms_tagscan = ms_scan;
-    res->ms_automaton = ms_auto;
+    res->ms_kernels = ctx->ms_phase_a + ms_emit;
     res->ms_emit = ms_emit;
     res->gpu_launches = launches;
-    ctx->last_n = n; ctx->last_s0 = totals[0]; ctx->last_s1 = totals[1]; ctx->last_ntok = m;
+    ctx->last_s0 = totals[0]; ctx->last_s1 = totals[1]; ctx->last_ntok = m;
     return 0;
 }
 
-extern "C" int mrz_run_resident(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result *res) {
-    if (!ctx || !prm || !res || n < 0 || n > ctx->max_chunk) return MRZ_E_ARG;
-    if (prm->level < 0 || prm->level > 9 || prm->chunk_bytes < 1 || prm->chunk_bytes > 8) return MRZ_E_ARG;
-    if (prm->victim_round_in < 0 || prm->victim_round_in >= kLevels[prm->level].chain) return MRZ_E_ARG;
-    CK(cudaSetDevice(ctx->device));
+// Automaton with token-buffer growth: a chunk whose tokens overflowed is redone with a larger buffer.
+static int run_automaton_grow(mrz_ctx *ctx, i64 n, const mrz_params *prm) {
     for (;;) {
-        int rc = run_once(ctx, n, prm, res);
+        int rc = run_phase_a(ctx, n, prm);
         if (rc != 1) return rc;
-        // token buffer overflowed: grow (bounded by one match per 31 bytes) and redo the chunk
         i64 cap = ctx->tok_cap * 8;
-        i64 hard = n / MRZ_MIN_MATCH + 16;
+        i64 hard = n / MRZ_MIN_MATCH + 16;   // bounded by one match per 31 bytes
         if (cap > hard) cap = hard;
         if (cap <= ctx->tok_cap) { ctx->err = "token capacity exhausted"; return MRZ_E_INTERNAL; }
         if ((rc = ensure_tokens(ctx, cap))) return rc;
     }
+}
+
+static int check_run_args(const mrz_ctx *ctx, i64 n, const mrz_params *prm) {
+    if (!ctx || !prm || n < 0 || n > ctx->max_chunk) return MRZ_E_ARG;
+    if (prm->level < 0 || prm->level > 9 || prm->chunk_bytes < 1 || prm->chunk_bytes > 8) return MRZ_E_ARG;
+    if (prm->victim_round_in < 0 || prm->victim_round_in >= kLevels[prm->level].chain) return MRZ_E_ARG;
+    return 0;
+}
+
+extern "C" int mrz_run_resident(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result *res) {
+    if (!res || check_run_args(ctx, n, prm)) return MRZ_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int rc = run_automaton_grow(ctx, n, prm);
+    if (rc) return rc;
+    return run_phase_b(ctx, res);
+}
+
+extern "C" int mrz_run_automaton(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result *res) {
+    if (!res || check_run_args(ctx, n, prm)) return MRZ_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int rc = run_automaton_grow(ctx, n, prm);
+    if (rc) return rc;
+    fill_automaton_result(ctx, res);
+    return 0;
+}
+
+extern "C" int mrz_run_emit(mrz_ctx *ctx, mrz_result *res) {
+    if (!ctx || !res) return MRZ_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    return run_phase_b(ctx, res);
+}
+
+// Variant v runs with victim_round_in = v on its own stream, tables and CTA; on the device the nvar automata
+// (one SM each) run side by side.  One host thread per variant drives the per-segment launch loop.
+extern "C" int mrz_run_variants(mrz_ctx *const *ctxs, int nvar, int64_t n, const mrz_params *prm, mrz_result *res) {
+    if (!ctxs || !prm || !res || nvar < 1 || prm->level < 0 || prm->level > 9 || nvar > kLevels[prm->level].chain) return MRZ_E_ARG;
+    std::vector<int> rcs((size_t)nvar, 0);
+    auto one = [&](int v) {
+        mrz_params p = *prm;
+        p.victim_round_in = v;
+        rcs[(size_t)v] = mrz_run_automaton(ctxs[v], n, &p, &res[v]);
+    };
+#ifndef MRZ_CUSIM
+    std::vector<std::thread> th;
+    for (int v = 1; v < nvar; v++) th.emplace_back(one, v);
+    one(0);
+    for (auto &t : th) t.join();
+#else
+    for (int v = 0; v < nvar; v++) one(v);   // the fiber emulator is single-threaded
+#endif
+    for (int v = 0; v < nvar; v++)
+        if (rcs[(size_t)v]) {
+            g_err = ctxs[v] ? ctxs[v]->err : "null variant context";
+            return rcs[(size_t)v];
+        }
+    return 0;
 }
 
 extern "C" int mrz_download(mrz_ctx *ctx, uint8_t *s0, int64_t s0_cap, uint8_t *s1, int64_t s1_cap) {

@@ -16,6 +16,7 @@ DECLARED_SYMBOLS = [
     "mrz_device_count", "mrz_version", "mrz_last_error", "mrz_ctx_create", "mrz_ctx_destroy",
     "mrz_rzip_chunk", "mrz_upload", "mrz_run_resident", "mrz_download", "mrz_host_alloc", "mrz_host_free",
     "mrz_debug_tags", "mrz_debug_crc32", "mrz_debug_tokens",
+    "mrz_ctx_create_variant", "mrz_run_automaton", "mrz_run_emit", "mrz_run_variants",
 ]
 
 
@@ -64,6 +65,11 @@ def bind(path):
         L.mrz_debug_tags.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_int64]
         L.mrz_debug_crc32.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_uint32)]
         L.mrz_debug_tokens.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
+        L.mrz_ctx_create_variant.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.mrz_run_automaton.argtypes = [C.c_void_p, C.c_int64, C.POINTER(MrzParams), C.POINTER(MrzResult)]
+        L.mrz_run_emit.argtypes = [C.c_void_p, C.POINTER(MrzResult)]
+        L.mrz_run_variants.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.POINTER(MrzParams),
+                                       C.POINTER(MrzResult)]
     return L
 
 
@@ -103,10 +109,16 @@ class PinnedBuffer:
 
 
 class Context:
-    def __init__(self, device=0, max_chunk=1 << 28, library=None):
-        self.L = library if library is not None else lib()
+    def __init__(self, device=0, max_chunk=1 << 28, library=None, parent=None):
+        """parent: create a variant context (mrz_ctx_create_variant) sharing the parent's chunk bytes."""
         self.h = C.c_void_p()
-        rc = self.L.mrz_ctx_create(device, max_chunk, C.byref(self.h))
+        if parent is not None:
+            self.L = parent.L
+            rc = self.L.mrz_ctx_create_variant(parent.h, C.byref(self.h))
+            max_chunk = parent.max_chunk
+        else:
+            self.L = library if library is not None else lib()
+            rc = self.L.mrz_ctx_create(device, max_chunk, C.byref(self.h))
         if rc:
             raise MrzError("mrz_ctx_create rc=%d: %s" % (rc, self.L.mrz_last_error(None).decode()))
         self.max_chunk = max_chunk
@@ -127,6 +139,16 @@ class Context:
     def run_resident(self, n, params):
         res = MrzResult()
         self._check(self.L.mrz_run_resident(self.h, n, C.byref(params), C.byref(res)), "mrz_run_resident")
+        return res
+
+    def run_automaton(self, n, params):
+        res = MrzResult()
+        self._check(self.L.mrz_run_automaton(self.h, n, C.byref(params), C.byref(res)), "mrz_run_automaton")
+        return res
+
+    def run_emit(self):
+        res = MrzResult()
+        self._check(self.L.mrz_run_emit(self.h, C.byref(res)), "mrz_run_emit")
         return res
 
     def download(self, res, s0=None, s1=None):
@@ -159,3 +181,38 @@ class Context:
         out = np.empty((max(1, cnt.value), 3), dtype=np.int64)
         self._check(self.L.mrz_debug_tokens(self.h, out.ctypes.data, cnt.value, C.byref(cnt)), "mrz_debug_tokens")
         return out[:cnt.value]
+
+
+class VariantSet:
+    """One resident chunk, `nvar` automata side by side: variant v runs with victim_round_in = v (include/mrz_gpu.h,
+    mrz_run_variants).  ctxs[0] is the parent (owns the chunk bytes), the others are variant contexts."""
+
+    def __init__(self, device, max_chunk, nvar, library=None):
+        self.parent = Context(device, max_chunk, library=library)
+        self.ctxs = [self.parent] + [Context(parent=self.parent) for _ in range(nvar - 1)]
+        self.nvar = nvar
+        self.L = self.parent.L
+
+    def close(self):
+        for c in reversed(self.ctxs):
+            c.close()
+        self.ctxs = []
+
+    def upload(self, arr):
+        self.parent.upload(arr)
+
+    def run(self, n, params, nvar=None):
+        """-> list of MrzResult, one per victim_round_in in range(nvar)."""
+        nvar = self.nvar if nvar is None else nvar
+        hs = (C.c_void_p * nvar)(*[c.h for c in self.ctxs[:nvar]])
+        res = (MrzResult * nvar)()
+        rc = self.L.mrz_run_variants(hs, nvar, n, C.byref(params), res)
+        if rc:
+            raise MrzError("mrz_run_variants rc=%d: %s" % (rc, self.L.mrz_last_error(None).decode()))
+        return list(res)
+
+    def emit(self, v, s0=None, s1=None):
+        """Streams of variant v (after run): -> (MrzResult, stream 0, stream 1)."""
+        r = self.ctxs[v].run_emit()
+        s0, s1 = self.ctxs[v].download(r, s0, s1)
+        return r, s0, s1

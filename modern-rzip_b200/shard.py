@@ -11,6 +11,11 @@ performs a victim eviction (SURVEY.md §8e).  Protocol (no data-path collective;
      chained value is valid; otherwise its owner re-runs it with the right input and the new output is
      all-gathered before the walk continues.
 
+`run_sharded_variants` is the variant-parallel form of the same chain (SURVEY.md §8e option 1): every rank runs each
+of its chunks for ALL max_chain_len values of victim_round_in side by side on its GPU (mrz_run_variants: one CTA and
+one table per variant), ONE all-gather carries the (chunk, vr_in) -> vr_out table, every rank walks the chain and
+emits only the chosen variant of its own chunks.  No chunk ever waits for another and none is re-run.
+
 The engine is any callable run(chunk_bytes, vr_in) -> (victim_events, vr_out, payload); bench.py passes the
 CUDA context, tests/test_shard_gloo.py the CPU-emulator build of the same kernels.
 """
@@ -67,3 +72,25 @@ def run_sharded(chunks, run, rank=0, world=1, device="cpu", vr_start=0):
             spec_in[k] = vr
         vr = vo
     return results, vr, reruns
+
+
+def run_sharded_variants(chunks, run_variants, n_variants, rank=0, world=1, device="cpu", vr_start=0):
+    """run_variants(chunk) -> [vr_out for vr_in in range(n_variants)] (the automata of all variants, no emission).
+    Returns ({k: chosen vr_in} for the chunks this rank owns, final victim_round)."""
+    n_chunks = len(chunks)
+    t = torch.full((n_chunks, n_variants), -1, dtype=torch.int64, device=device)
+    for k in range(n_chunks):
+        if owner(k, world) == rank:
+            outs = run_variants(chunks[k])
+            assert len(outs) == n_variants
+            t[k] = torch.tensor([int(x) for x in outs], dtype=torch.int64, device=device)
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)      # rows are disjoint: MAX over a -1-filled table is an all-gather
+    table = t.tolist()
+    chosen, vr = {}, vr_start
+    for k in range(n_chunks):
+        if owner(k, world) == rank:
+            chosen[k] = vr
+        vr = int(table[k][vr])
+        assert 0 <= vr < n_variants
+    return chosen, vr

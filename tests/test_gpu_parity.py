@@ -99,3 +99,39 @@ def test_crc_matches_zlib(gpu_ctx):
         data = H.gen_random(n, seed=n % 97 + 1)
         res, _, _ = gpu_ctx.rzip_chunk(data, mrz_py.make_params(7, 4, hidx))
         assert res.crc32 == zlib.crc32(data.tobytes()), n
+
+
+@pytest.mark.parametrize("level,size", [(7, 24 << 20), (1, 3 << 20), (8, 2 << 20)], ids=["L7-vm-16var", "L1-motif-2var", "L8-motif-32var"])
+def test_variant_parallel_chunk(level, size):
+    """mrz_run_variants (include/mrz_gpu.h): the automaton of one resident chunk for every victim_round_in at once —
+    concurrent CTAs, shared chunk bytes, own tables.  Each variant's carry and counters equal the oracle run with that
+    input, and the streams emitted afterwards (mrz_run_emit, any order) are the oracle's byte for byte."""
+    import mrz_py
+    chain = [1, 2, 2, 2, 3, 4, 6, 16, 32, 128][level]
+    data = H.as_u8(H.gen_motif(size, 3000 * level) if level != 7 else H.gen_vm_like(size, seed=47))
+    hidx, cb = H.hash_index(), H.chunk_bytes(data.size)
+    vs = mrz_py.VariantSet(0, data.size, chain)
+    try:
+        vs.upload(data)
+        for _ in range(2):                          # contexts are reusable
+            res = vs.run(data.size, mrz_py.make_params(level, cb, hidx, 0))
+        check_vs = sorted(set([0, 1, chain // 2, chain - 1]))
+        refs = {v: H.oracle_chunk(data, level=level, cb=cb, vr_in=v, hidx=hidx) for v in check_vs}
+        assert len({r["s0"] for r in refs.values()}) > 1, "the case must depend on victim_round_in"
+        seq = mrz_py.Context(0, data.size)          # the same variants one after the other through the plain entry point
+        try:
+            seq.upload(data)
+            for v in range(chain):
+                r1 = seq.run_resident(data.size, mrz_py.make_params(level, cb, hidx, v))
+                for k in ("victim_round_out", "victim_events", "inserts", "tag_hits", "tag_misses", "n_ops", "final_min_mask"):
+                    assert getattr(res[v], k) == getattr(r1, k), (v, k)
+        finally:
+            seq.close()
+        for v in reversed(check_vs):
+            assert res[v].victim_round_out == refs[v]["vr_out"]
+            assert res[v].victim_events == refs[v]["stats"]["victim_events"] > 0
+            r, s0, s1 = vs.emit(v)
+            assert s0.tobytes() == refs[v]["s0"] and s1.tobytes() == refs[v]["s1"], v
+            assert r.matches == refs[v]["stats"]["matches"] and r.literal_bytes == refs[v]["stats"]["literal_bytes"]
+    finally:
+        vs.close()

@@ -31,13 +31,33 @@ hidx = H.hash_index(); cb = H.chunk_bytes(CHUNK)
 def run(chunk, vr_in):
     res, s0, s1 = ctx.rzip_chunk(chunk, mrz_py.make_params(LEVEL, cb, hidx, vr_in))
     return res.victim_events, res.victim_round_out, (s0.tobytes(), s1.tobytes(), vr_in)
-results, vr, reruns = shard.run_sharded(chunks, run, rank, world)
+if sys.argv[6] == "variants":
+    # variant-parallel: all victim_round_in values of a chunk at once, one all-gather, no re-runs
+    chain = [1, 2, 2, 2, 3, 4, 6, 16, 32, 128][LEVEL]
+    sets = {}
+    def run_variants(chunk):
+        vs = mrz_py.VariantSet(0, CHUNK, chain, library=ctx.L)
+        vs.upload(chunk)
+        sets[id(chunk)] = vs
+        return [r.victim_round_out for r in vs.run(chunk.size, mrz_py.make_params(LEVEL, cb, hidx, 0))]
+    chosen, vr = shard.run_sharded_variants(chunks, run_variants, chain, rank, world)
+    results = {}
+    for k, v in chosen.items():
+        r, s0, s1 = sets[id(chunks[k])].emit(v)
+        results[k] = (s0.tobytes(), s1.tobytes(), v)
+    reruns = 0
+else:
+    results, vr, reruns = shard.run_sharded(chunks, run, rank, world)
 pickle.dump({"results": results, "vr": vr, "reruns": reruns}, open(os.path.join(out, "r%d.pkl" % rank), "wb"))
 ctx.close(); dist.destroy_process_group()
 '''
 
 
-def test_two_ranks_chain_equals_sequential_oracle():
+import pytest
+
+
+@pytest.mark.parametrize("mode", ["rerun", "variants"])
+def test_two_ranks_chain_equals_sequential_oracle(mode):
     subprocess.check_call(["make", "-C", os.path.join(ROOT, "tests", "cusim"), "libmrz_sim.so"], stdout=subprocess.DEVNULL)
     data = H.as_u8(H.gen_motif(NCHUNK * CHUNK, 5000))
     hidx, cb = H.hash_index(), H.chunk_bytes(CHUNK)
@@ -57,7 +77,7 @@ def test_two_ranks_chain_equals_sequential_oracle():
         procs = []
         for rank in range(2):
             env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-            procs.append(subprocess.Popen([sys.executable, w, ROOT, d, str(LEVEL), str(NCHUNK), str(CHUNK)], env=env))
+            procs.append(subprocess.Popen([sys.executable, w, ROOT, d, str(LEVEL), str(NCHUNK), str(CHUNK), mode], env=env))
         for p in procs:
             assert p.wait(timeout=600) == 0
         got, reruns = {}, 0
@@ -70,4 +90,7 @@ def test_two_ranks_chain_equals_sequential_oracle():
     for k in range(NCHUNK):
         assert got[k][2] == ref[k][2], "chunk %d ran with the wrong victim_round_in" % k
         assert got[k][0] == ref[k][0] and got[k][1] == ref[k][1], "chunk %d differs from the sequential oracle" % k
-    assert reruns >= 1 or all(x[2] == 0 for x in ref)
+    if mode == "rerun":
+        assert reruns >= 1 or all(x[2] == 0 for x in ref)
+    else:
+        assert reruns == 0

@@ -86,3 +86,29 @@ def test_other_automaton_geometries(sim_ctx, env):
         check(ctx, H.gen_vm_like(1 << 20, seed=13), level=6)
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("level,gen", [(1, lambda: H.gen_motif(1 << 20, 2000)), (6, lambda: H.gen_vm_like(2 << 20, seed=16))],
+                         ids=["level1-motif", "level6-vm"])
+def test_variant_parallel_chunk(sim_ctx, level, gen):
+    """mrz_run_variants: every victim_round_in of a resident chunk at once (shared chunk bytes, own tables); each
+    variant's counters, carry and — once chosen with mrz_run_emit — streams equal the oracle run with that input."""
+    import mrz_py
+    chain = [1, 2, 2, 2, 3, 4, 6, 16, 32, 128][level]
+    data = H.as_u8(gen())
+    hidx, cb = H.hash_index(), H.chunk_bytes(data.size)
+    vs = mrz_py.VariantSet(0, data.size, chain, library=sim_ctx.L)
+    try:
+        vs.upload(data)
+        res = vs.run(data.size, mrz_py.make_params(level, cb, hidx, 0))
+        refs = [H.oracle_chunk(data, level=level, cb=cb, vr_in=v, hidx=hidx) for v in range(chain)]
+        assert len({r["s0"] for r in refs}) > 1, "the case must depend on victim_round_in"
+        for v in reversed(range(chain)):          # emission order is free: tokens of every variant stay resident
+            assert res[v].victim_round_out == refs[v]["vr_out"]
+            assert res[v].victim_events == refs[v]["stats"]["victim_events"]
+            assert res[v].inserts == refs[v]["stats"]["inserts"]
+            r, s0, s1 = vs.emit(v)
+            assert s0.tobytes() == refs[v]["s0"] and s1.tobytes() == refs[v]["s1"]
+            assert r.matches == refs[v]["stats"]["matches"] and r.victim_round_out == refs[v]["vr_out"]
+    finally:
+        vs.close()
