@@ -28,6 +28,8 @@ import numpy as np
 if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
     os.environ["NCCL_DEBUG"] = "WARN"     # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
 
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")   # --variants: one hardware queue per automaton stream (before torch creates the context)
+
 _REAL_STDOUT = 1
 
 ROOT = os.path.dirname(os.path.abspath(__file__))

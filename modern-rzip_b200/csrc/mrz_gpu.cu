@@ -64,8 +64,11 @@ struct mrz_ctx {
     i64 h_dbg[40];
     u8 *d_s0; i64 s0_cap; u8 *d_s1; i64 s1_cap;
     u32 *d_crc_part, *d_crc_part2, *d_crc_misc;  // misc[0]=tail, misc[1]=final
-    // host staging
+    // host staging: pinned, so that the small read-backs are truly asynchronous.  (A D2H copy into pageable memory
+    // blocks inside the driver until the stream has drained; with one host thread per variant that serialised the
+    // automata of mrz_run_variants — measured: wall = nvar x one automaton.)
     u32 *h_crc; i64 h_crc_cap;
+    struct Mailbox { AutoState st; i64 totals[2]; u32 tailcrc; u32 crc; EmitTotals tot; i64 dbg[40]; } *h_mb;
     // last run
     i64 last_n, last_s0, last_s1, last_ntok;
     // between mrz_run_automaton and mrz_run_emit
@@ -155,6 +158,11 @@ static void crc_host_init() {
 extern "C" const char *mrz_version(void) { return "mrz_gpu 0.1 (sm_100a)"; }
 
 extern "C" int mrz_device_count(void) {
+    // mrz_run_variants drives one stream per automaton.  With the default of 8 hardware queues, streams that share a
+    // queue serialise behind each other's kernel -> read-back -> next launch chain (measured on B200: 16 variants ran
+    // 4 at a time; with 32 queues all 16 run side by side, +8 % over one).  Only effective before the CUDA context
+    // exists, which is why it sits in the first call every entry path makes; an explicit setting wins.
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess) {
@@ -215,7 +223,8 @@ extern "C" void mrz_ctx_destroy(mrz_ctx *ctx) {
     cudaFree(ctx->d_toks); cudaFree(ctx->d_a0); cudaFree(ctx->d_a1); cudaFree(ctx->d_off0); cudaFree(ctx->d_off1);
     cudaFree(ctx->d_bsum); cudaFree(ctx->d_tot); cudaFree(ctx->d_dbg); cudaFree(ctx->d_s0); cudaFree(ctx->d_s1);
     cudaFree(ctx->d_crc_part); cudaFree(ctx->d_crc_part2); cudaFree(ctx->d_crc_misc);
-    free(ctx->h_crc);
+    if (ctx->h_crc) cudaFreeHost(ctx->h_crc);
+    if (ctx->h_mb) cudaFreeHost(ctx->h_mb);
     for (auto &e : ctx->ev)
         if (e) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -294,8 +303,8 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk, mrz_ctx *par
     CK(cudaMalloc(&ctx->d_crc_part2, (size_t)(nblk / 32 + 1) * 4));
     CK(cudaMalloc(&ctx->d_crc_misc, 16));
     ctx->h_crc_cap = nblk / 32 + 64;
-    ctx->h_crc = (u32 *)malloc((size_t)ctx->h_crc_cap * 4);
-    if (!ctx->h_crc) return MRZ_E_NOMEM;
+    CK(cudaHostAlloc((void **)&ctx->h_crc, (size_t)ctx->h_crc_cap * 4, cudaHostAllocDefault));
+    CK(cudaHostAlloc((void **)&ctx->h_mb, sizeof(*ctx->h_mb), cudaHostAllocDefault));
     int rc;
     if ((rc = ensure_tokens(ctx, max_chunk / 256 + 1024))) return rc;
     if (parent) return 0;   // a variant allocates its emission buffers only if it is the one chosen to emit
@@ -410,9 +419,10 @@ static int run_phase_a(mrz_ctx *ctx, i64 n, const mrz_params *prm) {
         CK(cudaEventRecord(ctx->ev[3], s));
         launches += 4;
         i64 prev_p = h.p;
-        CK(cudaMemcpyAsync(&h, ctx->d_st, sizeof h, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(&ctx->h_mb->st, ctx->d_st, sizeof h, cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
         CK(cudaGetLastError());
+        h = ctx->h_mb->st;
         float a = 0, b = 0;
         cudaEventElapsedTime(&a, ctx->ev[1], ctx->ev[2]);
         cudaEventElapsedTime(&b, ctx->ev[2], ctx->ev[3]);
@@ -432,8 +442,9 @@ static int run_phase_a(mrz_ctx *ctx, i64 n, const mrz_params *prm) {
     }
 
     if (ctx->d_dbg) {
-        CK(cudaMemcpyAsync(ctx->h_dbg, ctx->d_dbg, 40 * 8, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(ctx->h_mb->dbg, ctx->d_dbg, 40 * 8, cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
+        memcpy(ctx->h_dbg, ctx->h_mb->dbg, sizeof ctx->h_dbg);
         static const char *nm[12] = {"refill", "gather", "plan", "conflict", "commit", "serial", "inval", "epilogue", "ops", "batches", "serial_ops", ""};
         fprintf(stderr, "[mrz profile] automaton cycles:");
         for (int q = 0; q < 11; q++) fprintf(stderr, " %s=%lld", nm[q], (long long)ctx->h_dbg[q]);
@@ -497,12 +508,13 @@ static int run_phase_b(mrz_ctx *ctx, mrz_result *res) {
     launches++;
     mrz_launch_exclusive_scan(ctx->d_a0, ctx->d_off0, items, ctx->d_bsum, ctx->d_off0 + items, s, &launches);
     mrz_launch_exclusive_scan(ctx->d_a1, ctx->d_off1, items, ctx->d_bsum, ctx->d_off1 + items, s, &launches);
-    i64 totals[2];
+    i64 *totals = ctx->h_mb->totals;
     CK(cudaMemcpyAsync(&totals[0], ctx->d_off0 + items, 8, cudaMemcpyDeviceToHost, s));
     CK(cudaMemcpyAsync(&totals[1], ctx->d_off1 + items, 8, cudaMemcpyDeviceToHost, s));
     // CRC partials -> host combine
     i64 nblk = n / 16384, ngrp = nblk / 32, nrest = nblk - ngrp * 32;
-    u32 tailcrc = 0;
+    u32 &tailcrc = ctx->h_mb->tailcrc;
+    tailcrc = 0;
     if (ngrp) CK(cudaMemcpyAsync(ctx->h_crc, ctx->d_crc_part2, (size_t)ngrp * 4, cudaMemcpyDeviceToHost, s));
     if (nrest)
         CK(cudaMemcpyAsync(ctx->h_crc + ngrp, ctx->d_crc_part + ngrp * 32, (size_t)nrest * 4, cudaMemcpyDeviceToHost, s));
@@ -518,12 +530,13 @@ static int run_phase_b(mrz_ctx *ctx, mrz_result *res) {
         i64 tl = n - nblk * 16384;
         raw = crc_shift(raw, (u64)tl) ^ tailcrc;
     }
-    u32 crc = raw ^ crc_shift(0xFFFFFFFFu, (u64)n) ^ 0xFFFFFFFFu;
-    CK(cudaMemcpyAsync(ctx->d_crc_misc + 1, &crc, 4, cudaMemcpyHostToDevice, s));
+    const u32 crc = raw ^ crc_shift(0xFFFFFFFFu, (u64)n) ^ 0xFFFFFFFFu;
+    ctx->h_mb->crc = crc;
+    CK(cudaMemcpyAsync(ctx->d_crc_misc + 1, &ctx->h_mb->crc, 4, cudaMemcpyHostToDevice, s));
     if ((rc = ensure_s0(ctx, totals[0]))) return rc;
     mrz_launch_emit(ctx->d_buf, ctx->d_toks, m, n, chunk_bytes, ctx->d_off0, ctx->d_off1, totals[1], ctx->d_s0,
                     ctx->d_s1, ctx->d_crc_misc + 1, s, &launches);
-    EmitTotals tot;
+    EmitTotals &tot = ctx->h_mb->tot;
     CK(cudaMemcpyAsync(&tot, ctx->d_tot, sizeof tot, cudaMemcpyDeviceToHost, s));
     CK(cudaEventRecord(ctx->ev[2], s));
     CK(cudaStreamSynchronize(s));

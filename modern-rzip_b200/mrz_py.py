@@ -9,6 +9,10 @@ import os
 
 import numpy as np
 
+# one hardware queue per automaton stream of mrz_run_variants (see mrz_device_count in csrc/mrz_gpu.cu); must be set
+# before anything in the process creates the CUDA context
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmrz_gpu.so")
 
