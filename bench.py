@@ -240,6 +240,10 @@ def variants_bench(args, rank, world, local_rank, config, barrier):
     launches = 0
     last = {}
 
+    def trace(msg):
+        if os.environ.get("MRZ_BENCH_TRACE"):
+            print("[variants rank %d] %s" % (rank, msg), file=sys.stderr, flush=True)
+
     def step(with_copies):
         nonlocal launches
         outs = [None] * C_
@@ -254,10 +258,12 @@ def variants_bench(args, rank, world, local_rank, config, barrier):
         work(0)
         for t in th:
             t.join()
+        trace("runs done")
         it = iter(range(C_))
         chosen, vr = shard.run_sharded_variants(
             chunks, lambda _c: [r.victim_round_out for r in outs[next(it)]], V, rank, world, device="cuda")
         b_alg = 0
+        trace("chain done: %r" % (chosen,))
         for c in range(C_):
             v = chosen[c * world + rank]
             launches += sum(int(r.gpu_launches) for r in outs[c])
@@ -266,6 +272,7 @@ def variants_bench(args, rank, world, local_rank, config, barrier):
             else:
                 r = sets[c].ctxs[v].run_emit()
             launches += int(r.gpu_launches) - int(outs[c][v].gpu_launches)
+            trace("emit chunk %d variant %d done" % (c, v))
             b_alg += n + r.s0_len + r.s1_len
             last[c] = (r, v, max(float(x.ms_automaton) for x in outs[c]), float(outs[c][v].ms_automaton))
         return b_alg, vr

@@ -9,6 +9,7 @@
 #include <string.h>
 #include <string>
 #ifndef MRZ_CUSIM
+#include <mutex>
 #include <thread>
 #endif
 #include <vector>
@@ -188,6 +189,7 @@ static int ensure_tokens(mrz_ctx *ctx, i64 cap) {
     if (ctx->d_toks) cudaFree(ctx->d_toks);
     ctx->d_toks = nullptr; ctx->tok_cap = 0;
     CK(cudaMalloc(&ctx->d_toks, (size_t)cap * sizeof(Token)));
+    if (!(getenv("MRZ_NO_ZERO_INIT") && strchr(getenv("MRZ_NO_ZERO_INIT"), 't'))) CK(cudaMemset(ctx->d_toks, 0, (size_t)cap * sizeof(Token)));
     ctx->tok_cap = cap;
     return 0;
 }
@@ -291,6 +293,20 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk, mrz_ctx *par
     CK(cudaMalloc(&ctx->d_cand_pos, (size_t)(SEG_CAND_CAP + 64) * sizeof(u32)));
     CK(cudaMalloc(&ctx->d_cand_tag, (size_t)(SEG_CAND_CAP + 64) * sizeof(i64)));
     CK(cudaMalloc(&ctx->d_tot, sizeof(EmitTotals)));
+    // Device memory recycled from an earlier process is not zero.  A second variant set created after a large run
+    // faulted (illegal address in the per-segment kernels) while the same program on a fresh box did not: something
+    // on the path reads a word of one of these work buffers before writing it.  Not root-caused yet
+    // (compute-sanitizer is closed on this pool); every work buffer starts zeroed, as on a fresh device.
+    const char *nz = getenv("MRZ_NO_ZERO_INIT");   // debugging knob: comma-free list of letters naming buffers left as allocated
+#define ZERO(letter, ptr, bytes) do { if (!(nz && strchr(nz, letter))) CK(cudaMemset(ptr, 0, bytes)); } while (0)
+    ZERO('g', ctx->d_gstate, mrz_grid_state_bytes());
+    ZERO('p', ctx->d_planio, mrz_planio_bytes());
+    ZERO('h', ctx->d_hidx, 256 * 8);
+    ZERO('s', ctx->d_st, sizeof(AutoState));
+    ZERO('c', ctx->d_tile_cnt, (SEG_MAX_TILES + 1) * sizeof(int));
+    ZERO('o', ctx->d_tile_off, (SEG_MAX_TILES + 2) * sizeof(i64));
+    ZERO('P', ctx->d_cand_pos, (size_t)(SEG_CAND_CAP + 64) * sizeof(u32));
+    ZERO('T', ctx->d_cand_tag, (size_t)(SEG_CAND_CAP + 64) * sizeof(i64));
     if (getenv("MRZ_PROFILE")) CK(cudaMalloc(&ctx->d_dbg, 40 * 8));
     if (parent) {
         ctx->d_s1 = parent->d_s1;
@@ -302,6 +318,9 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk, mrz_ctx *par
     CK(cudaMalloc(&ctx->d_crc_part, (size_t)nblk * 4));
     CK(cudaMalloc(&ctx->d_crc_part2, (size_t)(nblk / 32 + 1) * 4));
     CK(cudaMalloc(&ctx->d_crc_misc, 16));
+    ZERO('r', ctx->d_crc_part, (size_t)nblk * 4);
+    ZERO('r', ctx->d_crc_part2, (size_t)(nblk / 32 + 1) * 4);
+    ZERO('r', ctx->d_crc_misc, 16);
     ctx->h_crc_cap = nblk / 32 + 64;
     CK(cudaHostAlloc((void **)&ctx->h_crc, (size_t)ctx->h_crc_cap * 4, cudaHostAllocDefault));
     CK(cudaHostAlloc((void **)&ctx->h_mb, sizeof(*ctx->h_mb), cudaHostAllocDefault));
@@ -605,6 +624,14 @@ extern "C" int mrz_run_emit(mrz_ctx *ctx, mrz_result *res) {
 // (one SM each) run side by side.  One host thread per variant drives the per-segment launch loop.
 extern "C" int mrz_run_variants(mrz_ctx *const *ctxs, int nvar, int64_t n, const mrz_params *prm, mrz_result *res) {
     if (!ctxs || !prm || !res || nvar < 1 || prm->level < 0 || prm->level > 9 || nvar > kLevels[prm->level].chain) return MRZ_E_ARG;
+    if (!ctxs[0]) return MRZ_E_ARG;
+#ifndef MRZ_CUSIM
+    // One variant set per device at a time.  Measured on B200: the <= 32 automata of one set run side by side
+    // correctly, but two sets driven concurrently from two host threads (32 automata of 1 GiB tar-like chunks)
+    // ended in an illegal-address fault that is not root-caused yet — so concurrent callers queue here.
+    static std::mutex mu[64];
+    std::lock_guard<std::mutex> guard(mu[ctxs[0]->device & 63]);
+#endif
     std::vector<int> rcs((size_t)nvar, 0);
     auto one = [&](int v) {
         mrz_params p = *prm;

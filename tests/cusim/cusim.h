@@ -53,6 +53,7 @@ static inline cudaError_t cudaSetDevice(int) { return 0; }
 static inline cudaError_t cudaGetLastError() { return 0; }
 template <class T> static inline cudaError_t cudaMalloc(T **p, size_t n) {
     *p = (T *)aligned_alloc(256, (n + 255) / 256 * 256 + 256);
+    if (*p && getenv("CUSIM_POISON")) memset((void *)*p, 0xA5, (n + 255) / 256 * 256 + 256);   // recycled device memory is not zero
     return *p ? 0 : cudaErrorMemoryAllocation;
 }
 static inline cudaError_t cudaFree(void *p) { free(p); return 0; }
