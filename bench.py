@@ -222,6 +222,8 @@ def variants_bench(args, rank, world, local_rank, config, barrier):
     multi = world > 1
     if multi:
         import torch.distributed as dist
+    os.environ.setdefault("MRZ_VARIANTS_CONCURRENT", "1")   # this mode measures the side-by-side form (include/mrz_gpu.h)
+    config["MRZ_VARIANTS_CONCURRENT"] = os.environ["MRZ_VARIANTS_CONCURRENT"]
     n, C_, V = args.size, args.chunks_per_gpu, CHAIN[args.level]
     n_chunks = world * C_
     hidx, cb = H.hash_index(), H.chunk_bytes(n)

@@ -83,8 +83,10 @@ int mrz_download(mrz_ctx *ctx, uint8_t *s0, int64_t s0_cap, uint8_t *s1, int64_t
  *   mrz_run_automaton:      hash_search up to the token list (no streams): counters, victim_round_out, n_ops.
  *   mrz_run_emit:           put_literal/put_match/CRC (rzip.c:161-227, :617-666) for the tokens of the last
  *                           mrz_run_automaton of this context; then mrz_download from the same context.
- *   mrz_run_variants:       ctxs[v] runs with victim_round_in = v (prm->victim_round_in is ignored), all nvar
- *                           concurrently on the device; res[v] as mrz_run_automaton.  ctxs[0] may be the parent. */
+ *   mrz_run_variants:       ctxs[v] runs with victim_round_in = v (prm->victim_round_in is ignored); res[v] as
+ *                           mrz_run_automaton.  ctxs[0] may be the parent.  The variants run one after another
+ *                           unless MRZ_VARIANTS_CONCURRENT=1 is set, in which case all nvar automata run side by
+ *                           side (one host thread + stream each; experimental). */
 int mrz_ctx_create_variant(mrz_ctx *parent, mrz_ctx **out);
 int mrz_run_automaton(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result *res);
 int mrz_run_emit(mrz_ctx *ctx, mrz_result *res);

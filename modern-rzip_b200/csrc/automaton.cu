@@ -42,6 +42,9 @@
 //   oracle/spec_model.c is the CPU model of the speculation rules; tests/test_spec_model.py proves
 //   it equivalent to the sequential restatement, tests/test_sim_parity.py runs this very file on
 //   the CPU emulator, tests/test_gpu_parity.py on the B200.
+#ifndef MRZ_CUSIM
+#include <mutex>
+#endif
 #include "mrz_common.cuh"
 
 #define FULL 0xffffffffu
@@ -1491,8 +1494,21 @@ extern "C" int mrz_launch_automaton(const u8 *buf, i64 *ttag, i64 *toff, u64 *fi
                                     void *planio, cudaStream_t s) {
     PlanIO *io = (PlanIO *)planio;
 #ifndef MRZ_CUSIM
-    cudaError_t e = cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-    if (e != cudaSuccess) return (int)e;
+    // once per device: mrz_run_variants launches this kernel from many host threads at once, and the attribute must not
+    // be rewritten under a concurrent launch of the same function
+    cudaError_t e = cudaSuccess;
+    {
+        static std::mutex mu;
+        static bool set_for[64];
+        int dev = 0;
+        cudaGetDevice(&dev);
+        std::lock_guard<std::mutex> g(mu);
+        if (!set_for[dev & 63]) {
+            e = cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+            if (e != cudaSuccess) return (int)e;
+            set_for[dev & 63] = true;
+        }
+    }
     if (helpers > 0) {
         e = cudaMemsetAsync(io, 0, 8, s);   // seq, done
         if (e != cudaSuccess) return (int)e;

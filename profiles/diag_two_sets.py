@@ -1,5 +1,6 @@
 """Diagnostic: two resident chunks on one GPU, their variant sets driven from two host threads."""
 import os
+os.environ.setdefault("MRZ_VARIANTS_CONCURRENT", "1")
 import sys
 import threading
 

@@ -1,5 +1,6 @@
 """Diagnostic (not a bench): how the wall time of mrz_run_variants scales with the number of concurrent automata."""
 import os
+os.environ.setdefault("MRZ_VARIANTS_CONCURRENT", "1")
 import sys
 import time
 

@@ -102,11 +102,13 @@ def test_crc_matches_zlib(gpu_ctx):
 
 
 @pytest.mark.parametrize("level,size", [(7, 24 << 20), (1, 3 << 20), (8, 2 << 20)], ids=["L7-vm-16var", "L1-motif-2var", "L8-motif-32var"])
-def test_variant_parallel_chunk(level, size):
+@pytest.mark.parametrize("concurrent", ["0", "1"], ids=["one-after-another", "side-by-side"])
+def test_variant_parallel_chunk(level, size, concurrent, monkeypatch):
     """mrz_run_variants (include/mrz_gpu.h): the automaton of one resident chunk for every victim_round_in at once —
     concurrent CTAs, shared chunk bytes, own tables.  Each variant's carry and counters equal the oracle run with that
     input, and the streams emitted afterwards (mrz_run_emit, any order) are the oracle's byte for byte."""
     import mrz_py
+    monkeypatch.setenv("MRZ_VARIANTS_CONCURRENT", concurrent)
     chain = [1, 2, 2, 2, 3, 4, 6, 16, 32, 128][level]
     data = H.as_u8(H.gen_motif(size, 3000 * level) if level != 7 else H.gen_vm_like(size, seed=47))
     hidx, cb = H.hash_index(), H.chunk_bytes(data.size)
