@@ -131,10 +131,22 @@ def gen_dense(n, seed=5, out=None, base=1 << 20, mutations=100):
     return buf
 
 
-GENS = {"tar": gen_tar_like, "vm": gen_vm_like, "dense": gen_dense}
+def gen_random(n, seed=4, out=None):
+    """configs[3]: uniform random bytes (all literals, worst-case table pressure); drawn in 64 MiB pieces."""
+    rng = np.random.default_rng(seed)
+    buf = out if out is not None else np.empty(n, dtype=np.uint8)
+    step = 64 << 20
+    for pos in range(0, n, step):
+        m = min(step, n - pos)
+        buf[pos:pos + m] = rng.integers(0, 256, m, dtype=np.uint8)
+    return buf
+
+
+GENS = {"tar": gen_tar_like, "vm": gen_vm_like, "dense": gen_dense, "random": gen_random}
 KINDS = {"tar": "configs[1]: tar-like, duplicate bodies at distances up to the chunk size",
          "vm": "configs[2]: VM-image-like (4 KiB blocks: zero / copies / random / text)",
-         "dense": "configs[4]: dense repeats (1 MiB base block, 100 point mutations per copy)"}
+         "dense": "configs[4]: dense repeats (1 MiB base block, 100 point mutations per copy)",
+         "random": "configs[3]: incompressible uniform random bytes (all literals)"}
 
 
 # ------------------------------------------------------------------ clocks

@@ -192,6 +192,62 @@ def parse_archive(raw):
     return dict(magic=magic, chunks=chunks, trailer=bytes(raw[pos:]))
 
 
+def parse_archive_hashed(path):
+    """parse_archive for archives too large to hold as bytes: walks the file through np.memmap and returns per-chunk
+    SHA-256 of the two streams instead of the streams themselves (same layout, stream.c:1199-1293)."""
+    raw = np.memmap(path, dtype=np.uint8, mode="r")
+    total = raw.size
+
+    def le(a, b):
+        return int.from_bytes(bytes(raw[a:b]), "little")
+    assert bytes(raw[:4]) == b"MRZI"
+    magic = dict(major=int(raw[4]), minor=int(raw[5]), st_size=le(6, 14), hash_code=int(raw[14]), levels=int(raw[18]))
+    pos = 20 + int(raw[19])
+    chunks = []
+    while True:
+        cb, eof = int(raw[pos]), int(raw[pos + 1])
+        size = le(pos + 2, pos + 2 + cb)
+        init = pos + 2 + cb
+        hl = 1 + 3 * cb
+        endpos = init + 2 * hl
+        rec = dict(cb=cb, eof=eof, size=size, n_blocks=0)
+        for j in range(2):
+            h = init + j * hl
+            assert int(raw[h]) == 3
+            nxt = le(h + 1 + 2 * cb, h + hl)
+            sha, ln = hashlib.sha256(), 0
+            while nxt:
+                b = init + nxt
+                ctype, c_len, u_len = int(raw[b]), le(b + 1, b + 1 + cb), le(b + 1 + cb, b + 1 + 2 * cb)
+                nxt = le(b + 1 + 2 * cb, b + hl)
+                assert ctype == 3 and c_len == u_len, "only CTYPE_NONE blocks are parsed here"
+                for o in range(b + hl, b + hl + c_len, 1 << 26):
+                    sha.update(raw[o:min(o + (1 << 26), b + hl + c_len)])
+                ln += c_len
+                rec["n_blocks"] += 1
+                endpos = max(endpos, b + hl + c_len)
+            rec["s%d_len" % j] = ln
+            rec["s%d_sha256" % j] = sha.hexdigest()
+        chunks.append(rec)
+        pos = endpos
+        if eof:
+            break
+    trailer = bytes(raw[pos:total])
+    del raw
+    return dict(magic=magic, chunks=chunks, trailer=trailer)
+
+
+def sha256_file(path):
+    h = hashlib.sha256()
+    with open(path, "rb") as f:
+        while True:
+            b = f.read(1 << 26)
+            if not b:
+                break
+            h.update(b)
+    return h.hexdigest()
+
+
 def decode_tokens(s0, s1, cb, history=b""):
     """Replay a chunk's streams (runzip.c:120-207 semantics) -> bytes; checks the CRC."""
     out = bytearray()
