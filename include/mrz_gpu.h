@@ -4,11 +4,15 @@
  * /root/reference/src/rzip.c as cited; plain pointers and sizes only, no CUDA or torch types.
  * The host side (modern-rzip_b200/host/rzip_fd.c) keeps the reference's
  *     void rzip_fd(rzip_control *control, int fd_in, int fd_out)         (include/rzip.h:25)
- * and calls mrz_rzip_chunk() where the reference calls hash_search()      (src/rzip.c:507, :773).
+ * and calls into this library where the reference calls hash_search()     (src/rzip.c:507, :773).
  *
  * All functions return 0 on success or a negative MRZ_E_* code; mrz_last_error() gives text.
  * There is NO CPU fallback: without a CUDA device every compute entry point fails with
- * MRZ_E_NODEVICE.
+ * MRZ_E_NODEVICE.  The library reads no environment variables; everything tunable is in mrz_config.
+ *
+ * Threading: calls on DIFFERENT contexts may be made from different host threads at the same time
+ * (that is how the host overlaps the upload of chunk k+1 with the search of chunk k, and drives
+ * several GPUs); calls on one context must not overlap.
  */
 #ifndef MRZ_GPU_H
 #define MRZ_GPU_H
@@ -47,18 +51,32 @@ typedef struct {
     uint32_t crc32;           /* IEEE CRC32 of the chunk (rzip.c:662) */
     uint32_t reserved;
     double ms_kernels;        /* device time of the resident path (CUDA events), milliseconds */
-    double ms_tagscan, ms_automaton, ms_emit;   /* its parts */
+    double ms_tagscan, ms_automaton, ms_emit;   /* its parts: tag map (+ CRC), automaton launch, emission */
     int64_t gpu_launches;     /* kernels launched for this chunk */
 } mrz_result;
+
+/* Engine configuration (replaces every environment knob; zero = default). */
+typedef struct {
+    int32_t cluster_size;     /* CTAs per automaton: 1,2,4,8,16; 0 = as many as fit for the automata of a launch */
+    int32_t threads;          /* threads per CTA: 64..512, multiple of 32; 0 = 256 */
+    int32_t filter_log2_words;/* tag filter size: 2^x 64-bit words, 16..26; 0 = 24 (128 MiB) */
+    int32_t profile;          /* 1: collect the automaton's phase counters (mrz_get_profile) */
+    int32_t token_divisor;    /* initial token capacity = max_chunk / divisor (grown on demand); 0 = 128 */
+    int32_t poison;           /* debugging: fill every work buffer with 0xA5 at creation instead of leaving it as allocated */
+    int32_t reserved[2];
+} mrz_config;
 
 /* library / device ------------------------------------------------------------------------------ */
 int mrz_device_count(void);                       /* >=0, or MRZ_E_NODEVICE */
 const char *mrz_version(void);
 const char *mrz_last_error(const mrz_ctx *ctx);   /* ctx may be NULL: last error of a failed create */
+void mrz_config_default(mrz_config *cfg);
 
-/* A context owns one device's buffers for chunks up to max_chunk bytes: the chunk, the hash table
- * (levels[].mb_used MiB, rzip.c:518-531), candidate lists, tokens and the two output streams. */
+/* A context owns one device's buffers for chunks up to max_chunk bytes: the chunk and its tag map, one
+ * automaton slot (hash table levels[].mb_used MiB, rzip.c:518-531, filter, claims, tokens) and the two
+ * output streams. */
 int mrz_ctx_create(int device, int64_t max_chunk, mrz_ctx **out);
+int mrz_ctx_create_ex(int device, int64_t max_chunk, const mrz_config *cfg, mrz_ctx **out);
 void mrz_ctx_destroy(mrz_ctx *ctx);
 
 /* hash_search (rzip.c:507-667) for one chunk, host buffers in and out.
@@ -67,38 +85,52 @@ void mrz_ctx_destroy(mrz_ctx *ctx);
 int mrz_rzip_chunk(mrz_ctx *ctx, const uint8_t *chunk, int64_t n, const mrz_params *prm,
                    uint8_t *s0, int64_t s0_cap, uint8_t *s1, int64_t s1_cap, mrz_result *res);
 
-/* The same in three steps, for pipelining and for device-resident timing. */
+/* The same in steps, for pipelining and for device-resident timing. */
 int mrz_upload(mrz_ctx *ctx, const uint8_t *chunk, int64_t n);                 /* H2D, synchronous */
+/* piecewise upload (read -> pinned slab -> H2D of slab i while slab i+1 is being read): parts may be queued
+ * back to back; src must stay valid until mrz_upload_wait (a pinned src makes the copy asynchronous) */
+int mrz_upload_part(mrz_ctx *ctx, int64_t offset, const uint8_t *src, int64_t len);
+int mrz_upload_wait(mrz_ctx *ctx);                                              /* all queued parts have landed */
+int mrz_upload_finish(mrz_ctx *ctx, int64_t n);                                /* pads the chunk; call once after the last part */
 int mrz_run_resident(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result *res); /* kernels only */
 int mrz_download(mrz_ctx *ctx, uint8_t *s0, int64_t s0_cap, uint8_t *s1, int64_t s1_cap); /* D2H */
+/* piecewise download of stream `streamno` (0/1) of the last emission: bytes [offset, offset+len) */
+int mrz_download_part(mrz_ctx *ctx, int streamno, int64_t offset, uint8_t *dst, int64_t len);
 
 /* Variant-parallel chunks (the multi-GPU / multi-chunk answer to the one scalar that links chunks: the
  * function-local `static victim_round` of insert_hash, rzip.c:259, which enters the next chunk and is
  * output-relevant as soon as that chunk evicts a victim, rzip.c:278-291).  Instead of waiting for the previous
  * chunk's value, the automaton of a resident chunk is run for EVERY possible victim_round_in (0 .. max_chain_len-1,
- * levels[] rzip.c:65-73) side by side — one CTA, one hash table and one token list per variant; the automaton uses
- * 1 of 148 SMs — and the caller keeps the variant the chain selects.
- *   mrz_ctx_create_variant: a context that shares the parent's chunk bytes and stream-1 buffer and owns its own
- *                           table / filter / claims / candidate lists / tokens (≈ 0.3 GB + 0.1 x max_chunk).
+ * levels[] rzip.c:65-73) in ONE kernel launch — one thread-block cluster, one hash table and one token list per
+ * variant, the tag map shared — and the caller keeps the variant the chain selects.
+ *   mrz_ctx_create_variant: a context that shares the parent's chunk bytes, tag map and stream-1 buffer and owns
+ *                           its own table / filter / claims / tokens (≈ 0.25 GB + tokens).
  *   mrz_run_automaton:      hash_search up to the token list (no streams): counters, victim_round_out, n_ops.
  *   mrz_run_emit:           put_literal/put_match/CRC (rzip.c:161-227, :617-666) for the tokens of the last
- *                           mrz_run_automaton of this context; then mrz_download from the same context.
+ *                           automaton run of this context; then mrz_download from the same context.
  *   mrz_run_variants:       ctxs[v] runs with victim_round_in = v (prm->victim_round_in is ignored); res[v] as
- *                           mrz_run_automaton.  ctxs[0] may be the parent.  The variants run one after another
- *                           unless MRZ_VARIANTS_CONCURRENT=1 is set, in which case all nvar automata run side by
- *                           side (one host thread + stream each; experimental). */
+ *                           mrz_run_automaton.  ctxs[0] is the parent, the others its variants.
+ *   mrz_run_many:           the general form: `count` automata in one launch, ctxs[i] with n[i] / prms[i]; contexts
+ *                           may belong to different chunks (parents) of the same device. */
 int mrz_ctx_create_variant(mrz_ctx *parent, mrz_ctx **out);
 int mrz_run_automaton(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result *res);
 int mrz_run_emit(mrz_ctx *ctx, mrz_result *res);
 int mrz_run_variants(mrz_ctx *const *ctxs, int nvar, int64_t n, const mrz_params *prm, mrz_result *res);
+int mrz_run_many(mrz_ctx *const *ctxs, int count, const int64_t *n, const mrz_params *prms, mrz_result *res);
 
 /* Pinned host memory for the e2e path (cudaHostAlloc); optional. */
 void *mrz_host_alloc(int64_t bytes);
 void mrz_host_free(void *p);
 
+/* MRZ_NDBG (64) phase counters of the last automaton run of this context (cfg.profile = 1), and the launch
+ * geometry it used: geom[0] = CTAs per cluster, geom[1] = threads per CTA, geom[2] = automata in the launch. */
+int mrz_get_profile(mrz_ctx *ctx, int64_t counters[64], int32_t geom[3]);
+
 /* Building blocks exposed for parity tests (each is also used inside mrz_run_resident). */
-/* single_full_tag for every position (rzip.c:348-358): tags[p] for p in [0, n-30). */
+/* single_full_tag for every position (rzip.c:348-358): tags[p] for p in [0, count), count <= n-30. */
 int mrz_debug_tags(mrz_ctx *ctx, int64_t n, const int64_t hash_index[256], int64_t *tags_out, int64_t count);
+/* the trailing-ones map of the resident chunk (tagmap.cu): map[p] for p in [0, n), summary[b] for b in [0, (n+63)/64) */
+int mrz_debug_tagmap(mrz_ctx *ctx, int64_t n, const int64_t hash_index[256], uint8_t *map_out, uint8_t *summary_out);
 /* per-chunk CRC32 as gcry_md_write(crc_handle) accumulates it (rzip.c:494, :648-662) */
 int mrz_debug_crc32(mrz_ctx *ctx, int64_t n, uint32_t *crc_out);
 /* un-split match tokens of the last run: triples (pos, len, ofs) */

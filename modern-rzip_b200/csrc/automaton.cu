@@ -1,4 +1,4 @@
-// automaton.cu — the table automaton of hash_search, exact, as one 1024-thread CTA per chunk.
+// automaton.cu — the table automaton of hash_search, exact, as ONE persistent launch of thread-block clusters.
 //
 // Reproduces, operation for operation, the table semantics of src/rzip.c:
 //   find_best_match (rzip.c:426-462), insert_hash (rzip.c:256-301), clean_one_from_hash
@@ -6,97 +6,122 @@
 //   hash_search (rzip.c:571-599).
 //
 // B200 design (not the reference's loop):
-//   * the per-byte loop is gone: candidates (positions whose tag passes the lookup gate) come from
-//     tag_scan.cu as a position-ordered list;
-//   * the table is stored as two arrays (tags[], offs[]) instead of the reference's 16-byte
-//     entries: walks only ever look at tags, so a probe step moves half the bytes;
-//   * BATCHED SPECULATION: the next <=1024 candidate ops are *planned* in parallel, one thread
-//     each, against the live table read-only (insert walk, one level of displacement), then
-//     committed in order; the first op that cannot commit from its plan cuts the batch, runs
-//     exactly (below), and the batch carries on behind it - also behind an emitted match;
+//   * ONE LAUNCH, MANY AUTOMATA, NO HOST IN THE LOOP.  The grid is (automata) x (CTAs per cluster); automaton a —
+//     a chunk, or one victim_round_in variant of a chunk — is cluster a and walks its whole chunk before it
+//     returns.  A cluster is CL = 1..16 CTAs of T threads; a batch is B = CL*T candidate ops, one per thread.
+//     One SM can only keep ~1 uncoalesced request per clock in flight, which is what bounded the one-CTA design;
+//     a cluster spreads every phase of a batch over CL SMs and pays ~400 clk per cluster barrier
+//     (barrier.cluster, hardware) instead of ~4000 for a grid barrier through L2.  The state the CTAs share
+//     (running state, batch arrays, sweep queue) lives in a per-automaton block of global memory that stays in L2;
+//     every field has ONE writer between two barriers.
+//   * the per-byte loop is gone: candidates come from the bitness map of tagmap.cu.  Each batch the cluster reads
+//     the 64:1 summary of the next stretch of the chunk, compacts the non-empty blocks, reads those 64 map bytes
+//     into a bit mask and compacts the positions (two cluster-wide prefix sums); the 64-bit tag of a candidate is
+//     recomputed from the bytes (31 look-ups);
+//   * the table is stored as two arrays (tags[], offs[]): walks only ever look at tags;
+//   * BATCHED SPECULATION: the B ops are *planned* in parallel against the live table read-only (insert walk,
+//     one level of displacement) and committed in order; the first op that cannot commit from its plan cuts the
+//     batch.  If all it suffers from is a conflict, everything behind the cut that lost its plan is simply planned
+//     AGAIN against the updated table and the batch goes on (a round costs a few barriers); only ops that need a
+//     lookup, a deep displacement, an emission or a serial sweep step run on the exact executor (below);
 //   * EXACT CONFLICT RULE: an insert only ever RAISES the trailing-one count of the slot it writes
-//     (empty / due-for-sweep -> >= need, lesser -> greater), so a walk that passed a slot still
-//     passes it: only a write to a walk's own STOP slot can change its outcome, and an entry due for
-//     sweeping stops every walk, so a slot of the sweep queue can only be a stop slot too.  Plans
-//     CLAIM their stop slots with atomicMin((epoch, op index)) in a 16 MiB array (no hash, no
-//     clearing); a plan is invalid iff an earlier op claims one of its stop slots;
-//   * FORWARDING: when the earlier op's tag is no stop for the later walk (and not equal to its
-//     tag), the later plan walks on from the next slot, re-claims and remembers the dependency;
-//     iterated to a fixed point with __syncthreads rounds;
-//   * TAG FILTER: a blocked Bloom filter over every tag inserted in this chunk (one 64-bit word,
-//     three bits per tag, no false negatives).  A negative answer proves that no entry with an
-//     equal tag exists, so find_best_match's walk to the end of the probe cluster - hundreds of
-//     slots at high mask levels - is skipped altogether, and lookup-only ops touch no table slot;
-//   * GROUP SUMMARY: the insert walk looks for the first slot whose tag has fewer trailing one bits
-//     than `need` (empty, due for sweeping, or lesser than the new tag: rzip.c:264-277).  Global
-//     memory (L2) holds, per group of 16 slots, a 16-bit thermometer of the minimum trailing-one
-//     count; a walk skips 128 slots per 128-bit summary load and reads one group (256-bit loads);
-//     lowering is one atomicAnd, repair one atomicOr;
+//     (empty / due-for-sweep -> >= need, lesser -> greater), so a walk that passed a slot still passes it: only a
+//     write to a walk's own STOP slot can change its outcome, and an entry due for sweeping stops every walk, so a
+//     slot of the sweep queue can only be a stop slot too.  Plans CLAIM their stop slots with
+//     atomicMin((epoch, op index)) in a 16 MiB array (no hash, no clearing); a plan is invalid iff an earlier op
+//     claims one of its stop slots;
+//   * FORWARDING: when the earlier op's tag is no stop for the later walk (and not equal to its tag), the later
+//     plan walks on from the next slot, re-claims and remembers the dependency; iterated to a fixed point;
+//   * TAG FILTER: a blocked Bloom filter over every tag inserted in this chunk (no false negatives).  A negative
+//     answer proves that no entry with an equal tag exists, so find_best_match's walk to the end of the probe
+//     cluster is skipped altogether, and lookup-only ops touch no table slot;
+//   * GROUP SUMMARY: per group of 8 slots a 16-bit thermometer of the minimum trailing-one count (L2 resident);
+//     an insert walk skips 64 slots per 128-bit summary load; lowering is one atomicAnd, repair one atomicOr;
 //   * TWINS: positions p and p+1 with equal tags (buf[p] == buf[p+31]) are planned as a pair;
-//   * the sweep of clean_one_from_hash is pre-resolved per batch: a parallel scan keeps a queue of
-//     the next eligible slots, so the n-th overflow of a batch zeroes the n-th queued slot;
-//   * SERIAL OPS USE THE WHOLE CTA: the probe sequence of find_best_match is walked 4096 slots per
-//     step, equal-tag candidates are compared by the 32 warps in parallel (__ballot_sync / __ffs
-//     memcmp), long matches are extended 32 KiB per step by all threads; the insert walks of the
-//     cut op are warp-cooperative (first probe + 4096 slots of summary in one round trip).
-//   oracle/spec_model.c is the CPU model of the speculation rules; tests/test_spec_model.py proves
-//   it equivalent to the sequential restatement, tests/test_sim_parity.py runs this very file on
-//   the CPU emulator, tests/test_gpu_parity.py on the B200.
+//   * the sweep of clean_one_from_hash is pre-resolved: a parallel scan keeps a ring of the next eligible slots, so
+//     the n-th overflow of a batch zeroes the n-th queued slot.  A plan that overwrites a queued slot conflicts
+//     only when the sweep can reach that slot within this batch; otherwise it commits and the ring is cut there;
+//   * THE EXACT EXECUTOR (rank 0 of the cluster): the probe sequence of find_best_match is walked 4*T slots per
+//     step, equal-tag candidates are compared by the warps in parallel (__ballot_sync / __ffs memcmp), long
+//     matches are extended by all threads; the insert walks are warp-cooperative.
+//   oracle/spec_model.c is the CPU model of the speculation rules; tests/test_sim_parity.py runs this very file on
+//   the CPU emulator (clusters included), tests/test_gpu_parity.py on the B200.
 #ifndef MRZ_CUSIM
 #include <mutex>
 #endif
+#include <string.h>
 #include "mrz_common.cuh"
+#include "automaton.h"
 
 #define FULL 0xffffffffu
-#define AT 1024            // threads per CTA = ops per batch
-#define EQ_CAP 4096        // eligible-slot ring (power of two)
 #define LK_XCAP 2048       // a candidate still matching after this many bytes is extended by the whole CTA
 #define LK_XCAP2 (1 << 20)  // ... unless more than two candidates are that long: then the warps go on in parallel up to here
 #define LK_CAP 256         // equal-tag entries the CTA-wide lookup collects; more: the warp walk
-#define DENSE_LOOP 0       // 1: after an emission warp 0 examines the next 32 positions from the bytes (measured slower than letting the batch carry on)
-#define FWD_ITERS 6         // forwarding rounds per batch; later collisions go serial
-#define MAXWALK 16384      // longer insert walks are left to the serial path
-#define WLOG_CAP 64
+#define FWD_ITERS 6        // forwarding rounds per conflict phase; later collisions are planned again after the cut
+#define MAXWALK 16384      // longer insert walks are left to the exact executor
 #define GRP 8              // slots per summary group (= one 64-byte read of tags)
 #define GRP_SHIFT 3
 #define DUP_SALT 0x5bd1e9955bd1e995LL
 
-enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8, F_FOLLOW = 16, F_W2ELIG = 32, F_W1ELIG = 64 };
+enum { F_COMPLEX = 1, F_INSERT = 2, F_W1 = 4, F_CONF = 8, F_FOLLOW = 16, F_W2ELIG = 32, F_W1ELIG = 64,
+       F_ZONE = 128 };   // F_ZONE: the conflict is with the sweep, not with another plan: planning again cannot resolve it
 #define MAXDEP 3            // claimed slots a plan may walk past (forwarding)
+#define IDX_BITS 14         // MRZ_MAXB = 2^14 ops per batch
 #ifdef MRZ_CUSIM
 #define CLAIM_EPOCH_MAX 700u       // the CPU-emulator tests exercise the wrap-around (wipe + restart) path
 #else
-#define CLAIM_EPOCH_MAX 0x1FFFF0u
+#define CLAIM_EPOCH_MAX 0x1FFF0u
 #endif
-__device__ __forceinline__ unsigned claim_key(unsigned epoch, int j, int is_w1) { return ((0x1FFFFFu - epoch) << 11) | ((unsigned)j << 1) | (unsigned)is_w1; }
+#define EPOCH_TOP 0x1FFFFu
+__device__ __forceinline__ unsigned claim_key(unsigned epoch, int j, int is_w1) {
+    return ((EPOCH_TOP - epoch) << (IDX_BITS + 1)) | ((unsigned)j << 1) | (unsigned)is_w1;
+}
+#define KEY_IDX(o) ((int)(((o) >> 1) & (unsigned)(MRZ_MAXB - 1)))
+#define KEY_EPOCH(o) ((o) >> (IDX_BITS + 1))
+
+// ---- range checks of the -DMRZ_CHECK build: a violation records (site, index, bound) and clamps the index ----
+#ifdef MRZ_CHECK
+#define CHK(sh, site, idx, bound)                                                                    \
+    do {                                                                                             \
+        if ((i64)(idx) < 0 || (i64)(idx) >= (i64)(bound)) {                                          \
+            (sh)->run.error = 100 + (site); (sh)->err_a = (i64)(idx); (sh)->err_b = (i64)(bound);    \
+            (idx) = 0;                                                                               \
+        }                                                                                            \
+    } while (0)
+#else
+#define CHK(sh, site, idx, bound) do { } while (0)
+#endif
 
 // Blocked Bloom filter over inserted tags: word index and 3-bit mask (oracle/spec_model.c filt_hash).
-#define FILT_BITS 24
-__device__ __forceinline__ void filt_hash(i64 tag, u64 &word, u64 &bits) {
+struct Filt {
+    u64 *w;
+    int shift;   // 64 - log2(words)
+};
+__device__ __forceinline__ void filt_hash(const Filt &F, i64 tag, u64 &word, u64 &bits) {
     u64 x = (u64)tag;
     x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
-    word = x >> (64 - FILT_BITS);
+    word = x >> F.shift;
     bits = ((u64)1 << (x & 63)) | ((u64)1 << ((x >> 6) & 63)) | ((u64)1 << ((x >> 12) & 63));
 }
-__device__ __forceinline__ bool filt_query(const u64 *F, i64 tag) {
+__device__ __forceinline__ bool filt_query(const Filt &F, i64 tag) {
     u64 w, b;
-    filt_hash(tag, w, b);
-    return (__ldcg(F + w) & b) == b;
+    filt_hash(F, tag, w, b);
+    return (__ldcg(F.w + w) & b) == b;
 }
-__device__ __forceinline__ void filt_set(u64 *F, i64 tag) {
+__device__ __forceinline__ void filt_set(const Filt &F, i64 tag) {
     u64 w, b;
-    filt_hash(tag, w, b);
-    atomicOr((unsigned long long *)(F + w), (unsigned long long)b);
+    filt_hash(F, tag, w, b);
+    atomicOr((unsigned long long *)(F.w + w), (unsigned long long)b);
 }
 
-__device__ __forceinline__ int tz1c(i64 t) {   // trailing one bits, capped at 15 (summary nibble)
+__device__ __forceinline__ int tz1c(i64 t) {   // trailing one bits, capped at 15 (summary thermometer)
     int z = tz1(t);
     return z > 15 ? 15 : (z < 0 ? 15 : z);
 }
-// GROUP SUMMARY, in global memory (L2 resident, 512 KiB for the 64 MiB table): per group of 16 slots a 16-bit
+// GROUP SUMMARY, in global memory (L2 resident, 1 MiB for the 64 MiB table): per group of 8 slots a 16-bit
 // thermometer - bit i set <=> every tag of the group has more than i trailing one bits (as far as is known: the
 // code is a lower bound, all-zero = nothing known).  Lowering is one atomicAnd, raising one atomicOr: both fire
-// and forget, so plans on any SM and commits on the main CTA maintain it without read-modify-write loops.
+// and forget, so plans and commits on any SM maintain it without read-modify-write loops.
 __device__ __forceinline__ void sum_raise(u32 *gs, i64 g, int v) {      // plan phases: the whole group was seen, min = v
     if (v > 0) atomicOr(gs + (g >> 1), (((1u << v) - 1u) & 0x7fffu) << ((g & 1) * 16));
 }
@@ -104,20 +129,139 @@ __device__ __forceinline__ void sum_lower(u32 *gs, i64 g, int v) {      // commi
     atomicAnd(gs + (g >> 1), ~(0xffffu << ((g & 1) * 16)) | ((((1u << v) - 1u) & 0x7fffu) << ((g & 1) * 16)));
 }
 
-__device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int need, i64 hsize, i64 &stop_tag);
+// ---- cluster plumbing ----------------------------------------------------------------------------
+#ifdef MRZ_CUSIM
+__device__ __forceinline__ int cl_rank() { return cusim::cluster_rank(); }
+__device__ __forceinline__ int cl_size() { return cusim::cluster_size(); }
+__device__ __forceinline__ void csync(int) {
+    __syncthreads();
+    if (threadIdx.x == 0) cusim::sync_cluster();
+    __syncthreads();
+}
+#else
+__device__ __forceinline__ int cl_rank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return (int)r; }
+__device__ __forceinline__ int cl_size() { unsigned r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return (int)r; }
+// Barrier over all threads of the cluster; orders their global-memory accesses (release / acquire at cluster scope).
+__device__ __forceinline__ void csync(int CL) {
+    if (CL == 1) { __syncthreads(); return; }
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+#endif
 
-// Running state of the automaton, shared by the whole CTA (rzip_state, mrzip_private.h:388-416).
+// Running state of the automaton (rzip_state, mrzip_private.h:388-416).
 struct Run {
     i64 p, last, cur_p, cur_len, cur_ofs, min_mask, ins_mask, clean_ptr, count, vr;
     i64 hits, misses, inserts, vevents, nops, ntok;
-    int error;
+    int error, pad;
 };
 
+#define NSITE 6   // cluster-wide prefix sums per batch, each with its own exchange array
+// State shared by the CTAs of one automaton, in global memory (L2).  One writer per field between two barriers.
+struct Shared {
+    Run run;
+    i64 err_a, err_b;
+    i64 gp;                  // gather cursor: every position < gp has been gathered or skipped
+    i64 gp_next;             // atomicMin target while a batch is gathered
+    i64 e_scan;              // slots in [run.clean_ptr, e_scan) have been examined for the ring
+    unsigned e_idx, e_cnt;   // ring counters (monotonic)
+    int nr;                  // ops in the current batch
+    int exhausted;           // the gather reached the end of the chunk
+    int pos, ended, jumped, nlog;
+    int changed[2];
+    int qcut;                // atomicMin: smallest queued slot that a committed plan overwrote (0x7fffffff: none)
+    int pad0;
+    unsigned long long kcut; // cut search: min over (~round << 32 | op index << 1 | needs the exact executor)
+    unsigned long long tot[NSITE][MRZ_MAXCL];
+    int wlog[MRZ_WLOG_CAP];
+    int E[MRZ_EQ_CAP];       // ring of eligible slots, ascending
+    i64 b_pos[MRZ_MAXB], b_tag[MRZ_MAXB];   // batch: position / tag of op j
+    int pl_fl[MRZ_MAXB], pl_w2[MRZ_MAXB];   // plan flags / insert slot of op j (twins, commit)
+    unsigned long long pre[MRZ_MAXB];       // inclusive prefix over ops holding a valid plan
+    i64 blk[MRZ_MAXB];       // gather: non-empty 64-position blocks
+};
+typedef volatile Shared VS;
+
+#define PK_D(x) ((unsigned)((x) & 0xffffu))            // hash_count delta
+#define PK_I(x) ((unsigned)(((x) >> 16) & 0xffffu))    // inserts
+#define PK_M(x) ((unsigned)(((x) >> 32) & 0xffffu))    // tag misses (twins)
+#define PK_V(x) ((unsigned)(((x) >> 48) & 0xffffu))    // ops
+
+extern "C" size_t mrz_shared_bytes() { return sizeof(Shared); }
+
+// ---- shared memory of a CTA ----------------------------------------------------------------------
+struct Smem {
+    i64 hx[256];
+    i64 stk[3 * 64];
+    unsigned long long wsum[40];
+    unsigned long long cbase, ctotal;
+    int lk_fe, lk_n, red, pad;
+    int lk_pos[LK_CAP];     // CTA-wide lookup: positions (relative to the primary slot) of equal tags, ascending
+    i64 lk_len[LK_CAP], lk_rev[LK_CAP], lk_off[LK_CAP];   // match_len results per candidate
+    i64 lk_f[LK_CAP], lk_r[LK_CAP];                       // capped forward / backward lengths (first pass)
+    int wlog[MRZ_WLOG_CAP];
+};
+extern "C" size_t mrz_automaton_smem_bytes() { return sizeof(Smem); }
+
+#ifdef MRZ_CUSIM
+#define MRZ_SMEM_PTR(T, name) T *name = reinterpret_cast<T *>(cusim::dyn_smem())
+#else
+#define MRZ_SMEM_PTR(T, name) extern __shared__ __align__(16) unsigned char name##_raw[]; T *name = reinterpret_cast<T *>(name##_raw)
+#endif
+
+// exclusive prefix sum of v over the CTA (thread order); total in `total`.  Two block barriers.
+__device__ __forceinline__ unsigned long long block_excl_scan(unsigned long long v, unsigned long long *wsum, unsigned long long &total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    unsigned long long inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned long long u = __shfl_up_sync(FULL, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) wsum[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        unsigned long long w = lane < nw ? wsum[lane] : 0, wi = w;
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned long long u = __shfl_up_sync(FULL, wi, o);
+            if (lane >= o) wi += u;
+        }
+        wsum[lane] = wi - w;
+        if (lane == 31) wsum[32] = wi;
+    }
+    __syncthreads();
+    total = wsum[32];
+    const unsigned long long r = wsum[wid] + inc - v;
+    __syncthreads();   // wsum may be reused right away
+    return r;
+}
+
+// exclusive prefix sum of v over the CLUSTER (rank-major, then thread order); total in `total`.  One cluster barrier.
+__device__ __forceinline__ unsigned long long cluster_excl_scan(unsigned long long v, Smem *S, VS *sh, int site, int CL, int rank,
+                                                                unsigned long long &total) {
+    unsigned long long btot;
+    const unsigned long long ex = block_excl_scan(v, S->wsum, btot);
+    if (CL == 1) { total = btot; return ex; }
+    if (threadIdx.x == 0) sh->tot[site][rank] = btot;
+    csync(CL);
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        const unsigned long long t = lane < CL ? sh->tot[site][lane] : 0ULL;
+        unsigned long long below = lane < rank ? t : 0ULL, all = t;
+        for (int o = 16; o; o >>= 1) { below += __shfl_xor_sync(FULL, below, o); all += __shfl_xor_sync(FULL, all, o); }
+        if (lane == 0) { S->cbase = below; S->ctotal = all; }
+    }
+    __syncthreads();
+    total = S->ctotal;
+    const unsigned long long r = S->cbase + ex;
+    __syncthreads();
+    return r;
+}
+
+// ---- the exact executor: one warp runs one op on the live table with the reference semantics -----
 struct Warp {
     // constants
     const u8 *buf;
     i64 *ttag, *toff;   // the table: tags and offsets (struct hash_entry, rzip.c:59-62, split in two arrays)
-    u64 *filt;
+    Filt filt;
     u32 *gsum;          // group summary (global memory)
     Token *toks;
     i64 n, end, hmask, hsize, limit, tok_cap;
@@ -126,24 +270,25 @@ struct Warp {
     i64 p, last, cur_p, cur_len, cur_ofs, min_mask, ins_mask, clean_ptr, count, vr;
     i64 hits, misses, inserts, vevents, nops, ntok;
     int error;
-    // write log of the current op: (slot << 1) | zeroed; nlog > WLOG_CAP means overflow
+    // write log of the current op: (slot << 1) | zeroed; nlog > MRZ_WLOG_CAP means overflow
     int *wlog;
     int nlog;
     i64 clean_hint;   // no eligible slot exists in [clean_ptr, clean_hint)
-    i64 *prof;        // MRZ_PROFILE: cycles / calls of the parts of a serial op (dbg[20..])
+    i64 *prof;        // profile build: cycles / calls of the parts of a serial op
 
-    __device__ __forceinline__ void load(const Run &r) {
-        p = r.p; last = r.last; cur_p = r.cur_p; cur_len = r.cur_len; cur_ofs = r.cur_ofs;
-        min_mask = r.min_mask; ins_mask = r.ins_mask; clean_ptr = r.clean_ptr; count = r.count; vr = r.vr;
-        hits = r.hits; misses = r.misses; inserts = r.inserts; vevents = r.vevents; nops = r.nops; ntok = r.ntok;
-        error = r.error;
+    __device__ __forceinline__ void load(VS *sh) {
+        p = sh->run.p; last = sh->run.last; cur_p = sh->run.cur_p; cur_len = sh->run.cur_len; cur_ofs = sh->run.cur_ofs;
+        min_mask = sh->run.min_mask; ins_mask = sh->run.ins_mask; clean_ptr = sh->run.clean_ptr; count = sh->run.count; vr = sh->run.vr;
+        hits = sh->run.hits; misses = sh->run.misses; inserts = sh->run.inserts; vevents = sh->run.vevents; nops = sh->run.nops;
+        ntok = sh->run.ntok; error = sh->run.error;
     }
-    __device__ __forceinline__ void store(Run &r) const {
+    __device__ __forceinline__ void store(VS *sh) const {
         if (lane == 0) {
-            r.p = p; r.last = last; r.cur_p = cur_p; r.cur_len = cur_len; r.cur_ofs = cur_ofs;
-            r.min_mask = min_mask; r.ins_mask = ins_mask; r.clean_ptr = clean_ptr; r.count = count; r.vr = vr;
-            r.hits = hits; r.misses = misses; r.inserts = inserts; r.vevents = vevents; r.nops = nops; r.ntok = ntok;
-            r.error = error;
+            sh->run.p = p; sh->run.last = last; sh->run.cur_p = cur_p; sh->run.cur_len = cur_len; sh->run.cur_ofs = cur_ofs;
+            sh->run.min_mask = min_mask; sh->run.ins_mask = ins_mask; sh->run.clean_ptr = clean_ptr; sh->run.count = count; sh->run.vr = vr;
+            sh->run.hits = hits; sh->run.misses = misses; sh->run.inserts = inserts; sh->run.vevents = vevents; sh->run.nops = nops;
+            sh->run.ntok = ntok;
+            if (error) sh->run.error = error;
         }
     }
     // table writes of the serial path: lane 0 stores, the write is logged, the summary follows
@@ -152,18 +297,16 @@ struct Warp {
             __stcg(toff + slot, off);
             __stcg(ttag + slot, tag);
             sum_lower(gsum, slot >> GRP_SHIFT, tag ? tz1c(tag) : 0);
-            if (nlog < WLOG_CAP) wlog[nlog] = (int)(slot << 1) | (tag ? 0 : 1);
+            if (nlog < MRZ_WLOG_CAP) wlog[nlog] = (int)(slot << 1) | (tag ? 0 : 1);
         }
         nlog++;
         __syncwarp();
     }
 
-    // rzip.c:372-397.  Returns total length (0 if < 31) and the backward part in rev.
-    // The first step compares 256 bytes (most candidates fail there); a match that survives it is extended 4 KiB per
-    // step - 16 independent 8-byte compares per lane in flight - so that long matches run at memory speed, not at
-    // one dependent round trip per 256 bytes.
+    // rzip.c:372-397.  Longest common prefix of buf[a0..] / buf[b0..] (fwd) or longest common suffix of buf[..a0) /
+    // buf[..b0), at most maxlen bytes.  The first step compares 256 bytes (most candidates fail there); a match that
+    // survives it is extended 4 KiB per step - 16 independent 8-byte compares per lane in flight.
     __device__ __forceinline__ i64 extend(i64 a0, i64 b0, i64 maxlen, bool fwd) {
-        // fwd: longest common prefix of buf[a0..] and buf[b0..]; else longest common suffix of buf[..a0) and buf[..b0)
         i64 f = 0;
         int K = 1;
         while (f < maxlen) {
@@ -251,7 +394,7 @@ struct Warp {
     }
 
     // The selection half of find_best_match (rzip.c:445-456) over candidates the CTA has already compared
-    // (k_automaton: every warp ran match_len for a share of the equal-tag slots; results in slot order).
+    // (every warp ran match_len for a share of the equal-tag slots; results in slot order).
     __device__ __forceinline__ i64 lookup_pre(i64 &bofs, i64 &brev, int n, const i64 *len, const i64 *rv, const i64 *off) {
         i64 best = 0;
         for (int q = 0; q < n; q++) {
@@ -316,7 +459,8 @@ struct Warp {
             }
             if (displaced) {
                 if (sp >= 60) { error = 3; return; }
-                stk[3 * sp] = target; stk[3 * sp + 1] = ct; stk[3 * sp + 2] = coff;
+                if (lane == 0) { stk[3 * sp] = target; stk[3 * sp + 1] = ct; stk[3 * sp + 2] = coff; }
+                __syncwarp();
                 sp++;
                 coff = __ldcg(toff + target);
                 ct = otag;
@@ -331,8 +475,8 @@ struct Warp {
         }
     }
 
-    // find_stop for the serial path, by one warp: the first probe and 32 summary quad-words (4096 slots of summary) are
-    // fetched in ONE round trip, the candidate group in a second (16 lanes, one tag each); a stale candidate is repaired
+    // find_stop for the serial path, by one warp: the first probe and 32 summary quad-words (2048 slots of summary) are
+    // fetched in ONE round trip, the candidate group in a second (8 lanes, one tag each); a stale candidate is repaired
     // and the next one taken from the summary already in registers.  Same result as find_stop.
     __device__ __forceinline__ i64 find_stop_warp(i64 h, int need, i64 &stop_tag) {
         if (h >= hsize) return -1;
@@ -341,7 +485,7 @@ struct Warp {
         if (ngroups > ngroups_all) ngroups = ngroups_all;
         const u32 pass_bit = 1u << ((need > 15 ? 15 : need) - 1);
         const i64 g0 = h >> GRP_SHIFT;
-        // round trip 1: the rest of the first group (lanes 0..15) and the summary of the groups behind it (all lanes)
+        // round trip 1: the rest of the first group (lanes 0..7) and the summary of the groups behind it (all lanes)
         i64 wbase = (g0 + 1) >> 3;                       // first summary quad-word (8 groups each)
         uint4 w4 = __ldcg(reinterpret_cast<const uint4 *>(gsum + ((wbase + lane) << 2)));
         {
@@ -373,7 +517,7 @@ struct Warp {
                 if (gg >= g && gg < ngroups && !((wv[q >> 1] >> ((q & 1) * 16)) & pass_bit)) cand |= 1u << q;
             }
             const unsigned lm = __ballot_sync(FULL, cand != 0);
-            if (!lm) {                                   // nothing in these 4096 slots: next window of summary
+            if (!lm) {                                   // nothing in these 2048 slots: next window of summary
                 g = (wbase + 32) << 3;
                 wbase += 32;
                 if (g >= ngroups) return -1;
@@ -402,7 +546,7 @@ struct Warp {
         }
     }
 
-    // rzip.c:256-301 for a tag that has no equal entry in the table: every level of the displacement chain is a
+    // rzip.c:256-301 for a tag whose equal entries (if any) are known: every level of the displacement chain is a
     // summary-accelerated find_stop walk (all walks see the table before any write, as the reference's recursion does).
     // Returns false, having written nothing, when some level needs the general walk of insert().
     // n_eq / eq_pos: the slots (relative to the primary slot, ascending) that hold a tag equal to t, as collected by the
@@ -485,15 +629,15 @@ struct Warp {
 
     // One position that passed the lookup gate (rzip.c:573-599).  Returns true when a match was
     // emitted (p jumped to last_match).
-    // pre_n >= 0: the CTA has already walked the probe sequence and compared the pre_n equal-tag candidates
-    __device__ __noinline__ bool op(i64 pp, i64 t, i64 *stk, int pre_n = -1, const i64 *pre_len = nullptr, const i64 *pre_rev = nullptr,
-                                    const i64 *pre_off = nullptr, const int *pre_pos = nullptr) {
+    // pre_n >= 0: the CTA has already walked the probe sequence and compared the pre_n equal-tag candidates;
+    // pre_n == -2: the filter says no equal tag exists; pre_n == -1: ask the filter / walk on this warp.
+    __device__ __noinline__ bool op(i64 pp, i64 t, i64 *stk, int pre_n, const i64 *pre_len, const i64 *pre_rev,
+                                    const i64 *pre_off, const int *pre_pos) {
 #define PROF(slot, t0) do { if (prof && lane == 0) { prof[slot] += clock64() - (t0); prof[(slot) + 1] += 1; } } while (0)
         nops++;
         i64 bofs = 0, brev = 0;
         i64 c0 = clock64();
         const bool maybe = pre_n >= 0 ? true : pre_n == -2 ? false : filt_query(filt, t);   // negative: nothing to find
-        PROF(0, c0); c0 = clock64();
         i64 best = 0;
         if (maybe) best = pre_n >= 0 ? lookup_pre(bofs, brev, pre_n, pre_len, pre_rev, pre_off) : lookup(t, pp, bofs, brev);
         if (maybe) PROF(2, c0);
@@ -525,109 +669,9 @@ struct Warp {
             return true;
         }
         return false;
+#undef PROF
     }
 };
-
-__device__ __forceinline__ i64 xor_scan_incl(i64 v, int lane) {
-    for (int o = 1; o < 32; o <<= 1) {
-        i64 u = __shfl_up_sync(FULL, v, o);
-        if (lane >= o) v ^= u;
-    }
-    return v;
-}
-
-// First index in [lo, hi) whose cand_pos >= rel (hi if none); 32-ary search by one warp.
-__device__ __forceinline__ i64 list_seek(const u32 *cand_pos, i64 lo, i64 hi, u32 rel, int lane) {
-    while (hi - lo > 32) {
-        i64 len = hi - lo;
-        i64 idx = lo + (len * lane) / 32;
-        u32 v = __ldcg(cand_pos + idx);
-        unsigned ge = __ballot_sync(FULL, v >= rel);
-        if (!ge) {
-            lo = lo + (len * 31) / 32 + 1;
-        } else {
-            int l = __ffs(ge) - 1;
-            if (l == 0) return lo;
-            i64 nlo = lo + (len * (l - 1)) / 32 + 1;
-            hi = lo + (len * l) / 32 + 1;
-            lo = nlo;
-        }
-    }
-    bool in = lo + lane < hi;
-    u32 v = in ? __ldcg(cand_pos + lo + lane) : 0xffffffffu;
-    unsigned ge = __ballot_sync(FULL, in && v >= rel);
-    return ge ? lo + (__ffs(ge) - 1) : hi;
-}
-
-// ---- shared memory of the CTA ------------------------------------------------------------------
-struct Smem {
-    i64 hx[256];
-    i64 stk[3 * 64];
-    i64 b_tag[AT];          // batch: tag of op j
-    Run run;
-    i64 e_scan;             // slots in [run.clean_ptr, e_scan) have been examined for the queue
-    i64 li;                 // next candidate-list index
-    u32 b_rel[AT];          // batch: position of op j relative to seg_lo
-    int b_li[AT];           // batch: candidate-list index of op j
-    int pre[AT];            // inclusive prefix over planned ops: misses << 22 | inserts << 11 | dcount sum
-    int pl_fl[AT], pl_w2[AT];   // plan flags / insert slot of op j, for its twin
-    int E[EQ_CAP];          // ring of eligible slots, ascending
-    int lk_fe, lk_n;        // CTA-wide lookup: first empty position, equal-tag count
-    int lk_pos[LK_CAP];     //                  positions (relative to the primary slot) of equal tags, ascending
-    i64 lk_len[LK_CAP], lk_rev[LK_CAP], lk_off[LK_CAP];   // match_len results per candidate
-    i64 lk_f[LK_CAP], lk_r[LK_CAP];                       // capped forward / backward lengths (first pass)
-    unsigned epoch;         // claim epoch (monotonic over the chunk; AutoState.pad1 between launches)
-    int changed[2];
-    int wlog[WLOG_CAP];
-    int wsum[40];
-    unsigned e_idx, e_cnt;  // ring counters (monotonic)
-    unsigned cutmask[AT / 32];
-    int nr, pos, k, nlog, jumped, ended, bmax, red;
-};
-
-#ifdef MRZ_CUSIM
-#define MRZ_SMEM_PTR(T, name) T *name = reinterpret_cast<T *>(cusim::dyn_smem())
-#else
-#define MRZ_SMEM_PTR(T, name) extern __shared__ __align__(16) unsigned char name##_raw[]; T *name = reinterpret_cast<T *>(name##_raw)
-#endif
-
-// exclusive prefix sum of v over the CTA (thread order); total in `total`.  Two barriers.
-__device__ __forceinline__ int block_excl_scan(int v, int *wsum, int &total) {
-    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    int inc = v;
-    for (int o = 1; o < 32; o <<= 1) {
-        int u = __shfl_up_sync(FULL, inc, o);
-        if (lane >= o) inc += u;
-    }
-    if (lane == 31) wsum[wid] = inc;
-    __syncthreads();
-    if (wid == 0) {
-        int w = wsum[lane], wi = w;
-        for (int o = 1; o < 32; o <<= 1) {
-            int u = __shfl_up_sync(FULL, wi, o);
-            if (lane >= o) wi += u;
-        }
-        wsum[lane] = wi - w;
-        if (lane == 31) wsum[32] = wi;
-    }
-    __syncthreads();
-    total = wsum[32];
-    int r = wsum[wid] + inc - v;
-    return r;
-}
-
-// minimum of v over the CTA.  Two barriers; `red` must not be in use.
-__device__ __forceinline__ int block_min(int v, int *red) {
-    for (int o = 16; o; o >>= 1) {
-        int u = __shfl_xor_sync(FULL, v, o);
-        v = u < v ? u : v;
-    }
-    if (threadIdx.x == 0) *red = 0x7fffffff;
-    __syncthreads();
-    if ((threadIdx.x & 31) == 0) atomicMin(red, v);
-    __syncthreads();
-    return *red;
-}
 
 struct Plan {
     int flags, dcount;
@@ -639,7 +683,7 @@ struct Plan {
 
 // First slot s >= h with tz1(tags[s]) < need (an empty slot has tag 0, i.e. zero trailing ones), or -1 when
 // the walk reaches the end of the table / gets too long.  Whole groups whose summary says "every tag has >= need
-// trailing ones" are skipped unseen (one 128-bit load covers 8 groups = 128 slots); a group that is scanned
+// trailing ones" are skipped unseen (one 128-bit load covers 8 groups = 64 slots); a group that is scanned
 // completely without a hit has its summary repaired.  Tags are read eight at a time (two 256-bit loads).
 __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int need, i64 hsize, i64 &stop_tag) {
     if (h >= hsize) return -1;
@@ -653,15 +697,14 @@ __device__ __forceinline__ i64 find_stop(const i64 *ttag, u32 *gsum, i64 h, int 
     const u32 pass_bit = 1u << ((need > 15 ? 15 : need) - 1);   // need >= 1: set <=> the group holds no stop for this walk
     bool whole = (h & (GRP - 1)) == 0;
     for (;;) {
-        const i64 gend = (g + 1) << GRP_SHIFT;
         int mn = 15;
-        if ((h & (GRP - 1)) == GRP - 1) {   // the usual case at mask levels >= 4 (primary slots end in ...1111): one tag, one load
+        if ((h & (GRP - 1)) == GRP - 1) {   // the usual case at mask levels >= 3 (primary slots end in ...111): one tag, one load
             const i64 t = __ldcg(ttag + h);
             int z = tz1(t);
             if (z < 0) z = 64;
             if (z < need) { stop_tag = t; return h; }
-        } else
-        for (i64 o = h & ~(i64)7; o < gend; o += 8) {
+        } else {
+            const i64 o = h & ~(i64)7;
             i64 v[8];
             ld_i64x8_cg(ttag + o, v);
 #pragma unroll
@@ -700,10 +743,10 @@ __device__ __forceinline__ void plan_init(Plan &r) {
     r.w1_slot = -1; r.w2_slot = -1; r.w1_off = 0; r.w1_tag = 0;
 }
 
-// Phase A: plan the insert of (tag) against the table without modifying anything (oracle/spec_model.c
-// plan_op).  The caller has established through the tag filter that no equal tag exists.  The walk starts at
-// `start` (the tag's primary slot, or the slot after a claimed one when the plan is forwarded).
-__device__ __forceinline__ void plan_op(Plan &r, const i64 *ttag, const i64 *toff, u32 *gsum, const u64 *filt, i64 tag,
+// Plan the insert of (tag) against the table without modifying anything (oracle/spec_model.c plan_op).  The caller
+// has established through the tag filter that no equal tag exists.  The walk starts at `start` (the tag's primary
+// slot, or the slot after a claimed one when the plan is forwarded).
+__device__ __forceinline__ void plan_op(Plan &r, const i64 *ttag, const i64 *toff, u32 *gsum, const Filt &filt, i64 tag,
                                         i64 start, i64 hmask, i64 hsize, i64 min_mask, int chain) {
     const i64 btm = (min_mask << 1) | 1;
     const int kb = __popcll((u64)btm);                 // entries with fewer trailing ones are due for sweeping
@@ -726,7 +769,7 @@ __device__ __forceinline__ void plan_op(Plan &r, const i64 *ttag, const i64 *tof
         int d2 = 0;
         if (st2 != 0) {
             if ((st2 & btm) != btm) { d2 = -1; r.flags |= F_W1ELIG; }
-            else { r.flags |= F_COMPLEX; return; }     // a second displacement: serial
+            else { r.flags |= F_COMPLEX; return; }     // a second displacement: exact executor
         }
         r.flags |= F_W1;
         r.w1_slot = (int)g; r.w1_off = __ldcg(toff + s); r.w1_tag = st;
@@ -739,8 +782,7 @@ __device__ __forceinline__ void plan_op(Plan &r, const i64 *ttag, const i64 *tof
 // the bytes form a genuine run; B's insert walk passes A's entry and goes on from the next slot - or,
 // before the first overflow, overwrites A's entry when the tag itself is due for sweeping.
 __device__ __forceinline__ void plan_follower(Plan &r, const i64 *ttag, u32 *gsum, const u8 *buf, i64 pos, i64 tag,
-                                              int a_flags, int a_w2, i64 hmask, i64 hsize, i64 min_mask, int chain, i64 end,
-                                              i64 last) {
+                                              int a_flags, int a_w2, i64 hsize, i64 min_mask, int chain, i64 end, i64 last) {
     if (a_flags & F_COMPLEX) { r.flags |= F_COMPLEX; return; }
     if (!(a_flags & F_INSERT)) return;                       // both lookup-only, nothing to find
     if ((a_flags & F_W1) || chain == 1) { r.flags |= F_COMPLEX; return; }
@@ -755,7 +797,7 @@ __device__ __forceinline__ void plan_follower(Plan &r, const i64 *ttag, u32 *gsu
     const int kb = __popcll((u64)btm);
     const int myz = tz1(tag);
     r.flags |= F_INSERT | F_FOLLOW;
-    if ((tag & btm) != btm) {
+    if ((tag & btm) != btm) {      // the leader's own entry is due for sweeping (before the first overflow): overwrite it
         r.w2_slot = a_w2; r.dcount = 0;
     } else {
         i64 st;
@@ -767,89 +809,69 @@ __device__ __forceinline__ void plan_follower(Plan &r, const i64 *ttag, u32 *gsu
     }
 }
 
-// Refill the ring of eligible slots (those clean_one_from_hash will zero next, in order) by a
-// parallel scan of the table from e_scan; only meaningful once ins_mask == 2*min_mask+1.
-// The scan never goes past scan_end (the table end, or the window the current batch was planned with).
-__device__ __forceinline__ void refill_queue(Smem *S, const i64 *ttag, i64 scan_end, int want) {
-    const int tid = threadIdx.x;
-    const i64 btm = (S->run.min_mask << 1) | 1;
-    const i64 hsize = scan_end;
+// Refill the ring of eligible slots (those clean_one_from_hash will zero next, in order) by a parallel scan of the
+// table from e_scan, eight slots (one 64-byte line) per thread of the cluster; only meaningful once
+// ins_mask == 2*min_mask+1.  The scan never goes past scan_end.  Every thread of the cluster calls it.
+__device__ __forceinline__ void refill_queue(VS *sh, Smem *S, const i64 *ttag, i64 btm, i64 scan_end, int want, int CL, int rank, int j, int B) {
     for (;;) {
-        __syncthreads();
-        int avail = (int)(S->e_cnt - S->e_idx);
-        i64 scan = S->e_scan;
-        if (avail >= want || scan >= hsize || avail + 2 * AT > EQ_CAP) break;
-        // each thread examines two consecutive slots
-        i64 s0 = scan + 2 * tid;
-        bool g0 = false, g1 = false;
-        if (s0 < hsize) { i64 t = __ldcg(ttag + s0); g0 = t != 0 && (t & btm) != btm; }
-        if (s0 + 1 < hsize) { i64 t = __ldcg(ttag + s0 + 1); g1 = t != 0 && (t & btm) != btm; }
-        int total;
-        int ex = block_excl_scan((int)g0 + (int)g1, S->wsum, total);
-        unsigned base = S->e_cnt + (unsigned)ex;
-        if (g0) S->E[base++ & (EQ_CAP - 1)] = (int)s0;
-        if (g1) S->E[base & (EQ_CAP - 1)] = (int)(s0 + 1);
-        __syncthreads();
-        if (tid == 0) {
-            S->e_cnt += (unsigned)total;
-            i64 ns = scan + 2 * AT;
-            S->e_scan = ns < hsize ? ns : hsize;
-        }
-    }
-}
-
-// After a serial op (thread 0): bring the queue back in step with what the op wrote.
-__device__ __forceinline__ void sync_queue(Smem *S, int nlog) {
-    for (int w = 0; w < nlog; w++) {
-        int sl = S->wlog[w] >> 1;
-        if (S->wlog[w] & 1) {                    // zeroed by clean_one: consume the queue up to it
-            while (S->e_idx != S->e_cnt && S->E[S->e_idx & (EQ_CAP - 1)] <= sl) S->e_idx++;
-        } else if (sl < S->e_scan) {             // overwritten by an insert: if queued, cut the queue there
-            unsigned a = S->e_idx, b = S->e_cnt;
-            while (a != b) {
-                unsigned m = a + (b - a) / 2;
-                if (S->E[m & (EQ_CAP - 1)] < sl) a = m + 1; else b = m;
+        csync(CL);
+        const unsigned e_cnt = sh->e_cnt;
+        const int avail = (int)(e_cnt - sh->e_idx);
+        const i64 scan = sh->e_scan;
+        if (avail >= want || scan >= scan_end || avail + 8 * B > MRZ_EQ_CAP) break;
+        const i64 base = scan & ~(i64)7;
+        const i64 s0 = base + 8 * (i64)j;
+        unsigned m = 0;
+        if (s0 < scan_end) {
+            i64 v[8];
+            ld_i64x8_cg(ttag + s0, v);
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                const i64 s = s0 + q, t = v[q];
+                if (s >= scan && s < scan_end && t != 0 && (t & btm) != btm) m |= 1u << q;
             }
-            if (a != S->e_cnt && S->E[a & (EQ_CAP - 1)] == sl) { S->e_cnt = a; S->e_scan = sl; }
+        }
+        unsigned long long total;
+        const unsigned long long ex = cluster_excl_scan((unsigned long long)__popc(m), S, sh, 0, CL, rank, total);
+        unsigned at = e_cnt + (unsigned)ex;
+        for (int q = 0; q < 8; q++)
+            if ((m >> q) & 1u) sh->E[at++ & (MRZ_EQ_CAP - 1)] = (int)(s0 + q);
+        if (j == 0) {
+            sh->e_cnt = e_cnt + (unsigned)total;
+            const i64 ns = base + 8 * (i64)B;
+            sh->e_scan = ns < scan_end ? ns : scan_end;
         }
     }
 }
 
-// PLAN OFFLOAD.  The plan phase of a batch is bound by what one SM can issue (about one uncoalesced request per
-// cycle: ~20 k cycles for 1024 plans), so it is spread over H helper CTAs of the same cooperative grid: the main CTA
-// publishes the batch, every helper thread plans op (tid * H + helper) against the table - read-only, through L2 -
-// and writes the plan record; two flag hand-offs per batch, no grid barrier.  Commits, conflicts, sweeps and the
-// serial ops stay on the main CTA.
-struct PlanIO {
-    unsigned seq, done;       // batch number published by the main CTA / helper threads finished (both zeroed per launch)
-    int nr, chain;
-    i64 min_mask, ins_mask, last_now, hmask, hsize, end, seg_lo;
-    u32 rel[AT];
-    i64 tag[AT];
-    int flags[AT], dcount[AT], w1_slot[AT], w2_slot[AT];
-    i64 w1_off[AT], w1_tag[AT];
-};
-__device__ __forceinline__ unsigned wait_change(volatile unsigned *a, unsigned old) {
-#ifdef MRZ_CUSIM
-    return cusim::wait_change(a, old);
-#else
-    unsigned v;
-    while ((v = *a) == old) __nanosleep(40);
-    return v;
-#endif
+// After a serial op (one thread): bring the ring back in step with what the op wrote.
+__device__ __forceinline__ void sync_queue(VS *sh, const int *wlog, int nlog) {
+    for (int w = 0; w < nlog; w++) {
+        const int sl = wlog[w] >> 1;
+        if (wlog[w] & 1) {                       // zeroed by clean_one: consume the ring up to it
+            while (sh->e_idx != sh->e_cnt && sh->E[sh->e_idx & (MRZ_EQ_CAP - 1)] <= sl) sh->e_idx = sh->e_idx + 1;
+        } else if (sl < sh->e_scan) {            // overwritten by an insert: if queued, cut the ring there
+            unsigned a = sh->e_idx, b = sh->e_cnt;
+            while (a != b) {
+                const unsigned m = a + (b - a) / 2;
+                if (sh->E[m & (MRZ_EQ_CAP - 1)] < sl) a = m + 1; else b = m;
+            }
+            if (a != sh->e_cnt && sh->E[a & (MRZ_EQ_CAP - 1)] == sl) { sh->e_cnt = a; sh->e_scan = sl; }
+        }
+    }
 }
 
 // Match extension by the whole CTA: longest common prefix of buf[a0..] / buf[b0..] (fwd) or longest common suffix of
-// buf[..a0) / buf[..b0), at most maxlen bytes; 32 KiB per step, four independent 8-byte compares per thread in flight.
+// buf[..a0) / buf[..b0), at most maxlen bytes; 32*T bytes per step, four independent 8-byte compares per thread in flight.
 __device__ __forceinline__ i64 cta_extend(Smem *S, const u8 *buf, i64 a0, i64 b0, i64 maxlen, bool fwd) {
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, T = blockDim.x;
     i64 f = 0;
     while (f < maxlen) {
         if (tid == 0) S->lk_fe = 0x7fffffff;
         __syncthreads();
         int first = 0x7fffffff;
         for (int c = 3; c >= 0; c--) {
-            const int ci = c * AT + tid;
+            const int ci = c * T + tid;
             const i64 k = f + (i64)ci * 8;
             u64 x = 0;
             if (k < maxlen) x = fwd ? ld_u64_unaligned(buf, a0 + k) ^ ld_u64_unaligned(buf, b0 + k)
@@ -864,667 +886,769 @@ __device__ __forceinline__ i64 cta_extend(Smem *S, const u8 *buf, i64 a0, i64 b0
             f += (i64)(r >> 3) * 8 + (r & 7);
             break;
         }
-        f += (i64)4 * AT * 8;
+        f += (i64)4 * T * 8;
     }
     return f > maxlen ? maxlen : f;
 }
 
-// Runs the automaton over the current segment's candidate list (or to the end of the chunk).
-__global__ void __launch_bounds__(AT, 1)
-k_automaton(const u8 *__restrict__ buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum_global, unsigned *claim, const i64 *__restrict__ hidx,
-            AutoState *st, const i64 *__restrict__ tile_off, const u32 *__restrict__ cand_pos,
-            const i64 *__restrict__ cand_tag, Token *toks, i64 *dbg, PlanIO *io) {
-    if (st->done || st->error) return;
-    const int H = (int)gridDim.x - 1;             // helper CTAs (0: the main CTA plans by itself)
-    if (blockIdx.x > 0) {
-        // ------------------------------------------------------------ helper CTA: plans on request, touches nothing else
-        const int hid = (int)blockIdx.x - 1, per = AT / H;
-        if ((int)threadIdx.x >= per) return;
-        unsigned seen = 0;
-        for (;;) {
-            const unsigned sq = wait_change(&io->seq, seen);
-            if (sq == 0xffffffffu) return;
-            seen = sq;
-            __threadfence();
-            const int nr = *(volatile int *)&io->nr, chain = *(volatile int *)&io->chain;
-            const i64 min_mask = *(volatile i64 *)&io->min_mask, ins_mask = *(volatile i64 *)&io->ins_mask;
-            const i64 hmask = *(volatile i64 *)&io->hmask, hsize = *(volatile i64 *)&io->hsize;
-            const int j = (int)threadIdx.x * H + hid;
-            if (j < nr) {
-                const u32 rel = __ldcg(io->rel + j);
-                const i64 tag = __ldcg(io->tag + j);
-                const bool same = j > 0 && __ldcg(io->rel + j - 1) + 1 == rel && __ldcg(io->tag + j - 1) == tag;
-                const bool same_prev = j > 1 && __ldcg(io->rel + j - 2) + 2 == rel && __ldcg(io->tag + j - 2) == tag;
-                Plan pl;
-                plan_init(pl);
-                // a twin plans its leader's op itself: same tag, same table, same plan
-                if (filt_query(filt, tag)) pl.flags |= F_COMPLEX;
-                else if ((tag & ins_mask) == ins_mask)
-                    plan_op(pl, ttag, toff, gsum_global, filt, tag, tag & hmask, hmask, hsize, min_mask, chain);
-                if (same && !same_prev) {
-                    const int a_flags = pl.flags, a_w2 = pl.w2_slot;
-                    plan_init(pl);
-                    plan_follower(pl, ttag, gsum_global, buf, *(volatile i64 *)&io->seg_lo + (i64)rel, tag, a_flags, a_w2, hmask, hsize,
-                                  min_mask, chain, *(volatile i64 *)&io->end, *(volatile i64 *)&io->last_now);
-                }
-                __stcg(io->flags + j, pl.flags); __stcg(io->dcount + j, pl.dcount);
-                __stcg(io->w1_slot + j, pl.w1_slot); __stcg(io->w2_slot + j, pl.w2_slot);
-                __stcg(io->w1_off + j, pl.w1_off); __stcg(io->w1_tag + j, pl.w1_tag);
-            }
-            __threadfence();
-            __syncwarp();
-            if ((threadIdx.x & 31) == 0) atomicAdd(&io->done, 32u);
-        }
+// The 64-bit tag of position p (rzip.c:348-358) from the bytes: two 256-bit loads, 31 look-ups in shared memory.
+__device__ __forceinline__ i64 tag_at(const u8 *buf, const i64 *hx, i64 p) {
+#ifdef MRZ_CUSIM
+    i64 t = 0;
+    for (int i = 0; i < MRZ_MIN_MATCH; i++) t ^= hx[buf[p + i]];
+    return t;
+#else
+    const u8 *a = buf + (p & ~(i64)31);
+    u64 v[8];
+    asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(a));
+    asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(v[4]), "=l"(v[5]), "=l"(v[6]), "=l"(v[7]) : "l"(a + 32));
+    const int ws = (int)(p & 31) >> 3, sh = (int)(p & 7) * 8;
+    u64 a0, a1, a2, a3, a4;
+    switch (ws) {
+        case 0: a0 = v[0]; a1 = v[1]; a2 = v[2]; a3 = v[3]; a4 = v[4]; break;
+        case 1: a0 = v[1]; a1 = v[2]; a2 = v[3]; a3 = v[4]; a4 = v[5]; break;
+        case 2: a0 = v[2]; a1 = v[3]; a2 = v[4]; a3 = v[5]; a4 = v[6]; break;
+        default: a0 = v[3]; a1 = v[4]; a2 = v[5]; a3 = v[6]; a4 = v[7]; break;
     }
-    unsigned plan_seq = 0;
-    MRZ_SMEM_PTR(Smem, S);
-    i64 tm[20];
+    u64 w[4];
+    if (sh) {
+        w[0] = (a0 >> sh) | (a1 << (64 - sh)); w[1] = (a1 >> sh) | (a2 << (64 - sh));
+        w[2] = (a2 >> sh) | (a3 << (64 - sh)); w[3] = (a3 >> sh) | (a4 << (64 - sh));
+    } else { w[0] = a0; w[1] = a1; w[2] = a2; w[3] = a3; }
+    i64 t = 0;
 #pragma unroll
-    for (int q = 0; q < 20; q++) tm[q] = 0;
-    i64 t_prev = clock64();
-#define TICK(slot) do { i64 t_now = clock64(); tm[slot] += t_now - t_prev; t_prev = t_now; } while (0)
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (tid < 256) S->hx[tid] = hidx[tid];
+    for (int i = 0; i < MRZ_MIN_MATCH; i++) t ^= hx[(w[i >> 3] >> ((i & 7) * 8)) & 255u];
+    return t;
+#endif
+}
+
+// high bit of every byte of w that is >= k (all bytes < 128, k < 128), gathered into a nibble: bit i <=> byte i
+__device__ __forceinline__ unsigned ge_nibble(u32 w, u32 k4) {
+    const u32 x = ((w | 0x80808080u) - k4) & 0x80808080u;
+    return (((x >> 7) * 0x01020408u) >> 24) & 0xfu;
+}
+
+// ---- the kernel -----------------------------------------------------------------------------------
+// Cluster c of the grid runs automaton c: descs[c].  Persistent: returns when the chunk is done (or on error).
+__global__ void __launch_bounds__(MRZ_MAXT, 1)
+k_automaton(const AutoDesc *__restrict__ descs) {
+    const int CL = cl_size(), rank = cl_rank();
+    const AutoDesc D = descs[blockIdx.x / CL];
+    AutoState *st = D.st;
+    if (st->done || st->error) return;
+    MRZ_SMEM_PTR(Smem, S);
+    VS *sh = D.sh;
+    const u8 *__restrict__ buf = D.buf;
+    const u8 *__restrict__ bmap = D.bmap;
+    const u8 *__restrict__ bsum = D.bsum;
+    i64 *ttag = D.ttag, *toff = D.toff;
+    u32 *gsum = D.gsum;
+    unsigned *claim = D.claim;
+    i64 *dbg = D.dbg;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, T = blockDim.x;
+    const int B = CL * T, j = rank * T + tid;
+    Filt filt;
+    filt.w = D.filt; filt.shift = 64 - st->filt_bits;
+    for (int q = tid; q < 256; q += T) S->hx[q] = D.hidx[q];
     const i64 n = st->n, end = st->end, hmask = st->hmask, hsize = st->hsize, limit = st->limit;
     const int chain = st->chain;
-    const i64 seg_lo = st->seg_lo, seg_hi = st->seg_hi, ncand = st->seg_ncand;
-    if (tid == 0) {
-        Run &r = S->run;
-        r.p = st->p; r.last = st->last; r.cur_p = st->cur_p; r.cur_len = st->cur_len; r.cur_ofs = st->cur_ofs;
-        r.min_mask = st->min_mask; r.ins_mask = st->ins_mask; r.clean_ptr = st->clean_ptr; r.count = st->count;
-        r.vr = st->victim_round;
-        r.hits = st->tag_hits; r.misses = st->tag_misses; r.inserts = st->inserts; r.vevents = st->victim_events;
-        r.nops = st->n_ops; r.ntok = st->ntok; r.error = 0;
-        S->e_idx = S->e_cnt = 0; S->e_scan = r.clean_ptr;
-        S->li = 0; S->bmax = AT;
-        S->epoch = (unsigned)st->pad1; S->changed[0] = S->changed[1] = 0;
+    const i64 nblocks = (end >> MAP_BLK_SHIFT) + 1;          // 64-position blocks that hold a position <= end
+    (void)n;
+    if (j == 0) {
+        sh->run.p = st->p; sh->run.last = st->last; sh->run.cur_p = st->cur_p; sh->run.cur_len = st->cur_len; sh->run.cur_ofs = st->cur_ofs;
+        sh->run.min_mask = st->min_mask; sh->run.ins_mask = st->ins_mask; sh->run.clean_ptr = st->clean_ptr; sh->run.count = st->count;
+        sh->run.vr = st->victim_round;
+        sh->run.hits = st->tag_hits; sh->run.misses = st->tag_misses; sh->run.inserts = st->inserts; sh->run.vevents = st->victim_events;
+        sh->run.nops = st->n_ops; sh->run.ntok = st->ntok; sh->run.error = 0;
+        sh->err_a = sh->err_b = 0;
+        sh->e_idx = sh->e_cnt = 0; sh->e_scan = st->clean_ptr;
+        sh->gp = st->p + 1; sh->exhausted = 0;
+        sh->changed[0] = sh->changed[1] = 0;
+        sh->kcut = ~0ULL; sh->qcut = 0x7fffffff;
     }
-    Warp w;   // used by warp 0 only
-    w.buf = buf; w.ttag = ttag; w.toff = toff; w.filt = filt; w.gsum = gsum_global; w.toks = toks; w.lane = lane;
+    Warp w;   // used by warp 0 of rank 0 only
+    w.buf = buf; w.ttag = ttag; w.toff = toff; w.filt = filt; w.gsum = gsum; w.toks = D.toks; w.lane = lane;
     w.n = n; w.end = end; w.hmask = hmask; w.hsize = hsize; w.limit = limit; w.tok_cap = st->tok_cap; w.chain = chain;
-    w.wlog = S->wlog; w.nlog = 0; w.clean_hint = 0; w.prof = dbg ? dbg + 20 : nullptr;
-    __syncthreads();
+    w.wlog = S->wlog; w.nlog = 0; w.clean_hint = 0; w.prof = dbg ? dbg + 40 : nullptr;
+    unsigned epoch = 0;      // claim epoch: uniform over the cluster (every thread advances it identically)
+    unsigned round = 0;      // cut-search round, uniform
+    i64 tm[16];
+#pragma unroll
+    for (int q = 0; q < 16; q++) tm[q] = 0;
+    i64 t_prev = clock64();
+#define TICK(slot) do { if (dbg) { const i64 t_now = clock64(); tm[slot] += t_now - t_prev; t_prev = t_now; } } while (0)
+    csync(CL);   // the host has filled claim[] with 0xff: every key compares greater than any live one
 
     for (;;) {
-        // ---------------------------------------------------------------- batch set-up
-        if (S->run.error || S->li >= ncand) break;
-        const i64 min_mask = S->run.min_mask, ins_mask = S->run.ins_mask;
+        // ================================================================ batch set-up (uniform reads)
+        if (sh->run.error || sh->exhausted) break;
+        const i64 min_mask = sh->run.min_mask, ins_mask = sh->run.ins_mask;
         const i64 btm = (min_mask << 1) | 1;
         const bool steady = ins_mask == btm;   // inserts can no longer create sweep-eligible entries
-        const int bmax = S->bmax;
+        const i64 p_now = sh->run.p, last_now = sh->run.last, clean0 = sh->run.clean_ptr;
+        const int kgate = __popcll((u64)min_mask);
+        const i64 gp0 = sh->gp;
+        const i64 lo = gp0 > p_now + 1 ? gp0 : p_now + 1;
+        if (lo > end) {                        // every position up to `end` has been examined or jumped over (rzip.c:548)
+            csync(CL);
+            if (j == 0) sh->exhausted = 1;
+            csync(CL);
+            continue;
+        }
+        // ================================================================ sweep ring
         if (steady) {
-            if (tid == 0 && S->e_scan < S->run.clean_ptr) S->e_scan = S->run.clean_ptr;
-            refill_queue(S, ttag, hsize, bmax);
-        } else if (tid == 0) {
-            S->e_idx = S->e_cnt = 0; S->e_scan = S->run.clean_ptr;
-        }
-        __syncthreads();
-        TICK(0);   // queue refill
-        const i64 w_lo = S->run.clean_ptr, w_hi = steady ? S->e_scan : S->run.clean_ptr;
-        // ---------------------------------------------------------------- gather the next candidates
-        int nr = 0;
-        i64 li = S->li;
-        const i64 p_now = S->run.p, last_now = S->run.last;
-        for (;;) {
-            int room = bmax - nr;
-            if (room <= 0 || li >= ncand) break;
-            int m = (ncand - li) < room ? (int)(ncand - li) : room;
-            bool valid = false;
-            u32 rp = 0; i64 tg = 0;
-            if (tid < m) {
-                rp = __ldcg(cand_pos + li + tid); tg = __ldcg(cand_tag + li + tid);
-                valid = seg_lo + (i64)rp > p_now && (tg & min_mask) == min_mask;
-            }
-            int total;
-            int ex = block_excl_scan((int)valid, S->wsum, total);
-            if (valid) { S->b_rel[nr + ex] = rp; S->b_tag[nr + ex] = tg; S->b_li[nr + ex] = (int)(li + tid); }
-            nr += total;
-            li += m;
-            if (nr * 2 >= bmax) break;
-        }
-        __syncthreads();
-        TICK(1);   // gather
-        if (nr == 0) { if (tid == 0) S->li = li; __syncthreads(); continue; }
-        tm[8] += nr; tm[9] += 1;
-        // ---------------------------------------------------------------- phase A: plan
-        Plan pl;
-        plan_init(pl);
-        i64 my_pos = 0, my_tag = 0;
-        bool follower = false;
-        int lead_w2 = -1;
-        const i64 t_plan0 = clock64();
-        if (dbg && tid == 0) S->red = 0;
-        if (H > 0) {
-            // publish the batch, wait for the helpers' plan records
-            if (tid < nr) { __stcg(io->rel + tid, S->b_rel[tid]); __stcg(io->tag + tid, S->b_tag[tid]); }
-            if (tid == 0) {
-                io->nr = nr; io->chain = chain; io->min_mask = min_mask; io->ins_mask = ins_mask; io->last_now = last_now;
-                io->hmask = hmask; io->hsize = hsize; io->end = end; io->seg_lo = seg_lo;
-            }
-            plan_seq++;
-            __syncthreads();
-            if (tid == 0) {
-                __threadfence();
-                *(volatile unsigned *)&io->seq = plan_seq;
-                const unsigned target = plan_seq * (unsigned)AT;
-                unsigned v = *(volatile unsigned *)&io->done;
-                while (v != target) v = wait_change(&io->done, v);
-                __threadfence();
-            }
-            __syncthreads();
-            if (tid < nr) {
-                const u32 rel = S->b_rel[tid];
-                my_pos = seg_lo + (i64)rel; my_tag = S->b_tag[tid];
-                bool same = tid > 0 && S->b_rel[tid - 1] + 1 == rel && S->b_tag[tid - 1] == my_tag;
-                bool same_prev = tid > 1 && S->b_rel[tid - 2] + 2 == rel && S->b_tag[tid - 2] == my_tag;
-                follower = same && !same_prev;
-                pl.flags = __ldcg(io->flags + tid); pl.dcount = __ldcg(io->dcount + tid);
-                pl.w1_slot = __ldcg(io->w1_slot + tid); pl.w2_slot = __ldcg(io->w2_slot + tid);
-                pl.w1_off = __ldcg(io->w1_off + tid); pl.w1_tag = __ldcg(io->w1_tag + tid);
-                S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;
-            }
-            __syncthreads();
-            if (follower) lead_w2 = S->pl_w2[tid - 1];
+            csync(CL);   // every thread has read the state above
+            if (j == 0 && sh->e_scan < clean0) sh->e_scan = clean0;
+            refill_queue(sh, S, ttag, btm, hsize, B, CL, rank, j, B);
         } else {
-        if (tid < nr) {
-            const u32 rel = S->b_rel[tid];
-            my_pos = seg_lo + (i64)rel; my_tag = S->b_tag[tid];
-            // twin: same tag as the position just before, which is not itself the second of a pair
-            bool same = tid > 0 && S->b_rel[tid - 1] + 1 == rel && S->b_tag[tid - 1] == my_tag;
-            bool same_prev = tid > 1 && S->b_rel[tid - 2] + 2 == rel && S->b_tag[tid - 2] == my_tag;
-            follower = same && !same_prev;
-            if (!follower) {
-                if (filt_query(filt, my_tag)) pl.flags |= F_COMPLEX;          // an equal tag may exist
-                else if ((my_tag & ins_mask) == ins_mask)
-                    plan_op(pl, ttag, toff, gsum_global, filt, my_tag, my_tag & hmask, hmask, hsize, min_mask, chain);
-            }
-            S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot;
-            if (dbg) {   // per-op plan latency: mean and per-batch maximum (the barrier waits for the slowest walk)
-                const i64 dt = clock64() - t_plan0;
-                atomicAdd((unsigned long long *)&dbg[17], (unsigned long long)dt);
-                atomicMax(&S->red, (int)dt);
-            }
+            csync(CL);
+            if (j == 0) { sh->e_idx = sh->e_cnt = 0; sh->e_scan = clean0; }
         }
-        __syncthreads();
-        if (dbg && tid == 0) dbg[18] += S->red;
-        if (follower) {
-            lead_w2 = S->pl_w2[tid - 1];
-            plan_follower(pl, ttag, gsum_global, buf, my_pos, my_tag, S->pl_fl[tid - 1], lead_w2, hmask, hsize, min_mask,
-                          chain, end, last_now);
-        }
-        }
-        TICK(2);   // plan
-        // ---------------------------------------------------------------- conflicts: exact stop-slot claims with forwarding
-        // Every planned insert claims its stop slot(s) in claim[] (atomicMin of (epoch, op index)).  A plan whose stop slot
-        // is claimed by an EARLIER op either walks on from the next slot - when that op's tag is no stop for this walk,
-        // the claimed slot is remembered as a dependency - or gives up (F_CONF: serial).  Iterated to a fixed point.
-        const bool planned_ins = tid < nr && (pl.flags & (F_COMPLEX | F_INSERT)) == F_INSERT;
-        const int my_need = tz1(my_tag) > __popcll((u64)btm) ? tz1(my_tag) : __popcll((u64)btm);
-        for (int it = 0;; it++) {
-            if (S->epoch >= CLAIM_EPOCH_MAX) {   // claim keys exhausted: wipe the array, restart the epochs
-                __syncthreads();
-                for (i64 q = tid; q < hsize + 8; q += AT) claim[q] = 0xffffffffu;
-                __syncthreads();
-                if (tid == 0) S->epoch = 0;
-                __syncthreads();
+        TICK(0);
+        // ================================================================ gather the next candidates from the map
+        // level A: the non-empty 64-position blocks at or behind `lo`, in order
+        int nblk;                 // blocks handed to level B
+        const i64 blk_lo = lo >> MAP_BLK_SHIFT;
+        i64 my_blk = -1;
+        if (kgate <= MAP_BLK_SHIFT) {          // dense levels: every block is likely to hold a candidate
+            i64 need = ((i64)B << kgate >> MAP_BLK_SHIFT) * 2 + 2;
+            if (need > B) need = B;
+            if (need > nblocks - blk_lo) need = nblocks - blk_lo;
+            nblk = need > 0 ? (int)need : 0;
+            if (j < nblk) my_blk = blk_lo + j;
+            if (j == 0) sh->gp_next = (blk_lo + nblk) << MAP_BLK_SHIFT;
+            csync(CL);
+        } else {
+            int lv = kgate - 10;
+            if (lv < 0) lv = 0;
+            if (lv > 6) lv = 6;
+            const int nv = 1 << lv;                          // 16-byte summary vectors per thread
+            const i64 bb0 = blk_lo & ~(i64)15;
+            const i64 b0 = bb0 + (i64)j * 16 * nv;
+            const u32 k4 = (u32)kgate * 0x01010101u;
+            int cnt = 0;
+            for (int q = 0; q < nv; q++) {
+                const i64 bq = b0 + 16 * q;
+                if (bq >= nblocks) break;
+                const uint4 v = __ldg(reinterpret_cast<const uint4 *>(bsum + bq));
+                unsigned m = ge_nibble(v.x, k4) | (ge_nibble(v.y, k4) << 4) | (ge_nibble(v.z, k4) << 8) | (ge_nibble(v.w, k4) << 12);
+                if (bq < blk_lo) m &= ~((1u << (int)(blk_lo - bq)) - 1u);
+                if (bq + 16 > nblocks) m &= (1u << (int)(nblocks - bq)) - 1u;
+                cnt += __popc(m);
             }
-            const unsigned ep = S->epoch;
-            const unsigned ep_hi = claim_key(ep, 0, 0) >> 11;
-            bool live = planned_ins && !(pl.flags & (F_COMPLEX | F_CONF));
-            if (live && steady &&   // a stop slot that sits in the sweep queue: the order of sweeps and inserts matters
-                (((pl.flags & F_W2ELIG) && pl.w2_slot >= w_lo && pl.w2_slot < w_hi) ||
-                 ((pl.flags & F_W1ELIG) && pl.w1_slot >= w_lo && pl.w1_slot < w_hi))) {
-                pl.flags |= F_CONF;
-                live = false;
-                if (dbg) atomicAdd((unsigned long long *)&dbg[32], 1ULL);   // stop slot in the sweep queue
-            }
-            if (live) {
-                atomicMin(claim + pl.w2_slot, claim_key(ep, tid, 0));
-                if (pl.flags & F_W1) atomicMin(claim + pl.w1_slot, claim_key(ep, tid, 1));
-            }
-            __threadfence_block();
-            __syncthreads();
-            if (tid == 0) { S->epoch = ep + 1; S->changed[(it + 1) & 1] = 0; }
-            bool chg = false;
-            if (planned_ins && !live && it == 0) chg = false;
-            if (live) {
-                bool bad = false;
-                // a follower's plan builds on its leader's write: only older claims conflict, and the leader must not have moved
-                const int before = (pl.flags & F_FOLLOW) ? tid - 1 : tid;
-                int why = 0;
-                if ((pl.flags & F_FOLLOW) && S->pl_w2[tid - 1] != lead_w2) { bad = true; why = 33; }
-                for (int d = 0; d < pl.ndep && !bad; d++) {   // slots I walked past on the strength of an earlier op's claim
-                    const unsigned o = __ldcg(claim + pl.dep_slot[d]);
-                    const int oi = (int)((o >> 1) & 1023u);
-                    if ((o >> 11) != ep_hi || (o & 1u) || oi >= tid) { bad = true; why = 34; break; }
-                    const i64 ot = S->b_tag[oi];
-                    if (tz1(ot) < my_need || (ot & btm) != btm || ot == my_tag) { bad = true; why = 34; break; }
-                    pl.dep_own[d] = oi;
-                }
-                if (!bad) {
-                    const unsigned o = __ldcg(claim + pl.w2_slot);
-                    const int oi = (int)((o >> 1) & 1023u);
-                    if (oi < before) {   // my stop slot goes to an earlier op
-                        const i64 ot = S->b_tag[oi];
-                        if ((pl.flags & F_FOLLOW) || (o & 1u) || pl.ndep == MAXDEP || it >= FWD_ITERS || tz1(ot) < my_need ||
-                            (ot & btm) != btm || ot == my_tag) {   // an equal tag: my lookup must meet its entry (serial)
-                            bad = true;
-                            why = (pl.flags & F_FOLLOW) ? 33 : (o & 1u) ? 35 : ot == my_tag ? 36 : (tz1(ot) < my_need || (ot & btm) != btm) ? 37 : 38;
-                        }
-                        else {           // its tag is no stop for my walk: go on from the next slot
-                            pl.dep_slot[pl.ndep] = pl.w2_slot; pl.dep_own[pl.ndep] = oi; pl.ndep++;
-                            plan_op(pl, ttag, toff, gsum_global, filt, my_tag, (i64)pl.w2_slot + 1, hmask, hsize, min_mask, chain);
-                            S->pl_w2[tid] = pl.w2_slot;
-                            chg = true;
-                            if (dbg) atomicAdd((unsigned long long *)&dbg[16], 1ULL);
-                        }
-                    } else if ((pl.flags & F_W1) && (int)((__ldcg(claim + pl.w1_slot) >> 1) & 1023u) < tid) {
-                        bad = true;
-                        why = 39;
+            if (j == 0) sh->gp_next = (bb0 + (i64)B * 16 * nv) << MAP_BLK_SHIFT;
+            unsigned long long total;
+            unsigned long long at = cluster_excl_scan((unsigned long long)cnt, S, sh, 1, CL, rank, total);
+            if (cnt && at < (unsigned long long)B) {
+                for (int q = 0; q < nv; q++) {
+                    const i64 bq = b0 + 16 * q;
+                    if (bq >= nblocks) break;
+                    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(bsum + bq));
+                    unsigned m = ge_nibble(v.x, k4) | (ge_nibble(v.y, k4) << 4) | (ge_nibble(v.z, k4) << 8) | (ge_nibble(v.w, k4) << 12);
+                    if (bq < blk_lo) m &= ~((1u << (int)(blk_lo - bq)) - 1u);
+                    if (bq + 16 > nblocks) m &= (1u << (int)(nblocks - bq)) - 1u;
+                    while (m) {
+                        const int b = __ffs(m) - 1;
+                        m &= m - 1;
+                        if (at < (unsigned long long)B) sh->blk[at] = bq + b;
+                        else atomicMin((long long *)&sh->gp_next, (long long)((bq + b) << MAP_BLK_SHIFT));   // first block left for the next batch
+                        at++;
                     }
                 }
-                if (bad) { pl.flags |= F_CONF; chg = true; if (dbg) atomicAdd((unsigned long long *)&dbg[why], 1ULL); }
-                if (chg) S->pl_fl[tid] = pl.flags;
-            }
-            if (chg) S->changed[it & 1] = 1;
-            __syncthreads();
-            if (!S->changed[it & 1]) break;
-        }
-        if (tid < nr) { S->pl_fl[tid] = pl.flags; S->pl_w2[tid] = pl.w2_slot; }
-        {   // inclusive prefix over ops that still hold a valid plan: misses << 22 | inserts << 11 | dcount sum
-            int v = 0;
-            if (tid < nr && (pl.flags & (F_COMPLEX | F_CONF | F_INSERT)) == F_INSERT)
-                v = pl.dcount | (1 << 11) | ((pl.flags & F_FOLLOW) ? (1 << 22) : 0);
-            int total;
-            int ex = block_excl_scan(v, S->wsum, total);
-            S->pre[tid] = ex + v;
-        }
-        if (tid == 0) { S->pos = 0; S->ended = 0; S->jumped = 0; }
-        __syncthreads();
-        TICK(3);   // conflicts + prefix
-        // ---------------------------------------------------------------- phase B: in-order commit
-        for (;;) {
-            const int pos = S->pos;
-            const int base = pos ? S->pre[pos - 1] : 0;
-            const i64 cnt0 = S->run.count;
-            const int avail = (int)(S->e_cnt - S->e_idx);
-            const i64 cur_len = S->run.cur_len, cur_p = S->run.cur_p;
-            const unsigned e_idx0 = S->e_idx;
-            bool c = false;
-            if (tid >= pos && tid < nr) {
-                c = (pl.flags & (F_COMPLEX | F_CONF)) != 0;
-                c = c || (cur_len >= MRZ_MIN_MATCH && my_pos >= cur_p + MRZ_MIN_MATCH);   // an emission is due
-                if (!c && (pl.flags & F_INSERT) && pl.dcount == 1) {
-                    i64 T = cnt0 + (((unsigned)S->pre[tid] - (unsigned)base) & 0x7ffu);
-                    if (T > limit && (!steady || T - limit > avail)) c = true;             // needs a serial sweep step
+            } else if (cnt) {
+                // my first non-empty block is already beyond the batch
+                for (int q = 0; q < nv; q++) {
+                    const i64 bq = b0 + 16 * q;
+                    if (bq >= nblocks) break;
+                    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(bsum + bq));
+                    unsigned m = ge_nibble(v.x, k4) | (ge_nibble(v.y, k4) << 4) | (ge_nibble(v.z, k4) << 8) | (ge_nibble(v.w, k4) << 12);
+                    if (bq < blk_lo) m &= ~((1u << (int)(blk_lo - bq)) - 1u);
+                    if (bq + 16 > nblocks) m &= (1u << (int)(nblocks - bq)) - 1u;
+                    if (m) { atomicMin((long long *)&sh->gp_next, (long long)((bq + (__ffs(m) - 1)) << MAP_BLK_SHIFT)); break; }
                 }
             }
+            nblk = total < (unsigned long long)B ? (int)total : B;
+            csync(CL);
+            if (j < nblk) my_blk = sh->blk[j];
+        }
+        // level B: the candidate positions of those blocks, in order
+        u64 cmask = 0;
+        if (my_blk >= 0) {
+            const uint4 *src = reinterpret_cast<const uint4 *>(bmap + (my_blk << MAP_BLK_SHIFT));
+            const u32 k4 = (u32)kgate * 0x01010101u;
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const uint4 v = __ldg(src + q);
+                const u64 m16 = (u64)(ge_nibble(v.x, k4) | (ge_nibble(v.y, k4) << 4) | (ge_nibble(v.z, k4) << 8) | (ge_nibble(v.w, k4) << 12));
+                cmask |= m16 << (16 * q);
+            }
+            const i64 p0 = my_blk << MAP_BLK_SHIFT;
+            if (p0 < lo) cmask &= ~(((u64)1 << (int)(lo - p0)) - 1);        // lo - p0 < 64
+            if (p0 + 63 > end) cmask &= (end - p0 >= 63) ? ~(u64)0 : (((u64)1 << (int)(end - p0 + 1)) - 1);
+        }
+        int nr;
+        i64 my_pos = 0, my_tag = 0;
+        {
+            unsigned long long total;
+            unsigned long long at = cluster_excl_scan((unsigned long long)__popcll(cmask), S, sh, 2, CL, rank, total);
+            const i64 p0 = my_blk << MAP_BLK_SHIFT;
+            u64 m = cmask;
+            while (m) {
+                const int b = __ffsll((long long)m) - 1;
+                m &= m - 1;
+                if (at < (unsigned long long)B) sh->b_pos[at] = p0 + b;
+                else { atomicMin((long long *)&sh->gp_next, (long long)(p0 + b)); break; }      // first candidate left for the next batch
+                at++;
+            }
+            nr = total < (unsigned long long)B ? (int)total : B;
+            csync(CL);
+        }
+        if (j == 0) {
+            sh->gp = sh->gp_next;
+            sh->nr = nr;
+        }
+        if (nr == 0) { csync(CL); TICK(1); continue; }
+        i64 prev1 = -1, prev2 = -1;
+        if (j < nr) {
+            my_pos = sh->b_pos[j];
+            if (j > 0) prev1 = sh->b_pos[j - 1];
+            if (j > 1) prev2 = sh->b_pos[j - 2];
+            my_tag = tag_at(buf, S->hx, my_pos);
+            sh->b_tag[j] = my_tag;
+        }
+        TICK(1);
+        if (dbg && j == 0) { dbg[16] += nr; dbg[17] += 1; }
+        // ================================================================ phase A: plan (read-only against the table)
+        Plan pl;
+        plan_init(pl);
+        bool follower = false;
+        int lead_w2 = -1;
+        if (j < nr) {
+            // twin: same tag as the position just before, which is not itself the second of a pair
+            bool same = false, same_prev = false;
+            if (prev1 == my_pos - 1) {
+                const i64 hb = S->hx[buf[my_pos - 1]], hf = S->hx[buf[my_pos + 30]];
+                same = hb == hf;                                   // tag[p-1] == tag[p]
+                if (same && prev2 == my_pos - 2) same_prev = S->hx[buf[my_pos - 2]] == S->hx[buf[my_pos + 29]];   // tag[p-2] == tag[p-1]
+            }
+            follower = same && !same_prev;
+        }
+        {
+            // own plan; a follower in lane 0 plans its leader's op itself (same tag => same plan), the others get it by shuffle
+            if (j < nr && (!follower || lane == 0)) {
+                if (filt_query(filt, my_tag)) pl.flags |= F_COMPLEX;          // an equal tag may exist
+                else if ((my_tag & ins_mask) == ins_mask)
+                    plan_op(pl, ttag, toff, gsum, filt, my_tag, my_tag & hmask, hmask, hsize, min_mask, chain);
+            }
+            int a_flags = __shfl_up_sync(FULL, pl.flags, 1), a_w2 = __shfl_up_sync(FULL, pl.w2_slot, 1);
+            if (follower) {
+                if (lane == 0) { a_flags = pl.flags; a_w2 = pl.w2_slot; }
+                lead_w2 = a_w2;
+                plan_init(pl);
+                plan_follower(pl, ttag, gsum, buf, my_pos, my_tag, a_flags, a_w2, hsize, min_mask, chain, end, last_now);
+            }
+        }
+        if (j < nr) { sh->pl_fl[j] = pl.flags; sh->pl_w2[j] = pl.w2_slot; }
+        if (j == 0) { sh->pos = 0; sh->ended = 0; sh->jumped = 0; sh->qcut = 0x7fffffff; }
+        TICK(2);
+        const int my_need = tz1(my_tag) > __popcll((u64)btm) ? tz1(my_tag) : __popcll((u64)btm);
+        int pos = 0;
+        bool batch_ended = false;
+
+        for (;;) {   // ====================================================== rounds: conflicts -> cut -> commit -> (executor | plan again)
+            // ---------------------------------------------------------------- conflicts: exact stop-slot claims with forwarding
+            // Every live plan claims its stop slot(s) in claim[] (atomicMin of (epoch, op index)).  A plan whose stop slot
+            // is claimed by an EARLIER op either walks on from the next slot - when that op's tag is no stop for this walk,
+            // the claimed slot is remembered as a dependency - or gives up (F_CONF).  Iterated to a fixed point.
+            // The sweep can reach the slots of the ring up to s_safe within this batch (at most one sweep per op).
+            const i64 w_lo = sh->run.clean_ptr, w_hi = steady ? sh->e_scan : w_lo;
+            i64 s_safe = w_lo - 1;
+            if (steady && w_hi > w_lo) {
+                const unsigned ei = sh->e_idx, ec = sh->e_cnt;
+                const unsigned reach = (unsigned)(nr - pos);
+                s_safe = (ec - ei > reach) ? (i64)sh->E[(ei + reach) & (MRZ_EQ_CAP - 1)] : w_hi - 1;
+            }
+            for (int it = 0;; it++) {
+                if (epoch >= CLAIM_EPOCH_MAX) {   // claim keys exhausted: wipe the array, restart the epochs
+                    csync(CL);
+                    for (i64 q = j; q < hsize + 8; q += B) claim[q] = 0xffffffffu;
+                    epoch = 0;
+                    csync(CL);
+                }
+                const unsigned ep = epoch++;
+                const unsigned ep_hi = KEY_EPOCH(claim_key(ep, 0, 0));
+                const bool planned_ins = j >= pos && j < nr && (pl.flags & (F_COMPLEX | F_INSERT)) == F_INSERT;
+                bool live = planned_ins && !(pl.flags & F_CONF);
+                if (live && steady &&   // a stop slot the sweep may reach in this batch: the order of sweeps and inserts matters
+                    (((pl.flags & F_W2ELIG) && pl.w2_slot >= w_lo && pl.w2_slot <= s_safe) ||
+                     ((pl.flags & F_W1ELIG) && pl.w1_slot >= w_lo && pl.w1_slot <= s_safe))) {
+                    pl.flags |= F_CONF | F_ZONE;
+                    live = false;
+                    if (dbg) atomicAdd((unsigned long long *)&dbg[32], 1ULL);
+                }
+                if (live) {
+                    int s2 = pl.w2_slot; CHK(sh, 1, s2, hsize + 8);
+                    atomicMin(claim + s2, claim_key(ep, j, 0));
+                    if (pl.flags & F_W1) { int s1 = pl.w1_slot; CHK(sh, 2, s1, hsize + 8); atomicMin(claim + s1, claim_key(ep, j, 1)); }
+                }
+                csync(CL);
+                if (j == 0) sh->changed[(it + 1) & 1] = 0;   // last read before the barrier above, next written behind the one below
+                bool chg = false;
+                if (live) {
+                    bool bad = false;
+                    // a follower's plan builds on its leader's write: only older claims conflict, and the leader must not have moved
+                    const int before = (pl.flags & F_FOLLOW) ? j - 1 : j;
+                    int why = 0;
+                    if ((pl.flags & F_FOLLOW) && j - 1 >= pos && sh->pl_w2[j - 1] != lead_w2) { bad = true; why = 33; }
+                    for (int d = 0; d < pl.ndep && !bad; d++) {   // slots I walked past on the strength of an earlier op's claim
+                        const unsigned o = __ldcg(claim + pl.dep_slot[d]);
+                        const int oi = KEY_IDX(o);
+                        if (KEY_EPOCH(o) != ep_hi || (o & 1u) || oi >= j) { bad = true; why = 34; break; }
+                        const i64 ot = sh->b_tag[oi];
+                        if (tz1(ot) < my_need || (ot & btm) != btm || ot == my_tag) { bad = true; why = 34; break; }
+                        pl.dep_own[d] = oi;
+                    }
+                    if (!bad) {
+                        const unsigned o = __ldcg(claim + pl.w2_slot);
+                        const int oi = KEY_IDX(o);
+                        if (oi < before) {   // my stop slot goes to an earlier op
+                            const i64 ot = sh->b_tag[oi];
+                            if ((pl.flags & F_FOLLOW) || (o & 1u) || pl.ndep == MAXDEP || it >= FWD_ITERS || tz1(ot) < my_need ||
+                                (ot & btm) != btm || ot == my_tag) {   // an equal tag: my lookup must meet its entry
+                                bad = true;
+                                why = (pl.flags & F_FOLLOW) ? 33 : (o & 1u) ? 35 : ot == my_tag ? 36 : (tz1(ot) < my_need || (ot & btm) != btm) ? 37 : 38;
+                            } else {         // its tag is no stop for my walk: go on from the next slot
+                                pl.dep_slot[pl.ndep] = pl.w2_slot; pl.dep_own[pl.ndep] = oi; pl.ndep++;
+                                plan_op(pl, ttag, toff, gsum, filt, my_tag, (i64)pl.w2_slot + 1, hmask, hsize, min_mask, chain);
+                                sh->pl_w2[j] = pl.w2_slot;
+                                chg = true;
+                                if (dbg) atomicAdd((unsigned long long *)&dbg[31], 1ULL);
+                            }
+                        } else if ((pl.flags & F_W1) && KEY_IDX(__ldcg(claim + pl.w1_slot)) < j) {
+                            bad = true;
+                            why = 39;
+                        }
+                    }
+                    if (bad) { pl.flags |= F_CONF; chg = true; if (dbg) atomicAdd((unsigned long long *)&dbg[why], 1ULL); }
+                    if (chg) sh->pl_fl[j] = pl.flags;
+                }
+                if (chg) sh->changed[it & 1] = 1;
+                csync(CL);
+                if (!sh->changed[it & 1]) break;
+            }
+            TICK(3);
+            // ---------------------------------------------------------------- prefix over the ops of [pos, nr) that hold a valid plan, and the cut
+            round++;
+            const unsigned long long rkey = (unsigned long long)(~round) << 32;
+            unsigned long long incl;
             {
+                unsigned long long v = 0;
+                if (j >= pos && j < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
+                    v = 1ULL << 48;
+                    if (pl.flags & F_INSERT) v |= (unsigned long long)pl.dcount | (1ULL << 16) | ((pl.flags & F_FOLLOW) ? (1ULL << 32) : 0ULL);
+                }
+                unsigned long long total;
+                incl = cluster_excl_scan(v, S, sh, 3, CL, rank, total) + v;
+                if (j < nr) sh->pre[j] = incl;
+            }
+            const i64 cnt0 = sh->run.count;
+            const unsigned e_idx0 = sh->e_idx;
+            const int avail = (int)(sh->e_cnt - e_idx0);
+            {
+                const i64 cur_len = sh->run.cur_len, cur_p = sh->run.cur_p;
+                bool c = false, exact = false;
+                if (j >= pos && j < nr) {
+                    exact = (pl.flags & (F_COMPLEX | F_ZONE)) != 0 || (cur_len >= MRZ_MIN_MATCH && my_pos >= cur_p + MRZ_MIN_MATCH);   // an emission is due
+                    c = exact || (pl.flags & F_CONF) != 0;
+                    if (!c && (pl.flags & F_INSERT) && pl.dcount == 1) {
+                        const i64 Tc = cnt0 + (i64)PK_D(incl);
+                        if (Tc > limit && (!steady || Tc - limit > avail)) c = exact = true;   // needs a serial sweep step
+                    }
+                }
                 const unsigned bal = __ballot_sync(FULL, c);
-                if (lane == 0) S->cutmask[wid] = bal;
+                if (bal) {
+                    const int l = __ffs(bal) - 1;
+                    const int ex = __shfl_sync(FULL, (int)exact, l);
+                    if (lane == 0) atomicMin((unsigned long long *)&sh->kcut, rkey | ((unsigned long long)(j + l) << 1) | (unsigned long long)ex);
+                }
             }
-            __syncthreads();   // every thread has read pos / count / queue state; the mask is complete
-            int k = nr;        // first op of [pos, nr) that cannot be committed from its plan
-            for (int wd = pos >> 5; wd < ((nr + 31) >> 5); wd++) {
-                const unsigned m = S->cutmask[wd];
-                if (m) { k = wd * 32 + __ffs(m) - 1; break; }
+            csync(CL);
+            // ---------------------------------------------------------------- commit [pos, k)
+            int k = nr;          // first op of [pos, nr) that cannot be committed from its plan
+            bool k_exact = false;
+            {
+                const unsigned long long kc = sh->kcut;
+                if ((kc >> 32) == (rkey >> 32)) { k = (int)((kc & 0xffffffffu) >> 1); k_exact = (kc & 1ULL) != 0; }
             }
-            // commit [pos, k)
-            if (tid >= pos && tid < k && (pl.flags & F_INSERT)) {
+            unsigned long long d = 0;
+            int cleans = 0;
+            i64 Tk = cnt0;
+            if (k > pos) {
+                d = sh->pre[k - 1];
+                Tk = cnt0 + (i64)PK_D(d);
+                cleans = Tk > limit ? (int)(Tk - limit) : 0;
+            }
+            if (j >= pos && j < k && (pl.flags & F_INSERT)) {
                 if (pl.flags & F_W1) {
-                    __stcg(toff + pl.w1_slot, pl.w1_off);
-                    __stcg(ttag + pl.w1_slot, pl.w1_tag);
-                    sum_lower(gsum_global, pl.w1_slot >> GRP_SHIFT, tz1c(pl.w1_tag));
+                    int s1 = pl.w1_slot; CHK(sh, 3, s1, hsize);
+                    __stcg(toff + s1, pl.w1_off);
+                    __stcg(ttag + s1, pl.w1_tag);
+                    sum_lower(gsum, s1 >> GRP_SHIFT, tz1c(pl.w1_tag));
+                    if (steady && (pl.flags & F_W1ELIG) && s1 >= w_lo && s1 < w_hi) atomicMin((int *)&sh->qcut, s1);   // a ring slot the sweep does not reach in this batch
                 }
                 // a twin that overwrites its leader's entry in the same commit must win the slot
-                const bool overwritten = tid + 1 < k && (S->pl_fl[tid + 1] & F_FOLLOW) && S->pl_w2[tid + 1] == pl.w2_slot;
+                const bool overwritten = j + 1 < k && (sh->pl_fl[j + 1] & F_FOLLOW) && sh->pl_w2[j + 1] == pl.w2_slot;
+                int s2 = pl.w2_slot; CHK(sh, 4, s2, hsize);
                 if (!overwritten) {
-                    __stcg(toff + pl.w2_slot, my_pos);
-                    __stcg(ttag + pl.w2_slot, my_tag);
-                    sum_lower(gsum_global, pl.w2_slot >> GRP_SHIFT, tz1c(my_tag));
+                    __stcg(toff + s2, my_pos);
+                    __stcg(ttag + s2, my_tag);
+                    sum_lower(gsum, s2 >> GRP_SHIFT, tz1c(my_tag));
                 }
+                if (steady && (pl.flags & F_W2ELIG) && s2 >= w_lo && s2 < w_hi) atomicMin((int *)&sh->qcut, s2);
                 filt_set(filt, my_tag);
                 if (pl.flags & F_FOLLOW) filt_set(filt, my_tag ^ DUP_SALT);   // the tag is in the table twice now
             }
-            int cleans = 0;
-            if (k > pos) {
-                const unsigned d = (unsigned)S->pre[k - 1] - (unsigned)base;
-                i64 T = cnt0 + (d & 0x7ffu);
-                cleans = T > limit ? (int)(T - limit) : 0;
-                if (tid < cleans) {
-                    const int sl = S->E[(e_idx0 + tid) & (EQ_CAP - 1)];
-                    __stcg(ttag + sl, (i64)0);
-                    __stcg(toff + sl, (i64)0);
-                    sum_lower(gsum_global, sl >> GRP_SHIFT, 0);
-                }
-                if (tid == 0) {
-                    Run &r = S->run;
-                    r.count = T - cleans;
-                    r.inserts += (d >> 11) & 0x7ffu;
-                    r.misses += d >> 22;
-                    r.nops += k - pos;
-                    r.p = seg_lo + (i64)S->b_rel[k - 1];
-                    if (cleans) {
-                        S->e_idx += (unsigned)cleans;
-                        r.clean_ptr = S->E[(S->e_idx - 1) & (EQ_CAP - 1)];   // pointer stays on the last zeroed slot
-                    }
+            for (int q = j; q < cleans; q += B) {
+                int sl = sh->E[(e_idx0 + (unsigned)q) & (MRZ_EQ_CAP - 1)]; CHK(sh, 5, sl, hsize);
+                __stcg(ttag + sl, (i64)0);
+                __stcg(toff + sl, (i64)0);
+                sum_lower(gsum, sl >> GRP_SHIFT, 0);
+            }
+            if (j == 0 && k > pos) {
+                sh->run.count = Tk - cleans;
+                sh->run.inserts = sh->run.inserts + PK_I(d);
+                sh->run.misses = sh->run.misses + PK_M(d);
+                sh->run.nops = sh->run.nops + PK_V(d);
+                // the last op of [pos, k) that was not skipped behind a jump is op k-1 itself: positions ascend
+                sh->run.p = sh->b_pos[k - 1];
+                if (cleans) {
+                    sh->e_idx = e_idx0 + (unsigned)cleans;
+                    sh->run.clean_ptr = sh->E[(e_idx0 + (unsigned)cleans - 1) & (MRZ_EQ_CAP - 1)];   // pointer stays on the last zeroed slot
                 }
             }
-            if (k >= nr) { __syncthreads(); TICK(4); break; }
-            __syncthreads();
-            TICK(4);   // cut search + commit
-            tm[10] += 1;
-            if (tid == k) {   // why is this op serial?
-                int why = (pl.flags & F_COMPLEX) ? (follower ? 12 : ((pl.flags & F_INSERT) ? 13 : 11)) : (pl.flags & F_CONF) ? 14 : 15;
-                if (dbg) atomicAdd((unsigned long long *)&dbg[why], 1ULL);
+            csync(CL);
+            TICK(4);
+            if (k >= nr) break;
+            if (dbg && j == k) {   // why does this op cut the batch?
+                const int why = (pl.flags & F_COMPLEX) ? (follower ? 22 : ((pl.flags & F_INSERT) ? 23 : 21)) : k_exact ? 25 : 24;
+                atomicAdd((unsigned long long *)&dbg[why], 1ULL);
             }
-            // ---- the lookup of op k (find_best_match, rzip.c:426-462) by the whole CTA: the probe sequence is walked
-            // 4096 slots per step, equal tags are collected in slot order, and the 32 warps share the match_len calls
-            int pre_n = -2;   // -2: the filter says no equal tag; -1: ask / walk on the warp; >= 0: candidates compared
-            const i64 c_lk0 = clock64();
-            {
-                const i64 tk = S->b_tag[k], pk = seg_lo + (i64)S->b_rel[k];
-                if (filt_query(filt, tk)) {
-                    pre_n = -1;
-                    const i64 h = tk & hmask;
-                    if (tid == 0) S->lk_fe = 0x7fffffff;
-                    __syncthreads();
-                    int n_tot = 0;
-                    bool found = false;
-                    for (int base = 0;; base += AT * 4) {
-                        i64 et[4];
-#pragma unroll
-                        for (int q = 0; q < 4; q++) et[q] = __ldcg(ttag + ((h + base + tid * 4 + q) & hmask));
-                        unsigned eq4 = 0;
-#pragma unroll
-                        for (int q = 0; q < 4; q++) {
-                            if (et[q] == 0) atomicMin(&S->lk_fe, base + tid * 4 + q);
-                            else if (et[q] == tk) eq4 |= 1u << q;
-                        }
+            int npos = k;
+            if (k_exact) {
+                if (dbg && j == 0) tm[10] += 1;
+                // ---- the lookup of op k (find_best_match, rzip.c:426-462) by the whole CTA (rank 0): the probe sequence is
+                // walked 4*T slots per step, equal tags are collected in slot order, and the warps share the match_len calls
+                if (rank == 0) {
+                    int pre_n = -2;   // -2: the filter says no equal tag; -1: ask / walk on the warp; >= 0: candidates compared
+                    const i64 tk = sh->b_tag[k], pk = sh->b_pos[k];
+                    if (filt_query(filt, tk)) {
+                        pre_n = -1;
+                        const i64 h = tk & hmask;
+                        if (tid == 0) S->lk_fe = 0x7fffffff;
                         __syncthreads();
-                        const int fe = S->lk_fe;
+                        int n_tot = 0;
+                        bool found = false;
+                        for (int base = 0;; base += T * 4) {
+                            i64 et[4];
 #pragma unroll
-                        for (int q = 0; q < 4; q++)
-                            if (base + tid * 4 + q >= fe) eq4 &= ~(1u << q);   // beyond the first empty slot: not on the walk
-                        int total;
-                        int ex = block_excl_scan(__popc(eq4), S->wsum, total);
-                        for (int q = 0; q < 4; q++)
-                            if ((eq4 >> q) & 1u) {
-                                if (n_tot + ex < LK_CAP) S->lk_pos[n_tot + ex] = base + tid * 4 + q;
-                                ex++;
-                            }
-                        n_tot += total;
-                        found = fe != 0x7fffffff;
-                        if (found || n_tot > LK_CAP || base + AT * 4 >= hsize) break;
-                    }
-                    __syncthreads();
-                    if (found && n_tot <= LK_CAP) {
-                        // single_match_len (rzip.c:372-397) per candidate: the warps share the candidates for the first
-                        // LK_XCAP bytes either side; whatever still matches there is extended by the whole CTA, 32 KiB per step
-                        w.last = S->run.last;
-                        const i64 lo = w.last > 0 ? w.last : 0;
-                        const i64 maxf = end - pk;
-                        if (tid == 0) S->lk_n = 0;      // candidates still matching at the cap
-                        __syncthreads();
-                        for (int q = wid; q < n_tot; q += AT / 32) {
-                            const i64 off = __ldcg(toff + ((h + S->lk_pos[q]) & hmask));
-                            i64 f = 0, r = 0;
-                            if (off < pk) {
-                                i64 maxb = pk - lo;
-                                if (off < maxb) maxb = off;
-                                const i64 mf = maxf < LK_XCAP ? maxf : LK_XCAP, mb = maxb < LK_XCAP ? maxb : LK_XCAP;
-                                {   // the first 256 bytes of both directions in one round trip
-                                    const i64 kk = lane * 8;
-                                    u64 xf = 0, xb = 0;
-                                    if (kk < mf) xf = ld_u64_unaligned(buf, pk + kk) ^ ld_u64_unaligned(buf, off + kk);
-                                    if (kk < mb) xb = ld_u64_unaligned(buf, pk - 8 - kk) ^ ld_u64_unaligned(buf, off - 8 - kk);
-                                    unsigned mm = __ballot_sync(FULL, xf != 0);
-                                    if (mm) {
-                                        const int l = __ffs(mm) - 1;
-                                        int nb = xf ? ((__ffsll((long long)xf) - 1) >> 3) : 8;
-                                        nb = __shfl_sync(FULL, nb, l);
-                                        f = l * 8 + nb;
-                                    } else
-                                        f = mf > 256 ? 256 + w.extend(pk + 256, off + 256, mf - 256, true) : mf;
-                                    if (f > mf) f = mf;
-                                    mm = __ballot_sync(FULL, xb != 0);
-                                    if (mm) {
-                                        const int l = __ffs(mm) - 1;
-                                        int nb = xb ? (__clzll((long long)xb) >> 3) : 8;
-                                        nb = __shfl_sync(FULL, nb, l);
-                                        r = l * 8 + nb;
-                                    } else
-                                        r = mb > 256 ? 256 + w.extend(pk - 256, off - 256, mb - 256, false) : mb;
-                                    if (r > mb) r = mb;
-                                }
-                                if (lane == 0 && ((f == LK_XCAP && maxf > LK_XCAP) || (r == LK_XCAP && maxb > LK_XCAP))) atomicAdd(&S->lk_n, 1);
-                            }
-                            if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; S->lk_off[q] = off; }
-                        }
-                        __syncthreads();
-                        // many long candidates (dense repeats, deep chains): the warps carry on in parallel, one candidate
-                        // each, up to LK_XCAP2; the whole CTA then only extends what is still matching there
-                        const i64 cap = S->lk_n > 2 ? (i64)LK_XCAP2 : (i64)LK_XCAP;
-                        if (cap != LK_XCAP) {
-                            for (int q = wid; q < n_tot; q += AT / 32) {
-                                const i64 off = S->lk_off[q];
-                                if (off >= pk) continue;
-                                i64 f = S->lk_f[q], r = S->lk_r[q];
-                                i64 maxb = pk - lo;
-                                if (off < maxb) maxb = off;
-                                if (f == LK_XCAP && maxf > LK_XCAP) f += w.extend(pk + LK_XCAP, off + LK_XCAP, (maxf < cap ? maxf : cap) - LK_XCAP, true);
-                                if (r == LK_XCAP && maxb > LK_XCAP) r += w.extend(pk - LK_XCAP, off - LK_XCAP, (maxb < cap ? maxb : cap) - LK_XCAP, false);
-                                __syncwarp();
-                                if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; }
+                            for (int q = 0; q < 4; q++) et[q] = __ldcg(ttag + ((h + base + tid * 4 + q) & hmask));
+                            unsigned eq4 = 0;
+#pragma unroll
+                            for (int q = 0; q < 4; q++) {
+                                if (et[q] == 0) atomicMin(&S->lk_fe, base + tid * 4 + q);
+                                else if (et[q] == tk) eq4 |= 1u << q;
                             }
                             __syncthreads();
-                        }
-                        for (int q = 0; q < n_tot; q++) {
-                            const i64 off = S->lk_off[q];
-                            i64 f = S->lk_f[q], r = S->lk_r[q], m = 0;
-                            if (off < pk) {
-                                i64 maxb = pk - lo;
-                                if (off < maxb) maxb = off;
-                                if (f == cap && maxf > cap) f += cta_extend(S, buf, pk + cap, off + cap, maxf - cap, true);
-                                if (r == cap && maxb > cap) r += cta_extend(S, buf, pk - cap, off - cap, maxb - cap, false);
-                                m = f + r < MRZ_MIN_MATCH ? 0 : f + r;
-                            }
-                            if (tid == 0) { S->lk_len[q] = m; S->lk_rev[q] = r; }
+                            const int fe = S->lk_fe;
+#pragma unroll
+                            for (int q = 0; q < 4; q++)
+                                if (base + tid * 4 + q >= fe) eq4 &= ~(1u << q);   // beyond the first empty slot: not on the walk
+                            unsigned long long total;
+                            int ex = (int)block_excl_scan((unsigned long long)__popc(eq4), S->wsum, total);
+                            for (int q = 0; q < 4; q++)
+                                if ((eq4 >> q) & 1u) {
+                                    if (n_tot + ex < LK_CAP) S->lk_pos[n_tot + ex] = base + tid * 4 + q;
+                                    ex++;
+                                }
+                            n_tot += (int)total;
+                            found = fe != 0x7fffffff;
+                            if (found || n_tot > LK_CAP || base + T * 4 >= hsize) break;
                         }
                         __syncthreads();
-                        pre_n = n_tot;
-                    }
-                }
-            }
-            if (dbg && tid == 0) dbg[19] += clock64() - c_lk0;
-            // ---- op k on the live table, reference semantics (warp 0)
-            if (wid == 0) {
-                w.load(S->run);
-                w.nlog = 0;
-                i64 hint = w.clean_ptr;
-                if (steady) hint = (S->e_cnt != S->e_idx) ? (i64)S->E[S->e_idx & (EQ_CAP - 1)] : (S->e_scan > hint ? S->e_scan : hint);
-                w.clean_hint = hint;
-                const i64 pk = seg_lo + (i64)S->b_rel[k], tk = S->b_tag[k];
-                w.p = pk;
-                bool jumped = w.op(pk, tk, S->stk, pre_n, S->lk_len, S->lk_rev, S->lk_off, S->lk_pos);
-                w.clean_hint = 0;
-                const i64 c_dense = clock64();
-                if (jumped && !w.error) {
-                    // dense-match regime: examine the next positions directly from the bytes until a
-                    // window of 32 positions passes without an emission, then re-synchronise with the list
-                    for (; DENSE_LOOP;) {
-                        if (w.error || w.p >= w.end) break;
-                        i64 b0 = w.p + 1;                       // positions b0 + lane
-                        i64 v0 = S->hx[__ldg(buf + b0 + lane)];
-                        i64 v1 = S->hx[__ldg(buf + b0 + 32 + lane)];
-                        i64 P0 = xor_scan_incl(v0, lane);
-                        i64 tot0 = __shfl_sync(FULL, P0, 31);
-                        i64 P1 = tot0 ^ xor_scan_incl(v1, lane);
-                        int hi_i = lane + 30;
-                        i64 a0 = __shfl_sync(FULL, P0, hi_i & 31);
-                        i64 a1 = __shfl_sync(FULL, P1, hi_i & 31);
-                        i64 lo_v = __shfl_up_sync(FULL, P0, 1);
-                        if (lane == 0) lo_v = 0;
-                        i64 tq = (hi_i < 32 ? a0 : a1) ^ lo_v;
-                        bool again = false, bail = false;
-                        int lim = (w.end - w.p) < 32 ? (int)(w.end - w.p) : 32;   // positions b0..min(b0+31,end)
-                        // one round trip for the 32 filter words (op() asks again: a tag inserted inside this window is seen there)
-                        const unsigned fmask = __ballot_sync(FULL, filt_query(filt, tq));
-                        for (int j = 0; j < lim; j++) {
-                            i64 tj = __shfl_sync(FULL, tq, j);
-                            if ((tj & w.min_mask) != w.min_mask) continue;
-                            if ((fmask >> j) & 1u) {   // an equal tag may exist: its lookup belongs to the whole CTA (next cut op)
-                                w.p = b0 + j - 1;
-                                bail = true;
-                                break;
+                        if (found && n_tot <= LK_CAP) {
+                            // single_match_len (rzip.c:372-397) per candidate: the warps share the candidates for the first
+                            // LK_XCAP bytes either side; whatever still matches there is extended by the whole CTA
+                            w.last = sh->run.last;
+                            const i64 lo_m = w.last > 0 ? w.last : 0;
+                            const i64 maxf = end - pk;
+                            const int NW = T >> 5;
+                            if (tid == 0) S->lk_n = 0;      // candidates still matching at the cap
+                            __syncthreads();
+                            for (int q = wid; q < n_tot; q += NW) {
+                                const i64 off = __ldcg(toff + ((h + S->lk_pos[q]) & hmask));
+                                i64 f = 0, r = 0;
+                                if (off < pk) {
+                                    i64 maxb = pk - lo_m;
+                                    if (off < maxb) maxb = off;
+                                    const i64 mf = maxf < LK_XCAP ? maxf : LK_XCAP, mb = maxb < LK_XCAP ? maxb : LK_XCAP;
+                                    {   // the first 256 bytes of both directions in one round trip
+                                        const i64 kk = lane * 8;
+                                        u64 xf = 0, xb = 0;
+                                        if (kk < mf) xf = ld_u64_unaligned(buf, pk + kk) ^ ld_u64_unaligned(buf, off + kk);
+                                        if (kk < mb) xb = ld_u64_unaligned(buf, pk - 8 - kk) ^ ld_u64_unaligned(buf, off - 8 - kk);
+                                        unsigned mm = __ballot_sync(FULL, xf != 0);
+                                        if (mm) {
+                                            const int l = __ffs(mm) - 1;
+                                            int nb = xf ? ((__ffsll((long long)xf) - 1) >> 3) : 8;
+                                            nb = __shfl_sync(FULL, nb, l);
+                                            f = l * 8 + nb;
+                                        } else
+                                            f = mf > 256 ? 256 + w.extend(pk + 256, off + 256, mf - 256, true) : mf;
+                                        if (f > mf) f = mf;
+                                        mm = __ballot_sync(FULL, xb != 0);
+                                        if (mm) {
+                                            const int l = __ffs(mm) - 1;
+                                            int nb = xb ? (__clzll((long long)xb) >> 3) : 8;
+                                            nb = __shfl_sync(FULL, nb, l);
+                                            r = l * 8 + nb;
+                                        } else
+                                            r = mb > 256 ? 256 + w.extend(pk - 256, off - 256, mb - 256, false) : mb;
+                                        if (r > mb) r = mb;
+                                    }
+                                    if (lane == 0 && ((f == LK_XCAP && maxf > LK_XCAP) || (r == LK_XCAP && maxb > LK_XCAP))) atomicAdd(&S->lk_n, 1);
+                                }
+                                if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; S->lk_off[q] = off; }
                             }
-                            w.p = b0 + j;
-                            if (w.op(b0 + j, tj, S->stk)) { again = true; break; }
+                            __syncthreads();
+                            // many long candidates (dense repeats, deep chains): the warps carry on in parallel, one candidate
+                            // each, up to LK_XCAP2; the whole CTA then only extends what is still matching there
+                            const i64 cap = S->lk_n > 2 ? (i64)LK_XCAP2 : (i64)LK_XCAP;
+                            if (cap != LK_XCAP) {
+                                for (int q = wid; q < n_tot; q += NW) {
+                                    const i64 off = S->lk_off[q];
+                                    if (off >= pk) continue;
+                                    i64 f = S->lk_f[q], r = S->lk_r[q];
+                                    i64 maxb = pk - lo_m;
+                                    if (off < maxb) maxb = off;
+                                    if (f == LK_XCAP && maxf > LK_XCAP) f += w.extend(pk + LK_XCAP, off + LK_XCAP, (maxf < cap ? maxf : cap) - LK_XCAP, true);
+                                    if (r == LK_XCAP && maxb > LK_XCAP) r += w.extend(pk - LK_XCAP, off - LK_XCAP, (maxb < cap ? maxb : cap) - LK_XCAP, false);
+                                    __syncwarp();
+                                    if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; }
+                                }
+                                __syncthreads();
+                            }
+                            for (int q = 0; q < n_tot; q++) {
+                                const i64 off = S->lk_off[q];
+                                i64 f = S->lk_f[q], r = S->lk_r[q], m = 0;
+                                if (off < pk) {
+                                    i64 maxb = pk - lo_m;
+                                    if (off < maxb) maxb = off;
+                                    if (f == cap && maxf > cap) f += cta_extend(S, buf, pk + cap, off + cap, maxf - cap, true);
+                                    if (r == cap && maxb > cap) r += cta_extend(S, buf, pk - cap, off - cap, maxb - cap, false);
+                                    m = f + r < MRZ_MIN_MATCH ? 0 : f + r;
+                                }
+                                if (tid == 0) { S->lk_len[q] = m; S->lk_rev[q] = r; }
+                            }
+                            __syncthreads();
+                            pre_n = n_tot;
                         }
-                        if (again) continue;
-                        if (!bail) w.p = b0 + lim - 1;
-                        break;
                     }
-                    // re-synchronise with the candidate list - unless the batch simply carries on past the jump (below)
-                    bool stay = !w.error && w.nlog <= WLOG_CAP && w.min_mask == min_mask && w.ins_mask == ins_mask && w.p >= pk &&
-                                (i64)S->b_rel[nr - 1] > w.p - seg_lo;
-                    if (!stay) {
-                        i64 nli = ncand;
-                        if (!w.error && w.p < w.end && w.p + 1 < seg_hi) {
-                            i64 rel = w.p + 1 - seg_lo;
-                            i64 tile = rel / SCAN_TILE;
-                            nli = list_seek(cand_pos, tile_off[tile], tile_off[tile + 1], (u32)rel, lane);
+                    // ---- op k on the live table, reference semantics (warp 0)
+                    if (wid == 0) {
+                        w.load(sh);
+                        w.nlog = 0;
+                        i64 hint = w.clean_ptr;
+                        if (steady) {
+                            const unsigned ei = sh->e_idx, ec = sh->e_cnt;
+                            const i64 es = sh->e_scan;
+                            hint = (ec != ei) ? (i64)sh->E[ei & (MRZ_EQ_CAP - 1)] : (es > hint ? es : hint);
                         }
-                        if (lane == 0) S->li = nli;
+                        w.clean_hint = hint;
+                        w.p = pk;
+                        const bool jumped = w.op(pk, tk, S->stk, pre_n, S->lk_len, S->lk_rev, S->lk_off, S->lk_pos);
+                        w.clean_hint = 0;
+                        w.store(sh);
+                        if (lane == 0) {
+                            const bool mask_changed = w.min_mask != min_mask || w.ins_mask != ins_mask;
+                            const bool overflow = w.nlog > MRZ_WLOG_CAP;
+                            sh->jumped = jumped;
+                            sh->nlog = overflow ? 0 : w.nlog;
+                            for (int q = 0; q < sh->nlog; q++) sh->wlog[q] = S->wlog[q];
+                            int kp = nr;
+                            if (jumped && !mask_changed && !overflow && !w.error && w.p >= pk) {   // (a short match can end BEFORE op k: p goes back, rzip.c:597)
+                                // an emission skips the ops up to the end of the match; the plans beyond it stay good (only a
+                                // write to a plan's stop slot can spoil it): carry on with the first op past the jump
+                                int a = k + 1, b = nr;
+                                while (a < b) {
+                                    const int m = (a + b) >> 1;
+                                    if (sh->b_pos[m] <= w.p) a = m + 1; else b = m;
+                                }
+                                kp = a;
+                            }
+                            if (mask_changed || overflow || w.error || (jumped && kp >= nr)) {
+                                sh->ended = 1;
+                                sh->e_idx = sh->e_cnt = 0; sh->e_scan = w.clean_ptr;    // rebuild the ring
+                                // what this batch had gathered behind p is gathered again (a jump past the batch keeps the cursor)
+                                if (w.p + 1 < sh->gp) sh->gp = w.p + 1;
+                            } else {
+                                if (steady) sync_queue(sh, S->wlog, w.nlog);
+                                sh->pos = jumped ? kp : k + 1;
+                            }
+                        }
                     }
-                    if (dbg && lane == 0) { dbg[30] += clock64() - c_dense; dbg[31] += 1; }
                 }
-                w.store(S->run);
-                if (lane == 0) {
-                    bool mask_changed = w.min_mask != min_mask || w.ins_mask != ins_mask;
-                    bool overflow = w.nlog > WLOG_CAP;
-                    S->jumped = jumped;
-                    S->nlog = overflow ? 0 : w.nlog;
-                    int kp = nr;
-                    if (jumped && !mask_changed && !overflow && !w.error && w.p >= pk) {   // (a short match can end BEFORE op k: p goes back, rzip.c:597)
-                        // an emission skips the ops up to the end of the match; the plans beyond it stay good (only a
-                        // write to a plan's stop slot can spoil it): carry on with the first op past the jump
-                        int a = k + 1, b = nr;
-                        const i64 relp = w.p - seg_lo;
-                        while (a < b) {
-                            const int m = (a + b) >> 1;
-                            if ((i64)S->b_rel[m] <= relp) a = m + 1; else b = m;
-                        }
-                        kp = a;
-                    }
-                    if (mask_changed || overflow || w.error || (jumped && kp >= nr)) {
-                        S->ended = 1;
-                        S->e_idx = S->e_cnt = 0; S->e_scan = w.clean_ptr;    // rebuild the queue
-                        if (!jumped) S->li = (i64)S->b_li[k] + 1;
-                    } else {
-                        if (steady) sync_queue(S, w.nlog);
-                        S->pos = jumped ? kp : k + 1;
+                csync(CL);
+                TICK(5);
+                if (sh->ended) { batch_ended = true; break; }
+                // the op overwrote a queued slot and the ring was cut there: rebuild its tail, but only inside the
+                // window this batch was planned with
+                if (steady && sh->e_scan < w_hi) refill_queue(sh, S, ttag, btm, w_hi, MRZ_EQ_CAP, CL, rank, j, B);
+                npos = sh->pos;   // k + 1, or the first op past an emission's jump (the ops in between never run)
+                // later plans that read a slot this op wrote are no longer valid; nor is its twin's plan
+                if (j == npos && (pl.flags & F_FOLLOW)) pl.flags |= F_CONF;
+                if (j >= npos && j < nr)   // a plan forwarded over the claim of op k / of a skipped op assumed that op's planned write
+                    for (int dd = 0; dd < pl.ndep; dd++)
+                        if (pl.dep_own[dd] >= k && pl.dep_own[dd] < npos) pl.flags |= F_CONF;
+                if (j >= npos && j < nr && (pl.flags & F_FOLLOW) && j - 1 >= k && j - 1 < npos) pl.flags |= F_CONF;   // its leader was skipped
+                if (j >= npos && j < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
+                    const int nl = sh->nlog;
+                    for (int q = 0; q < nl; q++) {
+                        const int sl = sh->wlog[q] >> 1;
+                        bool hit = sl == pl.w2_slot || ((pl.flags & F_W1) && sl == pl.w1_slot);
+                        for (int dd = 0; dd < pl.ndep; dd++) hit = hit || sl == pl.dep_slot[dd];
+                        if (hit) { pl.flags |= F_CONF; break; }
                     }
                 }
             }
-            __syncthreads();
-            TICK(5);   // serial op
-            if (S->ended) break;
-            // the op overwrote a queued slot and the queue was cut there: rebuild its tail, but only inside the
-            // window this batch was planned with
-            if (steady && S->e_scan < w_hi) refill_queue(S, ttag, w_hi, EQ_CAP);
-            // later plans that read a slot this op wrote are no longer valid; nor is its twin's plan
-            const int npos = S->pos;   // k + 1, or the first op past an emission's jump (the ops in between never run)
-            if (tid == npos && (pl.flags & F_FOLLOW)) pl.flags |= F_CONF;
-            if (tid >= npos && tid < nr)   // a plan forwarded over the claim of op k / of a skipped op assumed that op's planned write
-                for (int d = 0; d < pl.ndep; d++)
-                    if (pl.dep_own[d] >= k && pl.dep_own[d] < npos) pl.flags |= F_CONF;
-            if (tid >= npos && tid < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
-                const int nl = S->nlog;
-                for (int q = 0; q < nl; q++) {
-                    int sl = S->wlog[q] >> 1;
-                    bool hit = sl == pl.w2_slot || ((pl.flags & F_W1) && sl == pl.w1_slot);
-                    for (int d = 0; d < pl.ndep; d++) hit = hit || sl == pl.dep_slot[d];
-                    if (hit) {
-                        pl.flags |= F_CONF;
-                        break;
+            pos = npos;
+            // ---------------------------------------------------------------- plan again what lost its plan
+            // All ops before `pos` are in the table now, so the first of these plans is exact; the others are as
+            // speculative as a first plan and are validated by the next round of claims.  A twin becomes an ordinary
+            // op: if its leader has been committed, the filter finds the leader's entry.
+            if (j >= pos && j < nr && (pl.flags & F_CONF) && !(pl.flags & F_COMPLEX)) {
+                plan_init(pl);
+                follower = false;
+                lead_w2 = -1;
+                if (filt_query(filt, my_tag)) pl.flags |= F_COMPLEX;
+                else if ((my_tag & ins_mask) == ins_mask)
+                    plan_op(pl, ttag, toff, gsum, filt, my_tag, my_tag & hmask, hmask, hsize, min_mask, chain);
+                sh->pl_fl[j] = pl.flags; sh->pl_w2[j] = pl.w2_slot;
+                if (dbg) atomicAdd((unsigned long long *)&dbg[30], 1ULL);
+            }
+            if (dbg && j == 0) tm[11] += 1;
+            TICK(6);
+        }
+        // ================================================================ batch epilogue
+        // a committed plan overwrote a slot of the ring that the sweep had not reached: cut the ring there
+        if (!batch_ended && steady) {
+            const int qc = sh->qcut;
+            if (qc != 0x7fffffff && rank == 0 && wid == 0) {
+                // first ring index whose slot is >= qc (32-ary search by one warp)
+                unsigned a = sh->e_idx, b = sh->e_cnt;
+                while (b - a > 32) {
+                    const unsigned len = b - a;
+                    const unsigned idx = a + (unsigned)(((unsigned long long)len * lane) / 32);
+                    const int v = sh->E[idx & (MRZ_EQ_CAP - 1)];
+                    const unsigned ge = __ballot_sync(FULL, v >= qc);
+                    if (!ge) a = a + (unsigned)(((unsigned long long)len * 31) / 32) + 1;
+                    else {
+                        const int l = __ffs(ge) - 1;
+                        if (l == 0) { b = a; break; }
+                        const unsigned na = a + (unsigned)(((unsigned long long)len * (l - 1)) / 32) + 1;
+                        b = a + (unsigned)(((unsigned long long)len * l) / 32) + 1;
+                        a = na;
                     }
                 }
+                if (b > a) {
+                    const bool in = a + lane < b;
+                    const int v = in ? sh->E[(a + lane) & (MRZ_EQ_CAP - 1)] : 0x7fffffff;
+                    const unsigned ge = __ballot_sync(FULL, in && v >= qc);
+                    a = ge ? a + (__ffs(ge) - 1) : b;
+                }
+                if (lane == 0 && a != sh->e_cnt) { sh->e_cnt = a; sh->e_scan = qc; }
             }
-            __syncthreads();
-            TICK(6);   // invalidation
         }
-        // ---------------------------------------------------------------- batch epilogue
-        if (tid == 0) {
-            if (!S->ended) S->li = li;                       // whole batch consumed
-            // batch size: small after an emission (the plans behind a jump are wasted), growing back
-            if (S->jumped) S->bmax = st->pad0 > 0 ? st->pad0 : AT;   // measured: restarting small after an emission only adds batches
-            else if (S->bmax < AT) S->bmax *= 2;
-        }
-        __syncthreads();
+        csync(CL);
         TICK(7);
     }
-    if (tid == 0 && dbg)
-        for (int q = 0; q < 11; q++) dbg[q] += tm[q];
-    if (tid == 0 && H > 0) {   // release the helper CTAs
-        __threadfence();
-        *(volatile unsigned *)&io->seq = 0xffffffffu;
+    if (j == 0 && dbg) {
+        for (int q = 0; q < 12; q++) dbg[q] += tm[q];
     }
-    // segment exhausted (or chunk finished)
-    if (tid == 0) {
-        const Run &r = S->run;
-        i64 p = r.p;
-        if (!r.error && p < seg_hi - 1) p = seg_hi - 1;
-        st->p = p; st->last = r.last; st->cur_p = r.cur_p; st->cur_len = r.cur_len; st->cur_ofs = r.cur_ofs;
-        st->min_mask = r.min_mask; st->ins_mask = r.ins_mask; st->clean_ptr = r.clean_ptr; st->count = r.count;
-        st->victim_round = r.vr;
-        st->tag_hits = r.hits; st->tag_misses = r.misses; st->inserts = r.inserts; st->victim_events = r.vevents;
-        st->n_ops = r.nops; st->ntok = r.ntok;
-        if (r.error) st->error = r.error;
-        if (p >= end) st->done = 1;
-        st->pad1 = (int)S->epoch;
+    if (j == 0) {
+        i64 p = sh->run.p;
+        const int err = sh->run.error;
+        if (!err && p < end) p = end;
+        st->p = p; st->last = sh->run.last; st->cur_p = sh->run.cur_p; st->cur_len = sh->run.cur_len; st->cur_ofs = sh->run.cur_ofs;
+        st->min_mask = sh->run.min_mask; st->ins_mask = sh->run.ins_mask; st->clean_ptr = sh->run.clean_ptr; st->count = sh->run.count;
+        st->victim_round = sh->run.vr;
+        st->tag_hits = sh->run.hits; st->tag_misses = sh->run.misses; st->inserts = sh->run.inserts; st->victim_events = sh->run.vevents;
+        st->n_ops = sh->run.nops; st->ntok = sh->run.ntok;
+        st->err_a = sh->err_a; st->err_b = sh->err_b;
+        if (err) st->error = err;
+        else st->done = 1;
     }
+#undef TICK
 }
 
-extern "C" size_t mrz_planio_bytes() { return sizeof(PlanIO); }
-
-// helpers = number of plan-offload CTAs (0, or a power of two <= 32); > 0 needs a cooperative launch: the CTAs wait on one another.
-extern "C" int mrz_launch_automaton(const u8 *buf, i64 *ttag, i64 *toff, u64 *filt, u32 *gsum, unsigned *claim, const i64 *hidx, AutoState *st,
-                                    const i64 *tile_off, const u32 *cand_pos, const i64 *cand_tag, Token *toks, i64 *dbg, int helpers,
-                                    void *planio, cudaStream_t s) {
-    PlanIO *io = (PlanIO *)planio;
 #ifndef MRZ_CUSIM
-    // once per device: mrz_run_variants launches this kernel from many host threads at once, and the attribute must not
-    // be rewritten under a concurrent launch of the same function
-    cudaError_t e = cudaSuccess;
-    {
-        static std::mutex mu;
-        static bool set_for[64];
-        int dev = 0;
-        cudaGetDevice(&dev);
-        std::lock_guard<std::mutex> g(mu);
-        if (!set_for[dev & 63]) {
-            e = cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-            if (e != cudaSuccess) return (int)e;
-            set_for[dev & 63] = true;
-        }
-    }
-    if (helpers > 0) {
-        e = cudaMemsetAsync(io, 0, 8, s);   // seq, done
-        if (e != cudaSuccess) return (int)e;
-        void *args[] = {(void *)&buf, (void *)&ttag, (void *)&toff, (void *)&filt, (void *)&gsum, (void *)&claim, (void *)&hidx, (void *)&st,
-                        (void *)&tile_off, (void *)&cand_pos, (void *)&cand_tag, (void *)&toks, (void *)&dbg, (void *)&io};
-        return (int)cudaLaunchCooperativeKernel((const void *)k_automaton, dim3(1 + helpers), dim3(AT), args, sizeof(Smem), s);
-    }
-    k_automaton<<<1, AT, sizeof(Smem), s>>>(buf, ttag, toff, filt, gsum, claim, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg, io);
-    return (int)cudaGetLastError();
+// function attributes: once per device, never rewritten under a concurrent launch from another host thread
+static int set_attributes_once() {
+    static std::mutex mu;
+    static bool set_for[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> g(mu);
+    if (set_for[dev & 63]) return 0;
+    cudaError_t e = cudaFuncSetAttribute(k_automaton, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(k_automaton, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) return (int)e;
+    set_for[dev & 63] = true;
+    return 0;
+}
+static void cluster_config(cudaLaunchConfig_t &cfg, cudaLaunchAttribute *at, int nclusters, int CL, int T, cudaStream_t s) {
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3((unsigned)(nclusters * CL));
+    cfg.blockDim = dim3((unsigned)T);
+    cfg.dynamicSmemBytes = sizeof(Smem);
+    cfg.stream = s;
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+}
+#endif
+
+// How many clusters of CL CTAs x T threads the device holds at once (0 on error).
+extern "C" int mrz_max_active_clusters(int CL, int T) {
+#ifndef MRZ_CUSIM
+    if (set_attributes_once()) return 0;
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute at[1];
+    cluster_config(cfg, at, 1, CL, T, 0);
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, k_automaton, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
 #else
-    if (helpers > 0) {
-        memset(io, 0, 8);
-        MRZ_LAUNCH_COOP(k_automaton, 1 + helpers, AT, sizeof(Smem), s, buf, ttag, toff, filt, gsum, claim, hidx, st, tile_off, cand_pos, cand_tag,
-                        toks, dbg, io);
-    } else
-        MRZ_LAUNCH_COOP(k_automaton, 1, AT, sizeof(Smem), s, buf, ttag, toff, filt, gsum, claim, hidx, st, tile_off, cand_pos, cand_tag, toks, dbg, io);
+    (void)CL; (void)T;
+    return 1 << 20;
+#endif
+}
+
+// nclusters automata (descs[0..nclusters)), CL CTAs of T threads each, one launch.
+extern "C" int mrz_launch_automata(const AutoDesc *descs, int nclusters, int CL, int T, cudaStream_t s) {
+#ifndef MRZ_CUSIM
+    cudaError_t e;
+    {
+        int rc = set_attributes_once();
+        if (rc) return rc;
+    }
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute at[1];
+    cluster_config(cfg, at, nclusters, CL, T, s);
+    e = cudaLaunchKernelEx(&cfg, k_automaton, descs);
+    return (int)e;
+#else
+    MRZ_LAUNCH_CLUSTER(k_automaton, nclusters * CL, CL, T, sizeof(Smem), s, descs);
     return 0;
 #endif
 }

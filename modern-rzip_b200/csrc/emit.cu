@@ -261,8 +261,13 @@ __global__ void k_crc_tail(const u8 *__restrict__ buf, i64 start, i64 len, u32 *
 }
 
 // ---- launchers ---------------------------------------------------------------------------------
-extern "C" void mrz_crc_upload_consts(const void *host_consts) {
+extern "C" void mrz_crc_upload_consts(const void *host_consts, cudaStream_t s) {
+#ifdef MRZ_CUSIM
+    (void)s;
     cudaMemcpyToSymbol(c_crc, host_consts, sizeof(CrcConst));
+#else
+    cudaMemcpyToSymbolAsync(c_crc, host_consts, sizeof(CrcConst), 0, cudaMemcpyHostToDevice, s);
+#endif
 }
 
 extern "C" void mrz_launch_crc(const u8 *buf, i64 n, u32 *part, u32 *part2, u32 *tail, cudaStream_t s, int *launches) {

@@ -1,6 +1,7 @@
 // Shared device-side definitions for the B200 rzip pre-processor.
 // Semantics follow /root/reference/src/rzip.c (cited per function); the code is a new design:
-// candidate lists instead of a per-byte loop, a warp-wide probe of 32 slots, token triples.
+// a per-position "bitness" map instead of a per-byte loop, a thread-block cluster per chunk,
+// token triples instead of byte streams.
 #pragma once
 #ifndef MRZ_CUSIM   // tests/cusim compiles these sources for the CPU emulator with -include cusim.h
 #include <cuda_runtime.h>
@@ -16,35 +17,41 @@ typedef unsigned int u32;
 #define MRZ_MIN_MATCH 31      // rzip.c:49 MINIMUM_MATCH
 #define MRZ_GREAT_MATCH 1024  // rzip.c:48 GREAT_MATCH
 #define MRZ_PAD 256           // zero padding before and after the chunk in HBM
-#define MRZ_FILT_WORDS (1 << 24)   // tag filter: 2^24 64-bit words = 128 MiB (automaton.cu FILT_BITS)
 
-#define SCAN_THREADS 256
-#define SCAN_RUN 32                            // positions per thread
-#define SCAN_TILE (SCAN_THREADS * SCAN_RUN)    // positions per CTA tile (8192)
-#define SEG_MAX_TILES 8192                     // <= 64 Mi positions per segment
-#define SEG_CAND_CAP (4 << 20)                 // flat candidate capacity per segment
-#define SEG_CAND_TARGET (1 << 20)              // aim for this many candidates per segment
+// ---- tag map (tagmap.cu) ------------------------------------------------------------------------
+// bmap[p] = number of trailing one bits of tag[p] (rzip.c:348-358) for p in [0, n-30), 0 beyond; a position passes
+// the lookup gate `(t & mask) == mask` (rzip.c:573) for mask = 2^k-1 iff bmap[p] >= k.  bsum[b] = max of bmap over
+// the 64 positions [64b, 64b+64).
+#define MAP_RUN 32                             // positions per thread
+#define MAP_THREADS 256
+#define MAP_TILE (MAP_THREADS * MAP_RUN)       // positions per CTA step (8192)
+#define MAP_BLK 64                             // positions per summary byte
+#define MAP_BLK_SHIFT 6
 
-// One hash-table slot (rzip.c:59-62 struct hash_entry): all-zero == empty (rzip.c:230).
-struct __align__(16) Slot {
-    i64 off;
-    i64 tag;
-};
+// ---- automaton (automaton.cu) -------------------------------------------------------------------
+#define MRZ_MAXCL 16          // CTAs per cluster (16 needs the non-portable cluster size attribute)
+#define MRZ_MAXT 512
+#define MRZ_MAXB (MRZ_MAXCL * MRZ_MAXT)   // ops per batch (8192); claim keys hold 14 bits of op index
+#define MRZ_EQ_CAP (1 << 18)  // ring of sweep-eligible slots (power of two)
+#define MRZ_WLOG_CAP 64
+#define MRZ_NDBG 64
 
+// One hash-table slot (rzip.c:59-62 struct hash_entry): all-zero == empty (rzip.c:230).  Stored as two arrays.
 // Un-split match token; literals are the gaps between matches.
 struct Token {
     i64 pos, len, ofs;
 };
 
-// Automaton state, resident in HBM between kernels (rzip_state, mrzip_private.h:388-416).
+// Automaton state exchanged with the host (rzip_state, mrzip_private.h:388-416): the host fills the constants and
+// the initial running state, the kernel writes the final one.
 struct AutoState {
     // chunk constants
     i64 n, end;               // chunk size, n - 31
     i64 hsize, hmask, limit;  // table geometry (rzip.c:521-529)
     int chain;                // levels[].max_chain_len
     int done;                 // 1 when p reached end
-    int error;                // non-zero: internal inconsistency / token overflow
-    int pad0;
+    int error;                // non-zero: 2 = token buffer full, other = internal inconsistency (site id)
+    int filt_bits;            // log2 of the tag filter's 64-bit words
     // running state
     i64 p;                    // last position examined (loop variable of rzip.c:548)
     i64 last;                 // st->last_match
@@ -55,12 +62,7 @@ struct AutoState {
     // counters
     i64 tag_hits, tag_misses, inserts, victim_events, n_ops;
     i64 ntok, tok_cap;
-    // current segment (written by the tag-scan kernels)
-    i64 seg_lo, seg_hi;       // candidate positions cover [seg_lo, seg_hi)
-    i64 seg_mask;             // lookup mask the list was filtered with
-    i64 seg_ncand;            // candidates in the flat list
-    int seg_tiles;            // tiles covered
-    int pad1;
+    i64 err_a, err_b;         // MRZ_CHECK: offending index / bound of a failed range check
 };
 
 struct EmitTotals {
@@ -70,20 +72,6 @@ struct EmitTotals {
 __device__ __forceinline__ int tz1(i64 t) {  // trailing one bits (rzip.c:247-252 lesser_bitness via ffsll(~x))
     u64 x = ~(u64)t;
     return x ? (__ffsll((long long)x) - 1) : -1;
-}
-
-__device__ __forceinline__ Slot ld_slot(const Slot *p) {
-    longlong2 v = __ldcg(reinterpret_cast<const longlong2 *>(p));
-    Slot s;
-    s.off = v.x;
-    s.tag = v.y;
-    return s;
-}
-__device__ __forceinline__ void st_slot(Slot *p, i64 off, i64 tag) {
-    longlong2 v;
-    v.x = off;
-    v.y = tag;
-    __stcg(reinterpret_cast<longlong2 *>(p), v);
 }
 
 // Eight consecutive i64 (64-byte aligned) with two 256-bit loads (LDG.E.256 on sm_100a), L2-coherent.

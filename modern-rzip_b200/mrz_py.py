@@ -9,10 +9,6 @@ import os
 
 import numpy as np
 
-# one hardware queue per automaton stream of mrz_run_variants (see mrz_device_count in csrc/mrz_gpu.cu); must be set
-# before anything in the process creates the CUDA context
-os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
-
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmrz_gpu.so")
 
@@ -20,8 +16,43 @@ DECLARED_SYMBOLS = [
     "mrz_device_count", "mrz_version", "mrz_last_error", "mrz_ctx_create", "mrz_ctx_destroy",
     "mrz_rzip_chunk", "mrz_upload", "mrz_run_resident", "mrz_download", "mrz_host_alloc", "mrz_host_free",
     "mrz_debug_tags", "mrz_debug_crc32", "mrz_debug_tokens",
-    "mrz_ctx_create_variant", "mrz_run_automaton", "mrz_run_emit", "mrz_run_variants",
+    "mrz_ctx_create_variant", "mrz_run_automaton", "mrz_run_emit", "mrz_run_variants", "mrz_run_many",
+    "mrz_config_default", "mrz_ctx_create_ex", "mrz_upload_part", "mrz_upload_wait", "mrz_upload_finish",
+    "mrz_download_part", "mrz_get_profile", "mrz_debug_tagmap",
 ]
+
+LEVELS = [(1, 4, 1), (2, 4, 2), (4, 4, 2), (8, 4, 2), (16, 4, 3), (32, 4, 4), (32, 2, 6), (64, 1, 16), (64, 1, 32), (64, 1, 128)]
+CHAIN = [c for _, _, c in LEVELS]     # levels[].max_chain_len, rzip.c:65-73
+
+
+def hash_index(skip_files=0):
+    """st->hash_index as the host computes it (host/rzip_fd.c init_hash_indexes, rzip.c:669-673): 256 entries of
+    (random() << 16) ^ random() from glibc's unseeded random() (== srandom(1)); file k of one command line uses draws
+    512k .. 512k+511 (main.c:651).  Restated here so that the harness does not need the oracle for its parameters."""
+    libc = C.CDLL(None)
+    libc.random.restype = C.c_long
+    libc.srandom(1)
+    for _ in range(512 * skip_files):
+        libc.random()
+    out = np.empty(256, dtype=np.int64)
+    for i in range(256):
+        a = libc.random()
+        b = libc.random()
+        out[i] = (a << 16) ^ b
+    return out
+
+
+def chunk_bytes(n):
+    """st->chunk_bytes (rzip.c:1006-1008): bytes needed for a distance inside a chunk of n bytes, at least 1."""
+    bits = 8
+    while n >> bits > 0:
+        bits += 1
+    return bits // 8 + (1 if bits % 8 else 0)
+
+
+class MrzConfig(C.Structure):
+    _fields_ = [("cluster_size", C.c_int32), ("threads", C.c_int32), ("filter_log2_words", C.c_int32),
+                ("profile", C.c_int32), ("token_divisor", C.c_int32), ("poison", C.c_int32), ("reserved", C.c_int32 * 2)]
 
 
 class MrzParams(C.Structure):
@@ -74,6 +105,16 @@ def bind(path):
         L.mrz_run_emit.argtypes = [C.c_void_p, C.POINTER(MrzResult)]
         L.mrz_run_variants.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.POINTER(MrzParams),
                                        C.POINTER(MrzResult)]
+        L.mrz_run_many.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_int64), C.POINTER(MrzParams),
+                                   C.POINTER(MrzResult)]
+        L.mrz_config_default.argtypes = [C.POINTER(MrzConfig)]
+        L.mrz_ctx_create_ex.argtypes = [C.c_int, C.c_int64, C.POINTER(MrzConfig), C.POINTER(C.c_void_p)]
+        L.mrz_upload_part.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
+        L.mrz_upload_wait.argtypes = [C.c_void_p]
+        L.mrz_upload_finish.argtypes = [C.c_void_p, C.c_int64]
+        L.mrz_download_part.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_int64]
+        L.mrz_get_profile.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
+        L.mrz_debug_tagmap.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]
     return L
 
 
@@ -113,8 +154,9 @@ class PinnedBuffer:
 
 
 class Context:
-    def __init__(self, device=0, max_chunk=1 << 28, library=None, parent=None):
-        """parent: create a variant context (mrz_ctx_create_variant) sharing the parent's chunk bytes."""
+    def __init__(self, device=0, max_chunk=1 << 28, library=None, parent=None, **config):
+        """parent: create a variant context (mrz_ctx_create_variant) sharing the parent's chunk bytes and tag map.
+        config: fields of mrz_config (cluster_size, threads, filter_log2_words, profile, token_divisor, poison)."""
         self.h = C.c_void_p()
         if parent is not None:
             self.L = parent.L
@@ -122,7 +164,11 @@ class Context:
             max_chunk = parent.max_chunk
         else:
             self.L = library if library is not None else lib()
-            rc = self.L.mrz_ctx_create(device, max_chunk, C.byref(self.h))
+            cfg = MrzConfig()
+            self.L.mrz_config_default(C.byref(cfg))
+            for k, v in config.items():
+                setattr(cfg, k, v)
+            rc = self.L.mrz_ctx_create_ex(device, max_chunk, C.byref(cfg), C.byref(self.h))
         if rc:
             raise MrzError("mrz_ctx_create rc=%d: %s" % (rc, self.L.mrz_last_error(None).decode()))
         self.max_chunk = max_chunk
@@ -179,6 +225,20 @@ class Context:
         self._check(self.L.mrz_debug_tags(self.h, n, hi, out.ctypes.data, count), "mrz_debug_tags")
         return out
 
+    def debug_tagmap(self, n, hash_index):
+        hi = (C.c_int64 * 256)(*[int(x) for x in hash_index])
+        bmap = np.empty(max(1, n), dtype=np.uint8)
+        bsum = np.empty(max(1, (n + 63) // 64), dtype=np.uint8)
+        self._check(self.L.mrz_debug_tagmap(self.h, n, hi, bmap.ctypes.data, bsum.ctypes.data), "mrz_debug_tagmap")
+        return bmap[:n], bsum[:(n + 63) // 64]
+
+    def profile(self):
+        """-> (64 phase counters of the last automaton run (profile=1), (CTAs per cluster, threads, automata))"""
+        cnt = (C.c_int64 * 64)()
+        geom = (C.c_int32 * 3)()
+        self._check(self.L.mrz_get_profile(self.h, cnt, geom), "mrz_get_profile")
+        return list(cnt), tuple(geom)
+
     def debug_tokens(self):
         cnt = C.c_int64()
         self.L.mrz_debug_tokens(self.h, None, 0, C.byref(cnt))
@@ -191,8 +251,8 @@ class VariantSet:
     """One resident chunk, `nvar` automata side by side: variant v runs with victim_round_in = v (include/mrz_gpu.h,
     mrz_run_variants).  ctxs[0] is the parent (owns the chunk bytes), the others are variant contexts."""
 
-    def __init__(self, device, max_chunk, nvar, library=None):
-        self.parent = Context(device, max_chunk, library=library)
+    def __init__(self, device, max_chunk, nvar, library=None, **config):
+        self.parent = Context(device, max_chunk, library=library, **config)
         self.ctxs = [self.parent] + [Context(parent=self.parent) for _ in range(nvar - 1)]
         self.nvar = nvar
         self.L = self.parent.L

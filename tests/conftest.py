@@ -15,7 +15,7 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def gpu_ctx():
     import mrz_py
-    ctx = mrz_py.Context(0, 1 << 28)
+    ctx = mrz_py.Context(0, 1 << 28, poison=1)   # every work buffer starts as 0xA5: a read-before-write cannot hide
     yield ctx
     ctx.close()
 
@@ -27,6 +27,7 @@ def sim_ctx():
     import mrz_py
     d = os.path.join(ROOT, "tests", "cusim")
     subprocess.check_call(["make", "-C", d, "libmrz_sim.so"], stdout=subprocess.DEVNULL)
-    ctx = mrz_py.Context(0, 1 << 26, library=mrz_py.bind(os.path.join(d, "libmrz_sim.so")))
+    # a cluster of 2 CTAs x 64 threads per automaton; every work buffer starts poisoned (0xA5), not zeroed
+    ctx = mrz_py.Context(0, 1 << 26, library=mrz_py.bind(os.path.join(d, "libmrz_sim.so")), cluster_size=2, threads=64, poison=1)
     yield ctx
     ctx.close()

@@ -17,6 +17,8 @@ static const int kMaxFibers = 16384;       // all resident blocks of a cooperati
 static const int kMaxBlocks = 256;
 static thread_local int grid_arrived = 0, grid_blocks = 0;
 static thread_local unsigned grid_gen = 0;
+static thread_local int cl_arrived[kMaxBlocks];
+static thread_local unsigned cl_gen[kMaxBlocks];
 
 extern "C" void cusim_switch(void **save_sp, void *load_sp);
 asm(R"(
@@ -57,6 +59,14 @@ void sync_grid() {
     Fiber *f = cur;
     if (++grid_arrived == grid_blocks) { grid_arrived = 0; grid_gen++; return; }
     f->status = 4; f->bar_gen = grid_gen;
+    yield_to_scheduler();
+}
+
+void sync_cluster() {
+    Fiber *f = cur;
+    Block &b = *blkp;
+    if (++cl_arrived[b.cluster] == b.csize) { cl_arrived[b.cluster] = 0; cl_gen[b.cluster]++; return; }
+    f->status = 6; f->bar_gen = cl_gen[b.cluster];
     yield_to_scheduler();
 }
 
@@ -121,6 +131,7 @@ static void run_resident(int nblocks, int nthreads) {
             if (f->status == 2 && f->warp_gen == b->warps[f->warp].gen) continue;
             if (f->status == 4 && f->bar_gen == grid_gen) continue;
             if (f->status == 5 && *f->wait_addr == f->wait_old) continue;
+            if (f->status == 6 && f->bar_gen == cl_gen[b->cluster]) continue;
             f->status = 0;
             cur = f;
             blkp = b;
@@ -149,6 +160,7 @@ static void setup_block(Block *b, int bi, int first_fiber, uint3_ bid, dim3 grid
     b->warps = warp_pool + (first_fiber / 32) + bi;   // disjoint even when nthreads is not a multiple of 32
     b->bdim = block; b->gdim = grid; b->body = body; b->nthreads = nthreads;
     b->bid = bid; b->nlive = nthreads; b->bar_arrived = 0; b->bar_gen = 0; b->smem = smem;
+    b->cluster = bi; b->crank = 0; b->csize = 1;
     for (int w = 0; w < nwarps; w++) { b->warps[w].arrived = 0; b->warps[w].gen = 0; }
     for (int i = 0; i < nthreads; i++) {
         Fiber *f = &fiber_pool[first_fiber + i];
@@ -172,6 +184,29 @@ void launch(dim3 grid, dim3 block, const std::function<void()> &body) {
                 setup_block(&block_pool[0], 0, 0, uint3_{bx, by, bz}, grid, block, &body, nullptr);
                 run_resident(1, nthreads);
             }
+    blkp = saved_blk;
+    cur = saved_cur;
+}
+
+void launch_cluster(dim3 grid, dim3 block, int cl, size_t smem_bytes, const std::function<void()> &body) {
+    int nthreads = (int)(block.x * block.y * block.z);
+    int nblocks = (int)grid.x;
+    if (nthreads < 1 || nthreads > kMaxThreads || nblocks < 1 || nblocks > kMaxBlocks || nblocks * nthreads > kMaxFibers || cl < 1 ||
+        nblocks % cl || grid.y != 1 || grid.z != 1) {
+        fprintf(stderr, "cusim: bad cluster launch %d x %d, cluster %d\n", nblocks, nthreads, cl);
+        abort();
+    }
+    ensure_pools();
+    Block *saved_blk = blkp;
+    Fiber *saved_cur = cur;
+    char *smem = (char *)calloc((size_t)nblocks, smem_bytes + 64);
+    for (int b = 0; b < nblocks; b++) {
+        setup_block(&block_pool[b], b, b * nthreads, uint3_{(unsigned)b, 0, 0}, grid, block, &body, smem + (size_t)b * (smem_bytes + 64));
+        block_pool[b].cluster = b / cl; block_pool[b].crank = b % cl; block_pool[b].csize = cl;
+        cl_arrived[b] = 0; cl_gen[b] = 0;
+    }
+    run_resident(nblocks, nthreads);
+    free(smem);
     blkp = saved_blk;
     cur = saved_cur;
 }

@@ -51,6 +51,8 @@ static inline const char *cudaGetErrorString(cudaError_t) { return "cusim error"
 static inline cudaError_t cudaGetDeviceCount(int *n) { *n = 1; return 0; }
 static inline cudaError_t cudaSetDevice(int) { return 0; }
 static inline cudaError_t cudaGetLastError() { return 0; }
+enum { cudaDevAttrMultiProcessorCount = 16 };
+static inline cudaError_t cudaDeviceGetAttribute(int *v, int, int) { *v = 4; return 0; }
 template <class T> static inline cudaError_t cudaMalloc(T **p, size_t n) {
     *p = (T *)aligned_alloc(256, (n + 255) / 256 * 256 + 256);
     if (*p && getenv("CUSIM_POISON")) memset((void *)*p, 0xA5, (n + 255) / 256 * 256 + 256);   // recycled device memory is not zero
@@ -105,6 +107,7 @@ struct Block {
     dim3 bdim, gdim;
     const std::function<void()> *body;
     void *smem;          // dynamic shared memory of a cooperative launch (one per block)
+    int cluster, crank, csize;   // thread-block cluster (launch_cluster): id, rank in cluster, CTAs per cluster
 };
 extern thread_local Fiber *cur;
 extern thread_local Block *blkp;     // block of the running fiber
@@ -113,6 +116,11 @@ void launch(dim3 grid, dim3 block, const std::function<void()> &body);
 // all blocks resident at once (cudaLaunchCooperativeKernel): grid-wide barriers become possible
 void launch_coop(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()> &body);
 void sync_grid();                    // called by ONE thread of every block
+// thread-block clusters: consecutive groups of `cl` blocks, all resident; barrier.cluster == sync_cluster()
+void launch_cluster(dim3 grid, dim3 block, int cl, size_t smem_bytes, const std::function<void()> &body);
+void sync_cluster();                 // called by ONE thread of every block of the cluster
+static inline int cluster_rank() { return blkp->crank; }
+static inline int cluster_size() { return blkp->csize; }
 // spin-wait of a cooperative kernel: the fiber sleeps until *addr != old (polled by the scheduler, no busy switching)
 unsigned wait_change(volatile unsigned *addr, unsigned old);
 static inline void *dyn_smem() { return blkp->smem; }
@@ -213,3 +221,5 @@ template <class T> static inline T atomicCAS(T *p, T c, T v) { T o = *p; if (o =
     cusim::launch(dim3(grid), dim3(block), [=]() { kernel(__VA_ARGS__); })
 #define MRZ_LAUNCH_COOP(kernel, grid, block, smem, stream, ...) \
     cusim::launch_coop(dim3(grid), dim3(block), (smem), [=]() { kernel(__VA_ARGS__); })
+#define MRZ_LAUNCH_CLUSTER(kernel, grid, cl, block, smem, stream, ...) \
+    cusim::launch_cluster(dim3(grid), dim3(block), (cl), (smem), [=]() { kernel(__VA_ARGS__); })

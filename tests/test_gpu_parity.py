@@ -101,14 +101,15 @@ def test_crc_matches_zlib(gpu_ctx):
         assert res.crc32 == zlib.crc32(data.tobytes()), n
 
 
-def _variant_case(level, size, reps=2):
-    """Every victim_round_in of one resident chunk through mrz_run_variants, checked against the plain entry point
-    (all variants) and the oracle (a few), then emitted in arbitrary order and compared byte for byte."""
+def _variant_case(level, size, reps=2, **config):
+    """Every victim_round_in of one resident chunk through mrz_run_variants (ONE launch, a cluster per variant), checked
+    against the plain entry point (all variants) and the oracle (a few), then emitted in arbitrary order and compared
+    byte for byte."""
     import mrz_py
-    chain = [1, 2, 2, 2, 3, 4, 6, 16, 32, 128][level]
+    chain = mrz_py.CHAIN[level]
     data = H.as_u8(H.gen_motif(size, 3000 * level) if level != 7 else H.gen_vm_like(size, seed=47))
     hidx, cb = H.hash_index(), H.chunk_bytes(data.size)
-    vs = mrz_py.VariantSet(0, data.size, chain)
+    vs = mrz_py.VariantSet(0, data.size, chain, **config)
     try:
         vs.upload(data)
         for _ in range(reps):                       # contexts are reusable
@@ -140,28 +141,47 @@ CASE_IDS = ["L7-vm-16var", "L1-motif-2var", "L8-motif-32var"]
 
 
 @pytest.mark.parametrize("level,size", CASES, ids=CASE_IDS)
-def test_variant_chunk(level, size, monkeypatch):
-    """mrz_run_variants (include/mrz_gpu.h), default form: the variants of one resident chunk one after another."""
-    monkeypatch.delenv("MRZ_VARIANTS_CONCURRENT", raising=False)
-    _variant_case(level, size, reps=1)
+def test_variant_chunk(level, size):
+    """mrz_run_variants (include/mrz_gpu.h): all variants of one resident chunk side by side in one launch, in process."""
+    _variant_case(level, size, reps=2, poison=1)
 
 
-@pytest.mark.parametrize("level,size", CASES, ids=CASE_IDS)
-def test_variant_chunk_side_by_side(level, size):
-    """The same with MRZ_VARIANTS_CONCURRENT=1 (one CTA + table per variant, all at once).  Experimental: it has ended
-    in a device fault / hang inside bench.py's process, so the case runs in a child process under a
-    timeout and an abnormal end is reported as xfail; a WRONG RESULT still fails the test."""
-    import os
-    import subprocess
-    import sys
-    code = "import sys; sys.path[:0] = [%r, %r]; import test_gpu_parity as t; t._variant_case(%d, %d); print('VARIANT-CASE-OK')" % (
-        os.path.dirname(os.path.abspath(__file__)), os.path.join(H.ROOT, "modern-rzip_b200"), level, size)
-    env = dict(os.environ, MRZ_VARIANTS_CONCURRENT="1")
+@pytest.mark.parametrize("config", [dict(cluster_size=1, threads=512), dict(cluster_size=2, threads=256), dict(cluster_size=8, threads=128),
+                                    dict(cluster_size=16, threads=64), dict(cluster_size=16, threads=512),
+                                    dict(cluster_size=4, threads=256, filter_log2_words=12)],
+                         ids=["1x512", "2x256", "8x128", "16x64", "16x512", "4x256-tiny-filter"])
+def test_cluster_geometries(config):
+    """The same automaton under other launch geometries (mrz_config): one CTA, small and the largest clusters; a tiny
+    tag filter makes almost every op take the exact executor."""
+    import mrz_py
+    ctx = mrz_py.Context(0, 1 << 26, poison=1, **config)
     try:
-        p = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=420)
-    except subprocess.TimeoutExpired:
-        pytest.xfail("side-by-side variants hung (open issue, DESIGN.md §6)")
-    if "AssertionError" in p.stderr:
-        pytest.fail("side-by-side variants produced a wrong result:\n" + p.stderr[-2000:])
-    if p.returncode != 0 or "VARIANT-CASE-OK" not in p.stdout:
-        pytest.xfail("side-by-side variants ended abnormally (open issue, DESIGN.md §6): " + p.stderr[-300:])
+        check(ctx, H.gen_random_repeats(8 << 20, 60))
+        check(ctx, H.gen_motif(3 << 20, 3000), level=1)
+        check(ctx, H.gen_vm_like(16 << 20))
+        check(ctx, H.gen_random(32 << 20), level=4)
+        check(ctx, H.gen_dense(8 << 20), level=9)
+    finally:
+        ctx.close()
+
+
+def test_tagmap_matches_prefix_xor(gpu_ctx):
+    """tagmap.cu against an independent restatement: tag[p] = X[p+31] ^ X[p] over a prefix-XOR of hash_index[buf[i]]."""
+    data = H.gen_random((3 << 20) + 12345, seed=78)
+    hidx = H.hash_index()
+    gpu_ctx.upload(data)
+    bmap, bsum = gpu_ctx.debug_tagmap(data.size, hidx)
+    h = hidx[data]
+    x = np.concatenate([[0], np.bitwise_xor.accumulate(h)])
+    tags = x[31:] ^ x[:-31]
+    tz = np.zeros(tags.size, dtype=np.int64)
+    t = tags.copy()
+    for i in range(48):
+        tz += ((t & 1) == 1) & (tz == i)
+        t >>= 1
+    want = np.zeros(data.size, dtype=np.uint8)
+    want[:tags.size] = tz
+    assert np.array_equal(bmap, want)
+    ws = np.zeros((data.size + 63) // 64 * 64, dtype=np.uint8)
+    ws[:data.size] = want
+    assert np.array_equal(bsum, ws.reshape(-1, 64).max(axis=1))

@@ -56,29 +56,21 @@ def test_degenerate(sim_ctx):
     check(sim_ctx, np.tile(H.gen_random(4099, seed=9), 100))
 
 
-def _ctx_with_env(env):
-    """A separate emulator context created under the given environment (the geometry is read at context creation)."""
+def _sim_ctx(**config):
+    """A separate emulator context with its own launch geometry (mrz_config)."""
     import os
     import mrz_py
-    old = {k: os.environ.get(k) for k in env}
-    os.environ.update(env)
-    try:
-        lib = mrz_py.bind(os.path.join(os.path.dirname(os.path.abspath(__file__)), "cusim", "libmrz_sim.so"))
-        return mrz_py.Context(0, 1 << 24, library=lib)
-    finally:
-        for k, v in old.items():
-            if v is None:
-                os.environ.pop(k, None)
-            else:
-                os.environ[k] = v
+    lib = mrz_py.bind(os.path.join(os.path.dirname(os.path.abspath(__file__)), "cusim", "libmrz_sim.so"))
+    return mrz_py.Context(0, 1 << 24, library=lib, poison=1, **config)
 
 
-@pytest.mark.parametrize("env", [{"MRZ_HELPERS": "2"}, {"MRZ_AUTOMATON": "grid", "MRZ_G": "5", "MRZ_T": "64"}],
-                         ids=["plan-offload-2-helpers", "grid-automaton"])
-def test_other_automaton_geometries(sim_ctx, env):
-    """Plan offload to helper CTAs (cooperative launch) and the multi-CTA grid automaton, on inputs with matches,
-    sweeps, victims and twins."""
-    ctx = _ctx_with_env(env)
+@pytest.mark.parametrize("config", [dict(cluster_size=1, threads=128), dict(cluster_size=4, threads=32), dict(cluster_size=8, threads=32),
+                                    dict(cluster_size=2, threads=64, filter_log2_words=10)],
+                         ids=["1x128", "4x32", "8x32", "2x64-tiny-filter"])
+def test_other_cluster_geometries(sim_ctx, config):
+    """One CTA, and clusters of 4 and 8 CTAs, on inputs with matches, sweeps, victims and twins; a tiny tag filter
+    (many false positives: every such op takes the exact executor)."""
+    ctx = _sim_ctx(**config)
     try:
         check(ctx, H.gen_random_repeats(2 << 20, 30, lo=2048, hi=65536))
         check(ctx, H.gen_motif(1 << 20, 2000), level=1)
