@@ -81,15 +81,15 @@ __device__ __forceinline__ unsigned claim_key(unsigned epoch, int j, int is_w1) 
 
 // ---- range checks of the -DMRZ_CHECK build: a violation records (site, index, bound) and clamps the index ----
 #ifdef MRZ_CHECK
-#define CHK(sh, site, idx, bound)                                                                    \
+#define CHK(sh, x, site, idx, bound)                                                                 \
     do {                                                                                             \
         if ((i64)(idx) < 0 || (i64)(idx) >= (i64)(bound)) {                                          \
-            (sh)->run.error = 100 + (site); (sh)->err_a = (i64)(idx); (sh)->err_b = (i64)(bound);    \
+            (sh)->err_a = (i64)(idx); (sh)->err_b = (i64)(bound); __stcg(&(sh)->err_site, 100 + (site)); \
             (idx) = 0;                                                                               \
         }                                                                                            \
     } while (0)
 #else
-#define CHK(sh, site, idx, bound) do { } while (0)
+#define CHK(sh, x, site, idx, bound) do { } while (0)
 #endif
 
 // Blocked Bloom filter over inserted tags: word index and 3-bit mask (oracle/spec_model.c filt_hash).
@@ -130,6 +130,15 @@ __device__ __forceinline__ void sum_lower(u32 *gs, i64 g, int v) {      // commi
 }
 
 // ---- cluster plumbing ----------------------------------------------------------------------------
+// The CTAs of a cluster share nothing through global memory that is hot: every CTA keeps a REPLICA of the
+// automaton's scalar state in its own shared memory.  A replica changes in one of two ways only: (1) every CTA
+// applies the same deterministic update from the same inputs (commit, gather, ring refill), or (2) the one CTA that
+// ran the exact executor PUSHES the result into every replica through distributed shared memory before the next
+// cluster barrier (remote stores are fire-and-forget; the readers then read their own shared memory, ~30 clk,
+// instead of L2, ~375 clk, or a volatile global load, ~745 clk: profiles/r2_micro_lat.txt).  Per-rank values that
+// everybody needs (scan totals, local minima) are pushed by each rank into slot [rank] of every replica.  A slot
+// that is rewritten in CONSECUTIVE barrier intervals is double-buffered: a CTA that has passed barrier k may write
+// before a slower CTA has read what it received before barrier k.
 #ifdef MRZ_CUSIM
 __device__ __forceinline__ int cl_rank() { return cusim::cluster_rank(); }
 __device__ __forceinline__ int cl_size() { return cusim::cluster_size(); }
@@ -138,15 +147,26 @@ __device__ __forceinline__ void csync(int) {
     if (threadIdx.x == 0) cusim::sync_cluster();
     __syncthreads();
 }
+template <class T> __device__ __forceinline__ T *remote_ptr(T *p, int r) { return reinterpret_cast<T *>(cusim::map_shared_rank((void *)p, r)); }
+__device__ __forceinline__ void prefetch_l2(const void *) {}
 #else
 __device__ __forceinline__ int cl_rank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return (int)r; }
 __device__ __forceinline__ int cl_size() { unsigned r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return (int)r; }
-// Barrier over all threads of the cluster; orders their global-memory accesses (release / acquire at cluster scope).
+// Barrier over all threads of the cluster; orders their global and (distributed) shared memory accesses.
 __device__ __forceinline__ void csync(int CL) {
     if (CL == 1) { __syncthreads(); return; }
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// generic address of the same shared-memory object in the CTA of rank r
+template <class T> __device__ __forceinline__ T *remote_ptr(T *p, int r) {
+    u64 out;
+    asm volatile("mapa.u64 %0, %1, %2;" : "=l"(out) : "l"((u64)(uintptr_t)p), "r"(r));
+    return reinterpret_cast<T *>((uintptr_t)out);
+}
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 #endif
+// store v into slot *p of the replica of rank r
+template <class T> __device__ __forceinline__ void push_to(T *p, int r, T v) { *(volatile T *)remote_ptr(p, r) = v; }
 
 // Running state of the automaton (rzip_state, mrzip_private.h:388-416).
 struct Run {
@@ -155,31 +175,39 @@ struct Run {
     int error, pad;
 };
 
-#define NSITE 6   // cluster-wide prefix sums per batch, each with its own exchange array
-// State shared by the CTAs of one automaton, in global memory (L2).  One writer per field between two barriers.
-struct Shared {
+#define NSITE 4   // cluster-wide prefix sums per batch, each with its own exchange slots
+// What the exact executor (rank 0) changes; pushed as one block of words into every replica.
+struct XRes {
     Run run;
-    i64 err_a, err_b;
     i64 gp;                  // gather cursor: every position < gp has been gathered or skipped
-    i64 gp_next;             // atomicMin target while a batch is gathered
     i64 e_scan;              // slots in [run.clean_ptr, e_scan) have been examined for the ring
     unsigned e_idx, e_cnt;   // ring counters (monotonic)
-    int nr;                  // ops in the current batch
-    int exhausted;           // the gather reached the end of the chunk
-    int pos, ended, jumped, nlog;
-    int changed[2];
-    int qcut;                // atomicMin: smallest queued slot that a committed plan overwrote (0x7fffffff: none)
-    int pad0;
-    unsigned long long kcut; // cut search: min over (~round << 32 | op index << 1 | needs the exact executor)
-    unsigned long long tot[NSITE][MRZ_MAXCL];
-    int wlog[MRZ_WLOG_CAP];
+    int ended, jumped, nlog, pos_after;
+    int wlog[MRZ_WLOG_CAP];  // (slot << 1) | zeroed
+};
+// Replica of the automaton's scalars, one per CTA, in shared memory.
+struct Rep {
+    XRes x;
+    int exhausted, pad;
+    unsigned long long tot[NSITE][MRZ_MAXCL];   // scan totals of rank r
+    unsigned long long lcut[2][MRZ_MAXCL];      // first op of rank r that cannot commit from its plan: idx << 1 | exact (0x7fffffff: none)
+    unsigned long long lcutpre[MRZ_MAXCL];      // ... and the prefix sum over the ops of rank r before it
+    i64 xmin[MRZ_MAXCL];                        // gather: first candidate of rank r that did not fit the batch
+    int qmin[MRZ_MAXCL];                        // commit: smallest ring slot a plan of rank r overwrote
+    unsigned chg[2][MRZ_MAXCL];                 // conflict phase: epoch for which rank r reported a change (double-buffered by iteration)
+};
+
+// Per-op arrays and the sweep ring, in global memory (L2); read with ld.cg, one writer per element between barriers.
+struct Shared {
+    i64 err_a, err_b;
+    int err_site, pad;       // MRZ_CHECK build: site of a failed range check (polled by every CTA)
     int E[MRZ_EQ_CAP];       // ring of eligible slots, ascending
     i64 b_pos[MRZ_MAXB], b_tag[MRZ_MAXB];   // batch: position / tag of op j
     int pl_fl[MRZ_MAXB], pl_w2[MRZ_MAXB];   // plan flags / insert slot of op j (twins, commit)
     unsigned long long pre[MRZ_MAXB];       // inclusive prefix over ops holding a valid plan
-    i64 blk[MRZ_MAXB];       // gather: non-empty 64-position blocks
 };
-typedef volatile Shared VS;
+#define LDG_(x) __ldcg(&(x))
+#define STG_(x, v) __stcg(&(x), (v))
 
 #define PK_D(x) ((unsigned)((x) & 0xffffu))            // hash_count delta
 #define PK_I(x) ((unsigned)(((x) >> 16) & 0xffffu))    // inserts
@@ -190,15 +218,16 @@ extern "C" size_t mrz_shared_bytes() { return sizeof(Shared); }
 
 // ---- shared memory of a CTA ----------------------------------------------------------------------
 struct Smem {
+    Rep rep;
     i64 hx[256];
     i64 stk[3 * 64];
     unsigned long long wsum[40];
     unsigned long long cbase, ctotal;
-    int lk_fe, lk_n, red, pad;
+    i64 lgp;                // CTA-local minimum for xmin
+    int lk_fe, lk_n, lmin, lq, lchg, pad;
     int lk_pos[LK_CAP];     // CTA-wide lookup: positions (relative to the primary slot) of equal tags, ascending
     i64 lk_len[LK_CAP], lk_rev[LK_CAP], lk_off[LK_CAP];   // match_len results per candidate
     i64 lk_f[LK_CAP], lk_r[LK_CAP];                       // capped forward / backward lengths (first pass)
-    int wlog[MRZ_WLOG_CAP];
 };
 extern "C" size_t mrz_automaton_smem_bytes() { return sizeof(Smem); }
 
@@ -208,7 +237,7 @@ extern "C" size_t mrz_automaton_smem_bytes() { return sizeof(Smem); }
 #define MRZ_SMEM_PTR(T, name) extern __shared__ __align__(16) unsigned char name##_raw[]; T *name = reinterpret_cast<T *>(name##_raw)
 #endif
 
-// exclusive prefix sum of v over the CTA (thread order); total in `total`.  Two block barriers.
+// exclusive prefix sum of v over the CTA (thread order); total in `total`.  Three block barriers.
 __device__ __forceinline__ unsigned long long block_excl_scan(unsigned long long v, unsigned long long *wsum, unsigned long long &total) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
     unsigned long long inc = v;
@@ -234,17 +263,21 @@ __device__ __forceinline__ unsigned long long block_excl_scan(unsigned long long
     return r;
 }
 
-// exclusive prefix sum of v over the CLUSTER (rank-major, then thread order); total in `total`.  One cluster barrier.
-__device__ __forceinline__ unsigned long long cluster_excl_scan(unsigned long long v, Smem *S, VS *sh, int site, int CL, int rank,
-                                                                unsigned long long &total) {
+// exclusive prefix sum of v over the CLUSTER (rank-major, then thread order); total in `total`.  ONE cluster barrier:
+// every rank pushes its total into slot [rank] of every replica, then sums the slots below its own.
+// `extra(ex)` is called by all threads between the push and the barrier, with the thread's exclusive prefix inside
+// its CTA: whatever else has to cross the cluster in the same hop.
+template <class F>
+__device__ __forceinline__ unsigned long long cluster_excl_scan(unsigned long long v, Smem *S, int site, int CL, int rank,
+                                                                unsigned long long &total, F extra) {
     unsigned long long btot;
     const unsigned long long ex = block_excl_scan(v, S->wsum, btot);
-    if (CL == 1) { total = btot; return ex; }
-    if (threadIdx.x == 0) sh->tot[site][rank] = btot;
+    if ((int)threadIdx.x < CL) push_to(&S->rep.tot[site][rank], (int)threadIdx.x, btot);
+    extra(ex);
     csync(CL);
     if (threadIdx.x < 32) {
         const int lane = threadIdx.x;
-        const unsigned long long t = lane < CL ? sh->tot[site][lane] : 0ULL;
+        const unsigned long long t = lane < CL ? S->rep.tot[site][lane] : 0ULL;
         unsigned long long below = lane < rank ? t : 0ULL, all = t;
         for (int o = 16; o; o >>= 1) { below += __shfl_xor_sync(FULL, below, o); all += __shfl_xor_sync(FULL, all, o); }
         if (lane == 0) { S->cbase = below; S->ctotal = all; }
@@ -255,6 +288,7 @@ __device__ __forceinline__ unsigned long long cluster_excl_scan(unsigned long lo
     __syncthreads();
     return r;
 }
+struct NoExtra { __device__ __forceinline__ void operator()(unsigned long long) const {} };
 
 // ---- the exact executor: one warp runs one op on the live table with the reference semantics -----
 struct Warp {
@@ -276,20 +310,21 @@ struct Warp {
     i64 clean_hint;   // no eligible slot exists in [clean_ptr, clean_hint)
     i64 *prof;        // profile build: cycles / calls of the parts of a serial op
 
-    __device__ __forceinline__ void load(VS *sh) {
-        p = sh->run.p; last = sh->run.last; cur_p = sh->run.cur_p; cur_len = sh->run.cur_len; cur_ofs = sh->run.cur_ofs;
-        min_mask = sh->run.min_mask; ins_mask = sh->run.ins_mask; clean_ptr = sh->run.clean_ptr; count = sh->run.count; vr = sh->run.vr;
-        hits = sh->run.hits; misses = sh->run.misses; inserts = sh->run.inserts; vevents = sh->run.vevents; nops = sh->run.nops;
-        ntok = sh->run.ntok; error = sh->run.error;
+    __device__ __forceinline__ void load(const Run &r) {
+        p = r.p; last = r.last; cur_p = r.cur_p; cur_len = r.cur_len; cur_ofs = r.cur_ofs;
+        min_mask = r.min_mask; ins_mask = r.ins_mask; clean_ptr = r.clean_ptr; count = r.count; vr = r.vr;
+        hits = r.hits; misses = r.misses; inserts = r.inserts; vevents = r.vevents; nops = r.nops; ntok = r.ntok;
+        error = r.error;
+        __syncwarp();   // every lane holds the state before lane 0 may store the next one
     }
-    __device__ __forceinline__ void store(VS *sh) const {
+    __device__ __forceinline__ void store(Run &r) const {
         if (lane == 0) {
-            sh->run.p = p; sh->run.last = last; sh->run.cur_p = cur_p; sh->run.cur_len = cur_len; sh->run.cur_ofs = cur_ofs;
-            sh->run.min_mask = min_mask; sh->run.ins_mask = ins_mask; sh->run.clean_ptr = clean_ptr; sh->run.count = count; sh->run.vr = vr;
-            sh->run.hits = hits; sh->run.misses = misses; sh->run.inserts = inserts; sh->run.vevents = vevents; sh->run.nops = nops;
-            sh->run.ntok = ntok;
-            if (error) sh->run.error = error;
+            r.p = p; r.last = last; r.cur_p = cur_p; r.cur_len = cur_len; r.cur_ofs = cur_ofs;
+            r.min_mask = min_mask; r.ins_mask = ins_mask; r.clean_ptr = clean_ptr; r.count = count; r.vr = vr;
+            r.hits = hits; r.misses = misses; r.inserts = inserts; r.vevents = vevents; r.nops = nops; r.ntok = ntok;
+            if (error) r.error = error;
         }
+        __syncwarp();
     }
     // table writes of the serial path: lane 0 stores, the write is logged, the summary follows
     __device__ __forceinline__ void write_slot(i64 slot, i64 off, i64 tag) {
@@ -811,13 +846,13 @@ __device__ __forceinline__ void plan_follower(Plan &r, const i64 *ttag, u32 *gsu
 
 // Refill the ring of eligible slots (those clean_one_from_hash will zero next, in order) by a parallel scan of the
 // table from e_scan, eight slots (one 64-byte line) per thread of the cluster; only meaningful once
-// ins_mask == 2*min_mask+1.  The scan never goes past scan_end.  Every thread of the cluster calls it.
-__device__ __forceinline__ void refill_queue(VS *sh, Smem *S, const i64 *ttag, i64 btm, i64 scan_end, int want, int CL, int rank, int j, int B) {
-    for (;;) {
-        csync(CL);
-        const unsigned e_cnt = sh->e_cnt;
-        const int avail = (int)(e_cnt - sh->e_idx);
-        const i64 scan = sh->e_scan;
+// ins_mask == 2*min_mask+1.  The scan never goes past scan_end.  Every thread of the cluster calls it; every CTA
+// updates its own replica of the ring counters identically.  One cluster barrier per iteration.
+__device__ __forceinline__ void refill_queue(Shared *sh, Smem *S, const i64 *ttag, i64 btm, i64 scan_end, int want, int CL, int rank, int j, int B) {
+    for (int iter = 0;; iter++) {
+        const unsigned e_cnt = S->rep.x.e_cnt;
+        const int avail = (int)(e_cnt - S->rep.x.e_idx);
+        const i64 scan = S->rep.x.e_scan;
         if (avail >= want || scan >= scan_end || avail + 8 * B > MRZ_EQ_CAP) break;
         const i64 base = scan & ~(i64)7;
         const i64 s0 = base + 8 * (i64)j;
@@ -832,33 +867,79 @@ __device__ __forceinline__ void refill_queue(VS *sh, Smem *S, const i64 *ttag, i
             }
         }
         unsigned long long total;
-        const unsigned long long ex = cluster_excl_scan((unsigned long long)__popc(m), S, sh, 0, CL, rank, total);
+        // (sites 0 and 3 alternate: a CTA that is already in the next iteration must not overwrite totals a slower one still reads)
+        const unsigned long long ex = cluster_excl_scan((unsigned long long)__popc(m), S, (iter & 1) ? 3 : 0, CL, rank, total, NoExtra());
         unsigned at = e_cnt + (unsigned)ex;
         for (int q = 0; q < 8; q++)
-            if ((m >> q) & 1u) sh->E[at++ & (MRZ_EQ_CAP - 1)] = (int)(s0 + q);
-        if (j == 0) {
-            sh->e_cnt = e_cnt + (unsigned)total;
+            if ((m >> q) & 1u) STG_(sh->E[at++ & (MRZ_EQ_CAP - 1)], (int)(s0 + q));
+        if (threadIdx.x == 0) {
+            S->rep.x.e_cnt = e_cnt + (unsigned)total;
             const i64 ns = base + 8 * (i64)B;
-            sh->e_scan = ns < scan_end ? ns : scan_end;
+            S->rep.x.e_scan = ns < scan_end ? ns : scan_end;
+        }
+        __syncthreads();
+    }
+}
+
+// After a serial op (one thread of rank 0): bring the ring back in step with what the op wrote.
+__device__ __forceinline__ void sync_queue(Shared *sh, XRes *x, const int *wlog, int nlog) {
+    for (int w = 0; w < nlog; w++) {
+        const int sl = wlog[w] >> 1;
+        if (wlog[w] & 1) {                       // zeroed by clean_one: consume the ring up to it
+            while (x->e_idx != x->e_cnt && LDG_(sh->E[x->e_idx & (MRZ_EQ_CAP - 1)]) <= sl) x->e_idx++;
+        } else if (sl < x->e_scan) {             // overwritten by an insert: if queued, cut the ring there
+            unsigned a = x->e_idx, b = x->e_cnt;
+            while (a != b) {
+                const unsigned m = a + (b - a) / 2;
+                if (LDG_(sh->E[m & (MRZ_EQ_CAP - 1)]) < sl) a = m + 1; else b = m;
+            }
+            if (a != x->e_cnt && LDG_(sh->E[a & (MRZ_EQ_CAP - 1)]) == sl) { x->e_cnt = a; x->e_scan = sl; }
         }
     }
 }
 
-// After a serial op (one thread): bring the ring back in step with what the op wrote.
-__device__ __forceinline__ void sync_queue(VS *sh, const int *wlog, int nlog) {
-    for (int w = 0; w < nlog; w++) {
-        const int sl = wlog[w] >> 1;
-        if (wlog[w] & 1) {                       // zeroed by clean_one: consume the ring up to it
-            while (sh->e_idx != sh->e_cnt && sh->E[sh->e_idx & (MRZ_EQ_CAP - 1)] <= sl) sh->e_idx = sh->e_idx + 1;
-        } else if (sl < sh->e_scan) {            // overwritten by an insert: if queued, cut the ring there
-            unsigned a = sh->e_idx, b = sh->e_cnt;
-            while (a != b) {
-                const unsigned m = a + (b - a) / 2;
-                if (sh->E[m & (MRZ_EQ_CAP - 1)] < sl) a = m + 1; else b = m;
-            }
-            if (a != sh->e_cnt && sh->E[a & (MRZ_EQ_CAP - 1)] == sl) { sh->e_cnt = a; sh->e_scan = sl; }
+// First ring index in [a, b) whose slot is >= key (b if none); 32-ary search by one warp over the ring in global memory.
+__device__ __forceinline__ unsigned ring_lower_bound(const Shared *sh, unsigned a, unsigned b, int key, int lane) {
+    while (b - a > 32) {
+        const unsigned len = b - a;
+        const unsigned idx = a + (unsigned)(((unsigned long long)len * lane) / 32);
+        const int v = LDG_(sh->E[idx & (MRZ_EQ_CAP - 1)]);
+        const unsigned ge = __ballot_sync(FULL, v >= key);
+        if (!ge) a = a + (unsigned)(((unsigned long long)len * 31) / 32) + 1;
+        else {
+            const int l = __ffs(ge) - 1;
+            if (l == 0) return a;
+            const unsigned na = a + (unsigned)(((unsigned long long)len * (l - 1)) / 32) + 1;
+            b = a + (unsigned)(((unsigned long long)len * l) / 32) + 1;
+            a = na;
         }
     }
+    const bool in = a + lane < b;
+    const int v = in ? LDG_(sh->E[(a + lane) & (MRZ_EQ_CAP - 1)]) : 0x7fffffff;
+    const unsigned ge = __ballot_sync(FULL, in && v >= key);
+    return ge ? a + (__ffs(ge) - 1) : b;
+}
+
+// First op index in [a, b) whose position is > p (b if none); 32-ary search by one warp over b_pos in global memory.
+__device__ __forceinline__ int pos_upper_bound(const Shared *sh, int a, int b, i64 p, int lane) {
+    while (b - a > 32) {
+        const int len = b - a;
+        const int idx = a + (len * lane) / 32;
+        const i64 v = LDG_(sh->b_pos[idx]);
+        const unsigned gt = __ballot_sync(FULL, v > p);
+        if (!gt) a = a + (len * 31) / 32 + 1;
+        else {
+            const int l = __ffs(gt) - 1;
+            if (l == 0) return a;
+            const int na = a + (len * (l - 1)) / 32 + 1;
+            b = a + (len * l) / 32 + 1;
+            a = na;
+        }
+    }
+    const bool in = a + lane < b;
+    const i64 v = in ? LDG_(sh->b_pos[a + lane]) : 0;
+    const unsigned gt = __ballot_sync(FULL, in && v > p);
+    return gt ? a + (__ffs(gt) - 1) : b;
 }
 
 // Match extension by the whole CTA: longest common prefix of buf[a0..] / buf[b0..] (fwd) or longest common suffix of
@@ -928,6 +1009,68 @@ __device__ __forceinline__ unsigned ge_nibble(u32 w, u32 k4) {
     return (((x >> 7) * 0x01020408u) >> 24) & 0xfu;
 }
 
+// Candidates (map byte >= kgate) of the span [a, a + s) of positions, s a power of two, in ascending order, restricted
+// to [lo, end]; f(pos) returns false to stop.  s <= 64: the map bytes are read directly; s > 64: the 64:1 summary
+// first, then the map bytes of the non-empty blocks only.
+template <class F>
+__device__ __forceinline__ void span_candidates(const u8 *__restrict__ bmap, const u8 *__restrict__ bsum, i64 a, int s, int kgate, i64 lo,
+                                                i64 end, i64 nblocks, F f) {
+    if (a > end || a + s <= lo) return;
+    const u32 k4 = (u32)kgate * 0x01010101u;
+    if (s <= 64) {
+        const i64 v0 = a & ~(i64)15;
+        const int nvec = s <= 16 ? 1 : s >> 4;
+        u64 m = 0;
+        for (int q = 0; q < nvec; q++) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(bmap + v0) + q);
+            const u64 m16 = (u64)(ge_nibble(v.x, k4) | (ge_nibble(v.y, k4) << 4) | (ge_nibble(v.z, k4) << 8) | (ge_nibble(v.w, k4) << 12));
+            m |= m16 << (16 * q);
+        }
+        if (s < 16) m &= (((u64)1 << s) - 1) << (int)(a - v0);
+        if (v0 < lo) m &= ~(((u64)1 << (int)(lo - v0)) - 1);            // lo - v0 < 64 here
+        if (v0 + 63 > end) m &= (((u64)1 << (int)(end - v0)) << 1) - 1;   // end - v0 in 0..62
+        while (m) {
+            const int b = __ffsll((long long)m) - 1;
+            m &= m - 1;
+            if (!f(v0 + b)) return;
+        }
+        return;
+    }
+    const i64 blk0 = a >> MAP_BLK_SHIFT, blk_lo = lo >> MAP_BLK_SHIFT;
+    const int nb = s >> MAP_BLK_SHIFT;                 // blocks in the span: 2, 4, ... 1024
+    const i64 vb0 = blk0 & ~(i64)15;
+    const int nvec = nb <= 16 ? 1 : nb >> 4;
+    for (int q = 0; q < nvec; q++) {
+        const i64 bq = vb0 + 16 * q;
+        if (bq >= nblocks) return;
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(bsum + bq));
+        unsigned m = ge_nibble(v.x, k4) | (ge_nibble(v.y, k4) << 4) | (ge_nibble(v.z, k4) << 8) | (ge_nibble(v.w, k4) << 12);
+        if (nb < 16) m &= ((1u << nb) - 1u) << (int)(blk0 - vb0);
+        if (bq < blk_lo) m &= (blk_lo - bq >= 16) ? 0u : ~((1u << (int)(blk_lo - bq)) - 1u);
+        if (bq + 16 > nblocks) m &= (1u << (int)(nblocks - bq)) - 1u;
+        while (m) {
+            const int bb = __ffs(m) - 1;
+            m &= m - 1;
+            const i64 p0 = (bq + bb) << MAP_BLK_SHIFT;
+            const uint4 *src = reinterpret_cast<const uint4 *>(bmap + p0);
+            u64 cm = 0;
+#pragma unroll
+            for (int w = 0; w < 4; w++) {
+                const uint4 x = __ldg(src + w);
+                const u64 m16 = (u64)(ge_nibble(x.x, k4) | (ge_nibble(x.y, k4) << 4) | (ge_nibble(x.z, k4) << 8) | (ge_nibble(x.w, k4) << 12));
+                cm |= m16 << (16 * w);
+            }
+            if (p0 < lo) cm &= ~(((u64)1 << (int)(lo - p0)) - 1);
+            if (p0 + 63 > end) cm &= (((u64)1 << (int)(end - p0)) << 1) - 1;
+            while (cm) {
+                const int b = __ffsll((long long)cm) - 1;
+                cm &= cm - 1;
+                if (!f(p0 + b)) return;
+            }
+        }
+    }
+}
+
 // ---- the kernel -----------------------------------------------------------------------------------
 // Cluster c of the grid runs automaton c: descs[c].  Persistent: returns when the chunk is done (or on error).
 __global__ void __launch_bounds__(MRZ_MAXT, 1)
@@ -937,13 +1080,16 @@ k_automaton(const AutoDesc *__restrict__ descs) {
     AutoState *st = D.st;
     if (st->done || st->error) return;
     MRZ_SMEM_PTR(Smem, S);
-    VS *sh = D.sh;
+    Shared *sh = D.sh;
+    XRes &x = S->rep.x;
     const u8 *__restrict__ buf = D.buf;
     const u8 *__restrict__ bmap = D.bmap;
     const u8 *__restrict__ bsum = D.bsum;
     i64 *ttag = D.ttag, *toff = D.toff;
     u32 *gsum = D.gsum;
-    unsigned *claim = D.claim;
+    // two claim arrays, used alternately (epoch parity): the claims of the NEXT epoch are made while the ones of the current
+    // epoch are still being read, and must not disturb them
+    unsigned *const claim0 = D.claim, *const claim1 = D.claim + D.claim_stride;
     i64 *dbg = D.dbg;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, T = blockDim.x;
     const int B = CL * T, j = rank * T + tid;
@@ -953,168 +1099,98 @@ k_automaton(const AutoDesc *__restrict__ descs) {
     const i64 n = st->n, end = st->end, hmask = st->hmask, hsize = st->hsize, limit = st->limit;
     const int chain = st->chain;
     const i64 nblocks = (end >> MAP_BLK_SHIFT) + 1;          // 64-position blocks that hold a position <= end
-    (void)n;
-    if (j == 0) {
-        sh->run.p = st->p; sh->run.last = st->last; sh->run.cur_p = st->cur_p; sh->run.cur_len = st->cur_len; sh->run.cur_ofs = st->cur_ofs;
-        sh->run.min_mask = st->min_mask; sh->run.ins_mask = st->ins_mask; sh->run.clean_ptr = st->clean_ptr; sh->run.count = st->count;
-        sh->run.vr = st->victim_round;
-        sh->run.hits = st->tag_hits; sh->run.misses = st->tag_misses; sh->run.inserts = st->inserts; sh->run.vevents = st->victim_events;
-        sh->run.nops = st->n_ops; sh->run.ntok = st->ntok; sh->run.error = 0;
-        sh->err_a = sh->err_b = 0;
-        sh->e_idx = sh->e_cnt = 0; sh->e_scan = st->clean_ptr;
-        sh->gp = st->p + 1; sh->exhausted = 0;
-        sh->changed[0] = sh->changed[1] = 0;
-        sh->kcut = ~0ULL; sh->qcut = 0x7fffffff;
+    if (tid == 0) {                                          // every CTA builds the same replica
+        x.run.p = st->p; x.run.last = st->last; x.run.cur_p = st->cur_p; x.run.cur_len = st->cur_len; x.run.cur_ofs = st->cur_ofs;
+        x.run.min_mask = st->min_mask; x.run.ins_mask = st->ins_mask; x.run.clean_ptr = st->clean_ptr; x.run.count = st->count;
+        x.run.vr = st->victim_round;
+        x.run.hits = st->tag_hits; x.run.misses = st->tag_misses; x.run.inserts = st->inserts; x.run.vevents = st->victim_events;
+        x.run.nops = st->n_ops; x.run.ntok = st->ntok; x.run.error = 0; x.run.pad = 0;
+        x.gp = st->p + 1; x.e_idx = x.e_cnt = 0; x.e_scan = st->clean_ptr;
+        x.ended = x.jumped = x.nlog = x.pos_after = 0;
+        S->rep.exhausted = 0;
+        for (int r = 0; r < MRZ_MAXCL; r++) S->rep.chg[0][r] = S->rep.chg[1][r] = 0xffffffffu;
     }
     Warp w;   // used by warp 0 of rank 0 only
     w.buf = buf; w.ttag = ttag; w.toff = toff; w.filt = filt; w.gsum = gsum; w.toks = D.toks; w.lane = lane;
     w.n = n; w.end = end; w.hmask = hmask; w.hsize = hsize; w.limit = limit; w.tok_cap = st->tok_cap; w.chain = chain;
-    w.wlog = S->wlog; w.nlog = 0; w.clean_hint = 0; w.prof = dbg ? dbg + 40 : nullptr;
+    w.wlog = x.wlog; w.nlog = 0; w.clean_hint = 0; w.prof = dbg ? dbg + 40 : nullptr;
+    if (j == 0) { sh->err_a = sh->err_b = 0; STG_(sh->err_site, 0); }
     unsigned epoch = 0;      // claim epoch: uniform over the cluster (every thread advances it identically)
-    unsigned round = 0;      // cut-search round, uniform
-    i64 tm[16];
+    i64 tm[12];
 #pragma unroll
-    for (int q = 0; q < 16; q++) tm[q] = 0;
+    for (int q = 0; q < 12; q++) tm[q] = 0;
     i64 t_prev = clock64();
 #define TICK(slot) do { if (dbg) { const i64 t_now = clock64(); tm[slot] += t_now - t_prev; t_prev = t_now; } } while (0)
-    csync(CL);   // the host has filled claim[] with 0xff: every key compares greater than any live one
+    csync(CL);   // replicas are built; the host has filled claim[] with 0xff: every key compares greater than any live one
 
     for (;;) {
-        // ================================================================ batch set-up (uniform reads)
-        if (sh->run.error || sh->exhausted) break;
-        const i64 min_mask = sh->run.min_mask, ins_mask = sh->run.ins_mask;
+        // ================================================================ batch set-up (every CTA reads its own replica)
+#ifdef MRZ_CHECK
+        if (LDG_(sh->err_site)) { if (tid == 0) x.run.error = LDG_(sh->err_site); __syncthreads(); }
+#endif
+        if (x.run.error || S->rep.exhausted) break;
+        const i64 min_mask = x.run.min_mask, ins_mask = x.run.ins_mask;
         const i64 btm = (min_mask << 1) | 1;
         const bool steady = ins_mask == btm;   // inserts can no longer create sweep-eligible entries
-        const i64 p_now = sh->run.p, last_now = sh->run.last, clean0 = sh->run.clean_ptr;
+        const i64 p_now = x.run.p, last_now = x.run.last;
         const int kgate = __popcll((u64)min_mask);
-        const i64 gp0 = sh->gp;
+        const i64 gp0 = x.gp;
         const i64 lo = gp0 > p_now + 1 ? gp0 : p_now + 1;
         if (lo > end) {                        // every position up to `end` has been examined or jumped over (rzip.c:548)
-            csync(CL);
-            if (j == 0) sh->exhausted = 1;
-            csync(CL);
+            __syncthreads();
+            if (tid == 0) S->rep.exhausted = 1;
+            __syncthreads();
             continue;
         }
         // ================================================================ sweep ring
-        if (steady) {
-            csync(CL);   // every thread has read the state above
-            if (j == 0 && sh->e_scan < clean0) sh->e_scan = clean0;
-            refill_queue(sh, S, ttag, btm, hsize, B, CL, rank, j, B);
-        } else {
-            csync(CL);
-            if (j == 0) { sh->e_idx = sh->e_cnt = 0; sh->e_scan = clean0; }
-        }
+        if (steady) refill_queue(sh, S, ttag, btm, hsize, B, CL, rank, j, B);
         TICK(0);
         // ================================================================ gather the next candidates from the map
-        // level A: the non-empty 64-position blocks at or behind `lo`, in order
-        int nblk;                 // blocks handed to level B
-        const i64 blk_lo = lo >> MAP_BLK_SHIFT;
-        i64 my_blk = -1;
-        if (kgate <= MAP_BLK_SHIFT) {          // dense levels: every block is likely to hold a candidate
-            i64 need = ((i64)B << kgate >> MAP_BLK_SHIFT) * 2 + 2;
-            if (need > B) need = B;
-            if (need > nblocks - blk_lo) need = nblocks - blk_lo;
-            nblk = need > 0 ? (int)need : 0;
-            if (j < nblk) my_blk = blk_lo + j;
-            if (j == 0) sh->gp_next = (blk_lo + nblk) << MAP_BLK_SHIFT;
-            csync(CL);
-        } else {
-            int lv = kgate - 10;
-            if (lv < 0) lv = 0;
-            if (lv > 6) lv = 6;
-            const int nv = 1 << lv;                          // 16-byte summary vectors per thread
-            const i64 bb0 = blk_lo & ~(i64)15;
-            const i64 b0 = bb0 + (i64)j * 16 * nv;
-            const u32 k4 = (u32)kgate * 0x01010101u;
-            int cnt = 0;
-            for (int q = 0; q < nv; q++) {
-                const i64 bq = b0 + 16 * q;
-                if (bq >= nblocks) break;
-                const uint4 v = __ldg(reinterpret_cast<const uint4 *>(bsum + bq));
-                unsigned m = ge_nibble(v.x, k4) | (ge_nibble(v.y, k4) << 4) | (ge_nibble(v.z, k4) << 8) | (ge_nibble(v.w, k4) << 12);
-                if (bq < blk_lo) m &= ~((1u << (int)(blk_lo - bq)) - 1u);
-                if (bq + 16 > nblocks) m &= (1u << (int)(nblocks - bq)) - 1u;
-                cnt += __popc(m);
-            }
-            if (j == 0) sh->gp_next = (bb0 + (i64)B * 16 * nv) << MAP_BLK_SHIFT;
-            unsigned long long total;
-            unsigned long long at = cluster_excl_scan((unsigned long long)cnt, S, sh, 1, CL, rank, total);
-            if (cnt && at < (unsigned long long)B) {
-                for (int q = 0; q < nv; q++) {
-                    const i64 bq = b0 + 16 * q;
-                    if (bq >= nblocks) break;
-                    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(bsum + bq));
-                    unsigned m = ge_nibble(v.x, k4) | (ge_nibble(v.y, k4) << 4) | (ge_nibble(v.z, k4) << 8) | (ge_nibble(v.w, k4) << 12);
-                    if (bq < blk_lo) m &= ~((1u << (int)(blk_lo - bq)) - 1u);
-                    if (bq + 16 > nblocks) m &= (1u << (int)(nblocks - bq)) - 1u;
-                    while (m) {
-                        const int b = __ffs(m) - 1;
-                        m &= m - 1;
-                        if (at < (unsigned long long)B) sh->blk[at] = bq + b;
-                        else atomicMin((long long *)&sh->gp_next, (long long)((bq + b) << MAP_BLK_SHIFT));   // first block left for the next batch
-                        at++;
-                    }
-                }
-            } else if (cnt) {
-                // my first non-empty block is already beyond the batch
-                for (int q = 0; q < nv; q++) {
-                    const i64 bq = b0 + 16 * q;
-                    if (bq >= nblocks) break;
-                    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(bsum + bq));
-                    unsigned m = ge_nibble(v.x, k4) | (ge_nibble(v.y, k4) << 4) | (ge_nibble(v.z, k4) << 8) | (ge_nibble(v.w, k4) << 12);
-                    if (bq < blk_lo) m &= ~((1u << (int)(blk_lo - bq)) - 1u);
-                    if (bq + 16 > nblocks) m &= (1u << (int)(nblocks - bq)) - 1u;
-                    if (m) { atomicMin((long long *)&sh->gp_next, (long long)((bq + (__ffs(m) - 1)) << MAP_BLK_SHIFT)); break; }
-                }
-            }
-            nblk = total < (unsigned long long)B ? (int)total : B;
-            csync(CL);
-            if (j < nblk) my_blk = sh->blk[j];
-        }
-        // level B: the candidate positions of those blocks, in order
-        u64 cmask = 0;
-        if (my_blk >= 0) {
-            const uint4 *src = reinterpret_cast<const uint4 *>(bmap + (my_blk << MAP_BLK_SHIFT));
-            const u32 k4 = (u32)kgate * 0x01010101u;
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const uint4 v = __ldg(src + q);
-                const u64 m16 = (u64)(ge_nibble(v.x, k4) | (ge_nibble(v.y, k4) << 4) | (ge_nibble(v.z, k4) << 8) | (ge_nibble(v.w, k4) << 12));
-                cmask |= m16 << (16 * q);
-            }
-            const i64 p0 = my_blk << MAP_BLK_SHIFT;
-            if (p0 < lo) cmask &= ~(((u64)1 << (int)(lo - p0)) - 1);        // lo - p0 < 64
-            if (p0 + 63 > end) cmask &= (end - p0 >= 63) ? ~(u64)0 : (((u64)1 << (int)(end - p0 + 1)) - 1);
-        }
+        // thread j looks at the s = 2^kgate positions [a, a + s): one candidate expected.  One cluster-wide prefix sum
+        // orders them; the cluster exchanges them through b_pos[] (thread j then takes candidate j).
+        const int ks = kgate < 16 ? kgate : 16, s = 1 << ks;
+        const i64 gbase = lo & ~((i64)s - 1);
+        const i64 a = gbase + (i64)j * s;
         int nr;
-        i64 my_pos = 0, my_tag = 0;
         {
+            int cnt = 0;
+            span_candidates(bmap, bsum, a, s, kgate, lo, end, nblocks, [&](i64) { cnt++; return true; });
+            if (tid == 0) S->lgp = 0x7fffffffffffffffLL;
             unsigned long long total;
-            unsigned long long at = cluster_excl_scan((unsigned long long)__popcll(cmask), S, sh, 2, CL, rank, total);
-            const i64 p0 = my_blk << MAP_BLK_SHIFT;
-            u64 m = cmask;
-            while (m) {
-                const int b = __ffsll((long long)m) - 1;
-                m &= m - 1;
-                if (at < (unsigned long long)B) sh->b_pos[at] = p0 + b;
-                else { atomicMin((long long *)&sh->gp_next, (long long)(p0 + b)); break; }      // first candidate left for the next batch
-                at++;
+            unsigned long long at = cluster_excl_scan((unsigned long long)cnt, S, 1, CL, rank, total, NoExtra());
+            if (cnt) {
+                i64 drop = -1;
+                span_candidates(bmap, bsum, a, s, kgate, lo, end, nblocks, [&](i64 pos) {
+                    if (at < (unsigned long long)B) {
+                        STG_(sh->b_pos[at], pos);
+                        prefetch_l2(buf + (pos & ~(i64)31));
+                        prefetch_l2(buf + (pos & ~(i64)31) + 63);
+                        at++;
+                        return true;
+                    }
+                    drop = pos;                  // first candidate left for the next batch
+                    return false;
+                });
+                if (drop >= 0) atomicMin((long long *)&S->lgp, (long long)drop);
             }
-            nr = total < (unsigned long long)B ? (int)total : B;
+            __syncthreads();
+            if (tid < CL) push_to(&S->rep.xmin[rank], tid, S->lgp);
             csync(CL);
+            nr = total < (unsigned long long)B ? (int)total : B;
+            if (tid == 0) {
+                i64 g = gbase + (i64)B * s;
+                for (int r = 0; r < CL; r++) g = S->rep.xmin[r] < g ? S->rep.xmin[r] : g;
+                x.gp = g;
+            }
         }
-        if (j == 0) {
-            sh->gp = sh->gp_next;
-            sh->nr = nr;
-        }
-        if (nr == 0) { csync(CL); TICK(1); continue; }
-        i64 prev1 = -1, prev2 = -1;
+        if (nr == 0) { __syncthreads(); TICK(1); continue; }
+        i64 my_pos = 0, my_tag = 0, prev1 = -1, prev2 = -1;
         if (j < nr) {
-            my_pos = sh->b_pos[j];
-            if (j > 0) prev1 = sh->b_pos[j - 1];
-            if (j > 1) prev2 = sh->b_pos[j - 2];
+            my_pos = LDG_(sh->b_pos[j]);
+            if (j > 0) prev1 = LDG_(sh->b_pos[j - 1]);
+            if (j > 1) prev2 = LDG_(sh->b_pos[j - 2]);
             my_tag = tag_at(buf, S->hx, my_pos);
-            sh->b_tag[j] = my_tag;
+            STG_(sh->b_tag[j], my_tag);
         }
         TICK(1);
         if (dbg && j == 0) { dbg[16] += nr; dbg[17] += 1; }
@@ -1127,8 +1203,7 @@ k_automaton(const AutoDesc *__restrict__ descs) {
             // twin: same tag as the position just before, which is not itself the second of a pair
             bool same = false, same_prev = false;
             if (prev1 == my_pos - 1) {
-                const i64 hb = S->hx[buf[my_pos - 1]], hf = S->hx[buf[my_pos + 30]];
-                same = hb == hf;                                   // tag[p-1] == tag[p]
+                same = S->hx[buf[my_pos - 1]] == S->hx[buf[my_pos + 30]];                                       // tag[p-1] == tag[p]
                 if (same && prev2 == my_pos - 2) same_prev = S->hx[buf[my_pos - 2]] == S->hx[buf[my_pos + 29]];   // tag[p-2] == tag[p-1]
             }
             follower = same && !same_prev;
@@ -1148,199 +1223,268 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 plan_follower(pl, ttag, gsum, buf, my_pos, my_tag, a_flags, a_w2, hsize, min_mask, chain, end, last_now);
             }
         }
-        if (j < nr) { sh->pl_fl[j] = pl.flags; sh->pl_w2[j] = pl.w2_slot; }
-        if (j == 0) { sh->pos = 0; sh->ended = 0; sh->jumped = 0; sh->qcut = 0x7fffffff; }
+        if (j < nr) { STG_(sh->pl_fl[j], pl.flags); STG_(sh->pl_w2[j], pl.w2_slot); }
         TICK(2);
         const int my_need = tz1(my_tag) > __popcll((u64)btm) ? tz1(my_tag) : __popcll((u64)btm);
-        int pos = 0;
+        int pos = 0;                 // ops before pos are done (committed, executed or skipped)
+        int pre0 = 0;                // the prefix sums in pre[] cover the ops of [pre0, nr)
+        bool need_conflict = true;   // plans were made since the last round of claims
         bool batch_ended = false;
+        int qacc = 0x7fffffff;       // smallest ring slot a committed plan overwrote (the ring is cut there at the end of the batch)
+        i64 w_lo = x.run.clean_ptr, w_hi = steady ? x.e_scan : w_lo, s_safe = w_lo - 1;
+        unsigned long long incl = 0;
 
-        for (;;) {   // ====================================================== rounds: conflicts -> cut -> commit -> (executor | plan again)
-            // ---------------------------------------------------------------- conflicts: exact stop-slot claims with forwarding
-            // Every live plan claims its stop slot(s) in claim[] (atomicMin of (epoch, op index)).  A plan whose stop slot
-            // is claimed by an EARLIER op either walks on from the next slot - when that op's tag is no stop for this walk,
-            // the claimed slot is remembered as a dependency - or gives up (F_CONF).  Iterated to a fixed point.
-            // The sweep can reach the slots of the ring up to s_safe within this batch (at most one sweep per op).
-            const i64 w_lo = sh->run.clean_ptr, w_hi = steady ? sh->e_scan : w_lo;
-            i64 s_safe = w_lo - 1;
-            if (steady && w_hi > w_lo) {
-                const unsigned ei = sh->e_idx, ec = sh->e_cnt;
-                const unsigned reach = (unsigned)(nr - pos);
-                s_safe = (ec - ei > reach) ? (i64)sh->E[(ei + reach) & (MRZ_EQ_CAP - 1)] : w_hi - 1;
-            }
-            for (int it = 0;; it++) {
-                if (epoch >= CLAIM_EPOCH_MAX) {   // claim keys exhausted: wipe the array, restart the epochs
+        for (;;) {   // ====================================================== rounds: [conflicts ->] cut -> commit -> (executor | plan again)
+            // the sweep can reach the slots of the ring up to s_safe within this batch (at most one sweep per op)
+            const bool ovf_possible = steady ? (int)(x.e_cnt - x.e_idx) < nr - pos : x.run.count + (nr - pos) > limit;
+            // zone: a stop slot the sweep may reach in this batch: the order of sweeps and inserts matters
+#define ZONE_CHECK()                                                                                                   \
+    if (steady && !(pl.flags & F_CONF) && (pl.flags & (F_COMPLEX | F_INSERT)) == F_INSERT &&                           \
+        (((pl.flags & F_W2ELIG) && pl.w2_slot >= w_lo && pl.w2_slot <= s_safe) ||                                       \
+         ((pl.flags & F_W1ELIG) && pl.w1_slot >= w_lo && pl.w1_slot <= s_safe))) {                                      \
+        pl.flags |= F_CONF | F_ZONE;                                                                                   \
+        if (dbg) atomicAdd((unsigned long long *)&dbg[32], 1ULL);                                                      \
+    }
+#define CLAIM(ep_)                                                                                                      \
+    if (j >= pos && j < nr && (pl.flags & (F_COMPLEX | F_INSERT | F_CONF)) == F_INSERT) {                               \
+        unsigned *const cw_ = ((ep_) & 1u) ? claim1 : claim0;                                                           \
+        int s2 = pl.w2_slot; CHK(sh, x, 1, s2, hsize + 8);                                                              \
+        atomicMin(cw_ + s2, claim_key(ep_, j, 0));                                                                      \
+        if (pl.flags & F_W1) { int s1 = pl.w1_slot; CHK(sh, x, 2, s1, hsize + 8); atomicMin(cw_ + s1, claim_key(ep_, j, 1)); } \
+    }
+            if (tid == 0) { S->lmin = 0x7fffffff; S->lq = 0x7fffffff; }
+            __syncthreads();
+            bool heavy = false;                    // this round computes the prefix sums afresh
+            unsigned long long heavy_total = 0;
+            if (need_conflict) {
+                // ------------------------------------------------------------ conflicts: exact stop-slot claims with forwarding
+                // Every live plan claims its stop slot(s) in claim[] (atomicMin of (epoch, op index)).  A plan whose stop slot
+                // is claimed by an EARLIER op either walks on from the next slot - when that op's tag is no stop for this walk,
+                // the claimed slot is remembered as a dependency - or gives up (F_CONF).  Iterated to a fixed point; the claims
+                // of the next epoch are made BEFORE the barrier that tells whether anybody changed: one hop per iteration.
+                {   // a dependency on an op that has been committed since is satisfied for good
+                    int nd = 0;
+                    for (int d = 0; d < pl.ndep; d++)
+                        if (pl.dep_own[d] >= pos) { pl.dep_slot[nd] = pl.dep_slot[d]; pl.dep_own[nd] = pl.dep_own[d]; nd++; }
+                    pl.ndep = nd;
+                }
+                w_lo = x.run.clean_ptr; w_hi = steady ? x.e_scan : w_lo; s_safe = w_lo - 1;
+                if (steady && w_hi > w_lo) {
+                    const unsigned ei = x.e_idx, ec = x.e_cnt, reach = (unsigned)(nr - pos);
+                    s_safe = (ec - ei > reach) ? (i64)LDG_(sh->E[(ei + reach) & (MRZ_EQ_CAP - 1)]) : w_hi - 1;
+                }
+                if (epoch + 4 * FWD_ITERS + 16 >= CLAIM_EPOCH_MAX) {   // claim keys nearly exhausted: wipe the arrays, restart the epochs
                     csync(CL);
-                    for (i64 q = j; q < hsize + 8; q += B) claim[q] = 0xffffffffu;
+                    for (i64 q = j; q < hsize + 8; q += B) claim0[q] = claim1[q] = 0xffffffffu;
+                    if (tid == 0) for (int r = 0; r < MRZ_MAXCL; r++) S->rep.chg[0][r] = S->rep.chg[1][r] = 0xffffffffu;
                     epoch = 0;
                     csync(CL);
                 }
-                const unsigned ep = epoch++;
-                const unsigned ep_hi = KEY_EPOCH(claim_key(ep, 0, 0));
-                const bool planned_ins = j >= pos && j < nr && (pl.flags & (F_COMPLEX | F_INSERT)) == F_INSERT;
-                bool live = planned_ins && !(pl.flags & F_CONF);
-                if (live && steady &&   // a stop slot the sweep may reach in this batch: the order of sweeps and inserts matters
-                    (((pl.flags & F_W2ELIG) && pl.w2_slot >= w_lo && pl.w2_slot <= s_safe) ||
-                     ((pl.flags & F_W1ELIG) && pl.w1_slot >= w_lo && pl.w1_slot <= s_safe))) {
-                    pl.flags |= F_CONF | F_ZONE;
-                    live = false;
-                    if (dbg) atomicAdd((unsigned long long *)&dbg[32], 1ULL);
-                }
-                if (live) {
-                    int s2 = pl.w2_slot; CHK(sh, 1, s2, hsize + 8);
-                    atomicMin(claim + s2, claim_key(ep, j, 0));
-                    if (pl.flags & F_W1) { int s1 = pl.w1_slot; CHK(sh, 2, s1, hsize + 8); atomicMin(claim + s1, claim_key(ep, j, 1)); }
-                }
+                unsigned ep = epoch++;
+                ZONE_CHECK();
+                CLAIM(ep);
                 csync(CL);
-                if (j == 0) sh->changed[(it + 1) & 1] = 0;   // last read before the barrier above, next written behind the one below
-                bool chg = false;
-                if (live) {
-                    bool bad = false;
-                    // a follower's plan builds on its leader's write: only older claims conflict, and the leader must not have moved
-                    const int before = (pl.flags & F_FOLLOW) ? j - 1 : j;
-                    int why = 0;
-                    if ((pl.flags & F_FOLLOW) && j - 1 >= pos && sh->pl_w2[j - 1] != lead_w2) { bad = true; why = 33; }
-                    for (int d = 0; d < pl.ndep && !bad; d++) {   // slots I walked past on the strength of an earlier op's claim
-                        const unsigned o = __ldcg(claim + pl.dep_slot[d]);
-                        const int oi = KEY_IDX(o);
-                        if (KEY_EPOCH(o) != ep_hi || (o & 1u) || oi >= j) { bad = true; why = 34; break; }
-                        const i64 ot = sh->b_tag[oi];
-                        if (tz1(ot) < my_need || (ot & btm) != btm || ot == my_tag) { bad = true; why = 34; break; }
-                        pl.dep_own[d] = oi;
-                    }
-                    if (!bad) {
-                        const unsigned o = __ldcg(claim + pl.w2_slot);
-                        const int oi = KEY_IDX(o);
-                        if (oi < before) {   // my stop slot goes to an earlier op
-                            const i64 ot = sh->b_tag[oi];
-                            if ((pl.flags & F_FOLLOW) || (o & 1u) || pl.ndep == MAXDEP || it >= FWD_ITERS || tz1(ot) < my_need ||
-                                (ot & btm) != btm || ot == my_tag) {   // an equal tag: my lookup must meet its entry
-                                bad = true;
-                                why = (pl.flags & F_FOLLOW) ? 33 : (o & 1u) ? 35 : ot == my_tag ? 36 : (tz1(ot) < my_need || (ot & btm) != btm) ? 37 : 38;
-                            } else {         // its tag is no stop for my walk: go on from the next slot
-                                pl.dep_slot[pl.ndep] = pl.w2_slot; pl.dep_own[pl.ndep] = oi; pl.ndep++;
-                                plan_op(pl, ttag, toff, gsum, filt, my_tag, (i64)pl.w2_slot + 1, hmask, hsize, min_mask, chain);
-                                sh->pl_w2[j] = pl.w2_slot;
-                                chg = true;
-                                if (dbg) atomicAdd((unsigned long long *)&dbg[31], 1ULL);
-                            }
-                        } else if ((pl.flags & F_W1) && KEY_IDX(__ldcg(claim + pl.w1_slot)) < j) {
-                            bad = true;
-                            why = 39;
+                for (int it = 0;; it++) {
+                    if (tid == 0) S->lchg = 0;
+                    __syncthreads();
+                    const unsigned ep_hi = KEY_EPOCH(claim_key(ep, 0, 0));
+                    const unsigned *const claim = (ep & 1u) ? claim1 : claim0;     // the claims of epoch ep (complete since the last barrier)
+                    const bool live = j >= pos && j < nr && (pl.flags & (F_COMPLEX | F_INSERT | F_CONF)) == F_INSERT;
+                    bool chg = false;
+                    if (live) {
+                        bool bad = false;
+                        // a follower's plan builds on its leader's write: only older claims conflict, and the leader must not have moved
+                        const int before = (pl.flags & F_FOLLOW) ? j - 1 : j;
+                        int why = 0;
+                        if ((pl.flags & F_FOLLOW) && j - 1 >= pos && LDG_(sh->pl_w2[j - 1]) != lead_w2) { bad = true; why = 33; }
+                        for (int d = 0; d < pl.ndep && !bad; d++) {   // slots I walked past on the strength of an earlier op's claim
+                            const unsigned o = __ldcg(claim + pl.dep_slot[d]);
+                            const int oi = KEY_IDX(o);
+                            if (KEY_EPOCH(o) != ep_hi || (o & 1u) || oi >= j) { bad = true; why = 34; break; }
+                            const i64 ot = LDG_(sh->b_tag[oi]);
+                            if (tz1(ot) < my_need || (ot & btm) != btm || ot == my_tag) { bad = true; why = 34; break; }
+                            pl.dep_own[d] = oi;
                         }
+                        if (!bad) {
+                            const unsigned o = __ldcg(claim + pl.w2_slot);
+                            const int oi = KEY_IDX(o);
+                            if (oi < before) {   // my stop slot goes to an earlier op
+                                const i64 ot = LDG_(sh->b_tag[oi]);
+                                if ((pl.flags & F_FOLLOW) || (o & 1u) || pl.ndep == MAXDEP || it >= FWD_ITERS || tz1(ot) < my_need ||
+                                    (ot & btm) != btm || ot == my_tag) {   // an equal tag: my lookup must meet its entry
+                                    bad = true;
+                                    why = (pl.flags & F_FOLLOW) ? 33 : (o & 1u) ? 35 : ot == my_tag ? 36 : (tz1(ot) < my_need || (ot & btm) != btm) ? 37 : 38;
+                                } else {         // its tag is no stop for my walk: go on from the next slot
+                                    pl.dep_slot[pl.ndep] = pl.w2_slot; pl.dep_own[pl.ndep] = oi; pl.ndep++;
+                                    plan_op(pl, ttag, toff, gsum, filt, my_tag, (i64)pl.w2_slot + 1, hmask, hsize, min_mask, chain);
+                                    STG_(sh->pl_w2[j], pl.w2_slot);
+                                    chg = true;
+                                    if (dbg) atomicAdd((unsigned long long *)&dbg[31], 1ULL);
+                                }
+                            } else if ((pl.flags & F_W1) && KEY_IDX(__ldcg(claim + pl.w1_slot)) < j) {
+                                bad = true;
+                                why = 39;
+                            }
+                        }
+                        if (bad) { pl.flags |= F_CONF; chg = true; if (dbg) atomicAdd((unsigned long long *)&dbg[why], 1ULL); }
+                        if (chg) { STG_(sh->pl_fl[j], pl.flags); S->lchg = 1; }
                     }
-                    if (bad) { pl.flags |= F_CONF; chg = true; if (dbg) atomicAdd((unsigned long long *)&dbg[why], 1ULL); }
-                    if (chg) sh->pl_fl[j] = pl.flags;
+                    const unsigned ep2 = epoch++;
+                    ZONE_CHECK();
+                    CLAIM(ep2);          // in case anybody changed: every live plan is validated again under the next epoch
+                    __syncthreads();
+                    // (slot [it & 1]: a CTA that is already in the next iteration must not overwrite what a slower one still reads)
+                    if (tid < CL && S->lchg) push_to(&S->rep.chg[it & 1][rank], tid, ep2);
+                    csync(CL);
+                    bool any = false;
+                    for (int r = 0; r < CL; r++) any = any || S->rep.chg[it & 1][r] == ep2;
+                    if (!any) break;
+                    ep = ep2;
                 }
-                if (chg) sh->changed[it & 1] = 1;
-                csync(CL);
-                if (!sh->changed[it & 1]) break;
+                TICK(3);
             }
-            TICK(3);
-            // ---------------------------------------------------------------- prefix over the ops of [pos, nr) that hold a valid plan, and the cut
-            round++;
-            const unsigned long long rkey = (unsigned long long)(~round) << 32;
-            unsigned long long incl;
+            // ---------------------------------------------------------------- [prefix over the valid plans of [pos, nr)] and the cut
+            const i64 cnt0 = x.run.count;
+            const unsigned e_idx0 = x.e_idx;
+            const int avail = (int)(x.e_cnt - e_idx0);
+            bool c_free = false, exact = false;     // the part of the cut condition that does not depend on the prefix sums
+            if (j >= pos && j < nr) {
+                exact = (pl.flags & (F_COMPLEX | F_ZONE)) != 0 || (x.run.cur_len >= MRZ_MIN_MATCH && my_pos >= x.run.cur_p + MRZ_MIN_MATCH);   // an emission is due
+                c_free = exact || (pl.flags & F_CONF) != 0;
+            }
             {
+                const unsigned bal = __ballot_sync(FULL, c_free), exb = __ballot_sync(FULL, exact);
+                if (bal && lane == 0) {
+                    const int l = __ffs(bal) - 1;
+                    atomicMin(&S->lmin, ((j + l) << 1) | (int)((exb >> l) & 1u));
+                }
+            }
+            if (need_conflict) {
                 unsigned long long v = 0;
                 if (j >= pos && j < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
                     v = 1ULL << 48;
                     if (pl.flags & F_INSERT) v |= (unsigned long long)pl.dcount | (1ULL << 16) | ((pl.flags & F_FOLLOW) ? (1ULL << 32) : 0ULL);
                 }
                 unsigned long long total;
-                incl = cluster_excl_scan(v, S, sh, 3, CL, rank, total) + v;
-                if (j < nr) sh->pre[j] = incl;
+                incl = cluster_excl_scan(v, S, 2, CL, rank, total, [&](unsigned long long ex) {
+                    // the local minimum is complete (the atomics came before block_excl_scan's barriers): it crosses the cluster in
+                    // the same hop as the scan totals, together with the prefix sum at the cut (what commits before it)
+                    const int lm = S->lmin;
+                    if (tid < CL) push_to(&S->rep.lcut[0][rank], tid, (unsigned long long)(unsigned)lm);
+                    if (lm != 0x7fffffff && j == (lm >> 1))
+                        for (int r = 0; r < CL; r++) push_to(&S->rep.lcutpre[rank], r, ex);
+                }) + v;
+                if (j < nr) STG_(sh->pre[j], incl);      // for the later rounds of this batch (visible behind the commit barrier)
+                heavy_total = total;
+                pre0 = pos;
+                heavy = true;
+                need_conflict = false;
+            } else {
+                __syncthreads();
+                if (tid < CL) push_to(&S->rep.lcut[0][rank], tid, (unsigned long long)(unsigned)S->lmin);
+                csync(CL);
             }
-            const i64 cnt0 = sh->run.count;
-            const unsigned e_idx0 = sh->e_idx;
-            const int avail = (int)(sh->e_cnt - e_idx0);
-            {
-                const i64 cur_len = sh->run.cur_len, cur_p = sh->run.cur_p;
-                bool c = false, exact = false;
-                if (j >= pos && j < nr) {
-                    exact = (pl.flags & (F_COMPLEX | F_ZONE)) != 0 || (cur_len >= MRZ_MIN_MATCH && my_pos >= cur_p + MRZ_MIN_MATCH);   // an emission is due
-                    c = exact || (pl.flags & F_CONF) != 0;
-                    if (!c && (pl.flags & F_INSERT) && pl.dcount == 1) {
-                        const i64 Tc = cnt0 + (i64)PK_D(incl);
-                        if (Tc > limit && (!steady || Tc - limit > avail)) c = exact = true;   // needs a serial sweep step
-                    }
-                }
-                const unsigned bal = __ballot_sync(FULL, c);
-                if (bal) {
-                    const int l = __ffs(bal) - 1;
-                    const int ex = __shfl_sync(FULL, (int)exact, l);
-                    if (lane == 0) atomicMin((unsigned long long *)&sh->kcut, rkey | ((unsigned long long)(j + l) << 1) | (unsigned long long)ex);
-                }
-            }
-            csync(CL);
-            // ---------------------------------------------------------------- commit [pos, k)
             int k = nr;          // first op of [pos, nr) that cannot be committed from its plan
             bool k_exact = false;
             {
-                const unsigned long long kc = sh->kcut;
-                if ((kc >> 32) == (rkey >> 32)) { k = (int)((kc & 0xffffffffu) >> 1); k_exact = (kc & 1ULL) != 0; }
+                unsigned m = 0x7fffffffu;
+                for (int r = 0; r < CL; r++) { const unsigned vv = (unsigned)S->rep.lcut[0][r]; m = vv < m ? vv : m; }
+                if (m != 0x7fffffffu) { k = (int)(m >> 1); k_exact = (m & 1u) != 0; }
             }
+            const unsigned long long basev = pos > pre0 ? LDG_(sh->pre[pos - 1]) : 0ULL;
+            // d: the sums over the ops of [pos, k).  Right after the scan nobody can read pre[] of another CTA yet: the sums
+            // come from the scan totals of the ranks below the cut's and the prefix its owner pushed along with it.
             unsigned long long d = 0;
+            if (heavy) {
+                if (k >= nr) d = heavy_total;
+                else {
+                    const int rk = k / T;
+                    for (int r = 0; r < rk; r++) d += S->rep.tot[2][r];
+                    d += S->rep.lcutpre[rk];
+                }
+            } else if (k > pos) d = LDG_(sh->pre[k - 1]) - basev;
+            if (ovf_possible) {   // rare: an insert may need a sweep step the ring cannot serve (first overflow / ring at the end of the table)
+                if (tid == 0) S->lmin = 0x7fffffff;
+                __syncthreads();
+                bool c = false;
+                if (j >= pos && j < k && (pl.flags & F_INSERT) && !(pl.flags & (F_COMPLEX | F_CONF)) && pl.dcount == 1) {
+                    const i64 Tc = cnt0 + (i64)PK_D(incl - basev);
+                    if (Tc > limit && (!steady || Tc - limit > avail)) c = true;   // needs a serial sweep step
+                }
+                const unsigned bal = __ballot_sync(FULL, c);
+                if (bal && lane == 0) atomicMin(&S->lmin, ((j + __ffs(bal) - 1) << 1) | 1);
+                __syncthreads();
+                if (tid < CL) push_to(&S->rep.lcut[1][rank], tid, (unsigned long long)(unsigned)S->lmin);
+                csync(CL);
+                unsigned m = 0x7fffffffu;
+                for (int r = 0; r < CL; r++) { const unsigned vv = (unsigned)S->rep.lcut[1][r]; m = vv < m ? vv : m; }
+                if (m != 0x7fffffffu && (int)(m >> 1) < k) {
+                    k = (int)(m >> 1); k_exact = true;
+                    d = k > pos ? LDG_(sh->pre[k - 1]) - basev : 0ULL;      // pre[] was stored before the barrier above
+                }
+            }
+            // ---------------------------------------------------------------- commit [pos, k)
             int cleans = 0;
             i64 Tk = cnt0;
             if (k > pos) {
-                d = sh->pre[k - 1];
                 Tk = cnt0 + (i64)PK_D(d);
                 cleans = Tk > limit ? (int)(Tk - limit) : 0;
             }
             if (j >= pos && j < k && (pl.flags & F_INSERT)) {
                 if (pl.flags & F_W1) {
-                    int s1 = pl.w1_slot; CHK(sh, 3, s1, hsize);
+                    int s1 = pl.w1_slot; CHK(sh, x, 3, s1, hsize);
                     __stcg(toff + s1, pl.w1_off);
                     __stcg(ttag + s1, pl.w1_tag);
                     sum_lower(gsum, s1 >> GRP_SHIFT, tz1c(pl.w1_tag));
-                    if (steady && (pl.flags & F_W1ELIG) && s1 >= w_lo && s1 < w_hi) atomicMin((int *)&sh->qcut, s1);   // a ring slot the sweep does not reach in this batch
+                    if (steady && (pl.flags & F_W1ELIG) && s1 >= w_lo && s1 < w_hi) atomicMin(&S->lq, s1);   // a ring slot the sweep does not reach in this batch
                 }
                 // a twin that overwrites its leader's entry in the same commit must win the slot
-                const bool overwritten = j + 1 < k && (sh->pl_fl[j + 1] & F_FOLLOW) && sh->pl_w2[j + 1] == pl.w2_slot;
-                int s2 = pl.w2_slot; CHK(sh, 4, s2, hsize);
+                const bool overwritten = j + 1 < k && (LDG_(sh->pl_fl[j + 1]) & F_FOLLOW) && LDG_(sh->pl_w2[j + 1]) == pl.w2_slot;
+                int s2 = pl.w2_slot; CHK(sh, x, 4, s2, hsize);
                 if (!overwritten) {
                     __stcg(toff + s2, my_pos);
                     __stcg(ttag + s2, my_tag);
                     sum_lower(gsum, s2 >> GRP_SHIFT, tz1c(my_tag));
                 }
-                if (steady && (pl.flags & F_W2ELIG) && s2 >= w_lo && s2 < w_hi) atomicMin((int *)&sh->qcut, s2);
+                if (steady && (pl.flags & F_W2ELIG) && s2 >= w_lo && s2 < w_hi) atomicMin(&S->lq, s2);
                 filt_set(filt, my_tag);
                 if (pl.flags & F_FOLLOW) filt_set(filt, my_tag ^ DUP_SALT);   // the tag is in the table twice now
             }
             for (int q = j; q < cleans; q += B) {
-                int sl = sh->E[(e_idx0 + (unsigned)q) & (MRZ_EQ_CAP - 1)]; CHK(sh, 5, sl, hsize);
+                int sl = LDG_(sh->E[(e_idx0 + (unsigned)q) & (MRZ_EQ_CAP - 1)]); CHK(sh, x, 5, sl, hsize);
                 __stcg(ttag + sl, (i64)0);
                 __stcg(toff + sl, (i64)0);
                 sum_lower(gsum, sl >> GRP_SHIFT, 0);
             }
-            if (j == 0 && k > pos) {
-                sh->run.count = Tk - cleans;
-                sh->run.inserts = sh->run.inserts + PK_I(d);
-                sh->run.misses = sh->run.misses + PK_M(d);
-                sh->run.nops = sh->run.nops + PK_V(d);
-                // the last op of [pos, k) that was not skipped behind a jump is op k-1 itself: positions ascend
-                sh->run.p = sh->b_pos[k - 1];
+            if (tid == 0 && k > pos) {           // every CTA applies the same update to its replica
+                x.run.count = Tk - cleans;
+                x.run.inserts += PK_I(d);
+                x.run.misses += PK_M(d);
+                x.run.nops += PK_V(d);
                 if (cleans) {
-                    sh->e_idx = e_idx0 + (unsigned)cleans;
-                    sh->run.clean_ptr = sh->E[(e_idx0 + (unsigned)cleans - 1) & (MRZ_EQ_CAP - 1)];   // pointer stays on the last zeroed slot
+                    x.e_idx = e_idx0 + (unsigned)cleans;
+                    x.run.clean_ptr = LDG_(sh->E[(e_idx0 + (unsigned)cleans - 1) & (MRZ_EQ_CAP - 1)]);   // pointer stays on the last zeroed slot
                 }
             }
+            __syncthreads();
+            if (tid < CL) push_to(&S->rep.qmin[rank], tid, S->lq);
             csync(CL);
+            for (int r = 0; r < CL; r++) qacc = S->rep.qmin[r] < qacc ? S->rep.qmin[r] : qacc;
             TICK(4);
             if (k >= nr) break;
             if (dbg && j == k) {   // why does this op cut the batch?
                 const int why = (pl.flags & F_COMPLEX) ? (follower ? 22 : ((pl.flags & F_INSERT) ? 23 : 21)) : k_exact ? 25 : 24;
                 atomicAdd((unsigned long long *)&dbg[why], 1ULL);
             }
-            int npos = k;
+            if (dbg && j == 0) tm[11] += 1;
             if (k_exact) {
                 if (dbg && j == 0) tm[10] += 1;
                 // ---- the lookup of op k (find_best_match, rzip.c:426-462) by the whole CTA (rank 0): the probe sequence is
                 // walked 4*T slots per step, equal tags are collected in slot order, and the warps share the match_len calls
                 if (rank == 0) {
                     int pre_n = -2;   // -2: the filter says no equal tag; -1: ask / walk on the warp; >= 0: candidates compared
-                    const i64 tk = sh->b_tag[k], pk = sh->b_pos[k];
+                    const i64 tk = LDG_(sh->b_tag[k]), pk = LDG_(sh->b_pos[k]);
+                    const i64 c_lk0 = clock64();
                     if (filt_query(filt, tk)) {
                         pre_n = -1;
                         const i64 h = tk & hmask;
@@ -1378,7 +1522,7 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                         if (found && n_tot <= LK_CAP) {
                             // single_match_len (rzip.c:372-397) per candidate: the warps share the candidates for the first
                             // LK_XCAP bytes either side; whatever still matches there is extended by the whole CTA
-                            w.last = sh->run.last;
+                            w.last = x.run.last;
                             const i64 lo_m = w.last > 0 ? w.last : 0;
                             const i64 maxf = end - pk;
                             const int NW = T >> 5;
@@ -1453,57 +1597,59 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                             pre_n = n_tot;
                         }
                     }
-                    // ---- op k on the live table, reference semantics (warp 0)
+                    if (dbg && tid == 0) { dbg[18] += clock64() - c_lk0; dbg[19] += pre_n != -2; }
+                    // ---- op k on the live table, reference semantics (warp 0), on the local replica
                     if (wid == 0) {
-                        w.load(sh);
+                        w.load(x.run);
                         w.nlog = 0;
                         i64 hint = w.clean_ptr;
-                        if (steady) {
-                            const unsigned ei = sh->e_idx, ec = sh->e_cnt;
-                            const i64 es = sh->e_scan;
-                            hint = (ec != ei) ? (i64)sh->E[ei & (MRZ_EQ_CAP - 1)] : (es > hint ? es : hint);
-                        }
+                        if (steady) hint = (x.e_cnt != x.e_idx) ? (i64)LDG_(sh->E[x.e_idx & (MRZ_EQ_CAP - 1)]) : (x.e_scan > hint ? x.e_scan : hint);
                         w.clean_hint = hint;
                         w.p = pk;
                         const bool jumped = w.op(pk, tk, S->stk, pre_n, S->lk_len, S->lk_rev, S->lk_off, S->lk_pos);
                         w.clean_hint = 0;
-                        w.store(sh);
+                        w.store(x.run);
+                        const bool mask_changed = w.min_mask != min_mask || w.ins_mask != ins_mask;
+                        const bool overflow = w.nlog > MRZ_WLOG_CAP;
+                        int kp = nr;
+                        // an emission skips the ops up to the end of the match; the plans beyond it stay good (only a write to a
+                        // plan's stop slot can spoil it): carry on with the first op past the jump
+                        // (a short match can end BEFORE op k: p goes back, rzip.c:597: the batch ends)
+                        if (jumped && !mask_changed && !overflow && !w.error && w.p >= pk) kp = pos_upper_bound(sh, k + 1, nr, w.p, lane);
                         if (lane == 0) {
-                            const bool mask_changed = w.min_mask != min_mask || w.ins_mask != ins_mask;
-                            const bool overflow = w.nlog > MRZ_WLOG_CAP;
-                            sh->jumped = jumped;
-                            sh->nlog = overflow ? 0 : w.nlog;
-                            for (int q = 0; q < sh->nlog; q++) sh->wlog[q] = S->wlog[q];
-                            int kp = nr;
-                            if (jumped && !mask_changed && !overflow && !w.error && w.p >= pk) {   // (a short match can end BEFORE op k: p goes back, rzip.c:597)
-                                // an emission skips the ops up to the end of the match; the plans beyond it stay good (only a
-                                // write to a plan's stop slot can spoil it): carry on with the first op past the jump
-                                int a = k + 1, b = nr;
-                                while (a < b) {
-                                    const int m = (a + b) >> 1;
-                                    if (sh->b_pos[m] <= w.p) a = m + 1; else b = m;
-                                }
-                                kp = a;
-                            }
+                            x.jumped = jumped;
+                            x.nlog = overflow ? 0 : w.nlog;
                             if (mask_changed || overflow || w.error || (jumped && kp >= nr)) {
-                                sh->ended = 1;
-                                sh->e_idx = sh->e_cnt = 0; sh->e_scan = w.clean_ptr;    // rebuild the ring
+                                x.ended = 1;
+                                x.e_idx = x.e_cnt = 0; x.e_scan = w.clean_ptr;    // rebuild the ring
                                 // what this batch had gathered behind p is gathered again (a jump past the batch keeps the cursor)
-                                if (w.p + 1 < sh->gp) sh->gp = w.p + 1;
+                                if (w.p + 1 < x.gp) x.gp = w.p + 1;
                             } else {
-                                if (steady) sync_queue(sh, S->wlog, w.nlog);
-                                sh->pos = jumped ? kp : k + 1;
+                                x.ended = 0;
+                                if (steady) {
+                                    sync_queue(sh, &x, x.wlog, w.nlog);
+                                    if (x.e_cnt == x.e_idx && x.e_scan < w.clean_ptr) x.e_scan = w.clean_ptr;
+                                }
+                                x.pos_after = jumped ? kp : k + 1;
                             }
+                        }
+                        __syncwarp();
+                        // the result goes into every other replica
+                        const int nwords = (int)(sizeof(XRes) / 8);
+                        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&x);
+                        for (int r = 1; r < CL; r++) {
+                            volatile unsigned long long *dst = reinterpret_cast<volatile unsigned long long *>(remote_ptr(&x, r));
+                            for (int q = lane; q < nwords; q += 32) dst[q] = src[q];
                         }
                     }
                 }
                 csync(CL);
                 TICK(5);
-                if (sh->ended) { batch_ended = true; break; }
+                if (x.ended) { batch_ended = true; break; }
                 // the op overwrote a queued slot and the ring was cut there: rebuild its tail, but only inside the
                 // window this batch was planned with
-                if (steady && sh->e_scan < w_hi) refill_queue(sh, S, ttag, btm, w_hi, MRZ_EQ_CAP, CL, rank, j, B);
-                npos = sh->pos;   // k + 1, or the first op past an emission's jump (the ops in between never run)
+                if (steady && x.e_scan < w_hi) refill_queue(sh, S, ttag, btm, w_hi, MRZ_EQ_CAP, CL, rank, j, B);
+                const int npos = x.pos_after;   // k + 1, or the first op past an emission's jump (the ops in between never run)
                 // later plans that read a slot this op wrote are no longer valid; nor is its twin's plan
                 if (j == npos && (pl.flags & F_FOLLOW)) pl.flags |= F_CONF;
                 if (j >= npos && j < nr)   // a plan forwarded over the claim of op k / of a skipped op assumed that op's planned write
@@ -1511,78 +1657,59 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                         if (pl.dep_own[dd] >= k && pl.dep_own[dd] < npos) pl.flags |= F_CONF;
                 if (j >= npos && j < nr && (pl.flags & F_FOLLOW) && j - 1 >= k && j - 1 < npos) pl.flags |= F_CONF;   // its leader was skipped
                 if (j >= npos && j < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
-                    const int nl = sh->nlog;
+                    const int nl = x.nlog;
                     for (int q = 0; q < nl; q++) {
-                        const int sl = sh->wlog[q] >> 1;
+                        const int sl = x.wlog[q] >> 1;
                         bool hit = sl == pl.w2_slot || ((pl.flags & F_W1) && sl == pl.w1_slot);
                         for (int dd = 0; dd < pl.ndep; dd++) hit = hit || sl == pl.dep_slot[dd];
                         if (hit) { pl.flags |= F_CONF; break; }
                     }
                 }
+                pos = npos;
+            } else {
+                // ------------------------------------------------------------ plan again what lost its plan
+                // All ops before `pos` are in the table now, so the first of these plans is exact; the others are as
+                // speculative as a first plan and are validated by the next round of claims.  A twin becomes an ordinary
+                // op: if its leader has been committed, the filter finds the leader's entry.
+                pos = k;
+                if (j >= pos && j < nr && (pl.flags & F_CONF) && !(pl.flags & F_COMPLEX)) {
+                    plan_init(pl);
+                    follower = false;
+                    lead_w2 = -1;
+                    if (filt_query(filt, my_tag)) pl.flags |= F_COMPLEX;
+                    else if ((my_tag & ins_mask) == ins_mask)
+                        plan_op(pl, ttag, toff, gsum, filt, my_tag, my_tag & hmask, hmask, hsize, min_mask, chain);
+                    STG_(sh->pl_fl[j], pl.flags); STG_(sh->pl_w2[j], pl.w2_slot);
+                    if (dbg) atomicAdd((unsigned long long *)&dbg[30], 1ULL);
+                }
+                need_conflict = true;
             }
-            pos = npos;
-            // ---------------------------------------------------------------- plan again what lost its plan
-            // All ops before `pos` are in the table now, so the first of these plans is exact; the others are as
-            // speculative as a first plan and are validated by the next round of claims.  A twin becomes an ordinary
-            // op: if its leader has been committed, the filter finds the leader's entry.
-            if (j >= pos && j < nr && (pl.flags & F_CONF) && !(pl.flags & F_COMPLEX)) {
-                plan_init(pl);
-                follower = false;
-                lead_w2 = -1;
-                if (filt_query(filt, my_tag)) pl.flags |= F_COMPLEX;
-                else if ((my_tag & ins_mask) == ins_mask)
-                    plan_op(pl, ttag, toff, gsum, filt, my_tag, my_tag & hmask, hmask, hsize, min_mask, chain);
-                sh->pl_fl[j] = pl.flags; sh->pl_w2[j] = pl.w2_slot;
-                if (dbg) atomicAdd((unsigned long long *)&dbg[30], 1ULL);
-            }
-            if (dbg && j == 0) tm[11] += 1;
             TICK(6);
         }
+#undef ZONE_CHECK
+#undef CLAIM
         // ================================================================ batch epilogue
-        // a committed plan overwrote a slot of the ring that the sweep had not reached: cut the ring there
-        if (!batch_ended && steady) {
-            const int qc = sh->qcut;
-            if (qc != 0x7fffffff && rank == 0 && wid == 0) {
-                // first ring index whose slot is >= qc (32-ary search by one warp)
-                unsigned a = sh->e_idx, b = sh->e_cnt;
-                while (b - a > 32) {
-                    const unsigned len = b - a;
-                    const unsigned idx = a + (unsigned)(((unsigned long long)len * lane) / 32);
-                    const int v = sh->E[idx & (MRZ_EQ_CAP - 1)];
-                    const unsigned ge = __ballot_sync(FULL, v >= qc);
-                    if (!ge) a = a + (unsigned)(((unsigned long long)len * 31) / 32) + 1;
-                    else {
-                        const int l = __ffs(ge) - 1;
-                        if (l == 0) { b = a; break; }
-                        const unsigned na = a + (unsigned)(((unsigned long long)len * (l - 1)) / 32) + 1;
-                        b = a + (unsigned)(((unsigned long long)len * l) / 32) + 1;
-                        a = na;
-                    }
-                }
-                if (b > a) {
-                    const bool in = a + lane < b;
-                    const int v = in ? sh->E[(a + lane) & (MRZ_EQ_CAP - 1)] : 0x7fffffff;
-                    const unsigned ge = __ballot_sync(FULL, in && v >= qc);
-                    a = ge ? a + (__ffs(ge) - 1) : b;
-                }
-                if (lane == 0 && a != sh->e_cnt) { sh->e_cnt = a; sh->e_scan = qc; }
-            }
+        // a committed plan overwrote a slot of the ring that the sweep had not reached: cut the ring there (every CTA, its replica)
+        if (!batch_ended && steady && qacc != 0x7fffffff && wid == 0) {
+            const unsigned a = ring_lower_bound(sh, x.e_idx, x.e_cnt, qacc, lane);
+            if (lane == 0 && a != x.e_cnt) { x.e_cnt = a; x.e_scan = qacc; }
         }
-        csync(CL);
+        __syncthreads();
         TICK(7);
     }
+    csync(CL);
     if (j == 0 && dbg) {
         for (int q = 0; q < 12; q++) dbg[q] += tm[q];
     }
     if (j == 0) {
-        i64 p = sh->run.p;
-        const int err = sh->run.error;
+        i64 p = x.run.p;
+        const int err = x.run.error;
         if (!err && p < end) p = end;
-        st->p = p; st->last = sh->run.last; st->cur_p = sh->run.cur_p; st->cur_len = sh->run.cur_len; st->cur_ofs = sh->run.cur_ofs;
-        st->min_mask = sh->run.min_mask; st->ins_mask = sh->run.ins_mask; st->clean_ptr = sh->run.clean_ptr; st->count = sh->run.count;
-        st->victim_round = sh->run.vr;
-        st->tag_hits = sh->run.hits; st->tag_misses = sh->run.misses; st->inserts = sh->run.inserts; st->victim_events = sh->run.vevents;
-        st->n_ops = sh->run.nops; st->ntok = sh->run.ntok;
+        st->p = p; st->last = x.run.last; st->cur_p = x.run.cur_p; st->cur_len = x.run.cur_len; st->cur_ofs = x.run.cur_ofs;
+        st->min_mask = x.run.min_mask; st->ins_mask = x.run.ins_mask; st->clean_ptr = x.run.clean_ptr; st->count = x.run.count;
+        st->victim_round = x.run.vr;
+        st->tag_hits = x.run.hits; st->tag_misses = x.run.misses; st->inserts = x.run.inserts; st->victim_events = x.run.vevents;
+        st->n_ops = x.run.nops; st->ntok = x.run.ntok;
         st->err_a = sh->err_a; st->err_b = sh->err_b;
         if (err) st->error = err;
         else st->done = 1;
@@ -1652,3 +1779,4 @@ extern "C" int mrz_launch_automata(const AutoDesc *descs, int nclusters, int CL,
     return 0;
 #endif
 }
+

@@ -13,7 +13,8 @@ struct AutoDesc {
     i64 *ttag, *toff;     // the hash table: tags[] and offsets[]
     u64 *filt;            // tag filter
     u32 *gsum;            // group summary
-    unsigned *claim;      // per-slot claims of the current batch
+    unsigned *claim;      // per-slot claims of the current batch: two arrays of claim_stride entries, used alternately
+    i64 claim_stride;
     Token *toks;          // un-split match tokens (output)
     Shared *sh;
     AutoState *st;        // in: constants + initial state; out: final state

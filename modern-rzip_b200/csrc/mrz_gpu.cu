@@ -323,7 +323,7 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk, const mrz_co
     DA(ctx->d_gsum, (size_t)(ctx->tab_slots / 8 / 2 + 1024) * 4);   // 16-bit thermometer per 8 slots (automaton.cu GRP)
     ctx->filt_bits = c.filter_log2_words;
     DA(ctx->d_filt, (size_t)8 << ctx->filt_bits);
-    DA(ctx->d_claim, (size_t)(ctx->tab_slots + 32) * 4);
+    DA(ctx->d_claim, (size_t)(ctx->tab_slots + 32) * 4 * 2);    // two arrays (automaton.cu: alternating epochs)
     DA(ctx->d_sh, mrz_shared_bytes());
     DA(ctx->d_st, sizeof(AutoState));
     DA(ctx->d_tot, sizeof(EmitTotals));
@@ -489,13 +489,13 @@ static int run_phase_a_many(mrz_ctx *const *ctxs, int count, const i64 *ns, cons
             init_state(h, c, ns[todo[(size_t)q]], &prms[todo[(size_t)q]]);
             AutoDesc &d = droot->h_mb->desc[q];
             d.buf = r->d_buf; d.bmap = r->d_bmap; d.bsum = r->d_bsum; d.hidx = r->d_hidx;
-            d.ttag = c->d_tab; d.toff = c->d_tab + c->tab_slots + 32; d.filt = c->d_filt; d.gsum = c->d_gsum; d.claim = c->d_claim;
+            d.ttag = c->d_tab; d.toff = c->d_tab + c->tab_slots + 32; d.filt = c->d_filt; d.gsum = c->d_gsum; d.claim = c->d_claim; d.claim_stride = c->tab_slots + 32;
             d.toks = c->d_toks; d.sh = c->d_sh; d.st = c->d_st; d.dbg = c->d_dbg;
             CK(cudaMemcpyAsync(c->d_st, &h, sizeof h, cudaMemcpyHostToDevice, s));
             CK(cudaMemsetAsync(c->d_tab, 0, (size_t)(c->tab_slots + 32) * 16, s));  // rzip.c:518-519
             CK(cudaMemsetAsync(c->d_gsum, 0, (size_t)(c->tab_slots / 8 / 2 + 1024) * 4, s));
             CK(cudaMemsetAsync(c->d_filt, 0, (size_t)8 << c->filt_bits, s));
-            CK(cudaMemsetAsync(c->d_claim, 0xff, (size_t)(c->tab_slots + 32) * 4, s));
+            CK(cudaMemsetAsync(c->d_claim, 0xff, (size_t)(c->tab_slots + 32) * 4 * 2, s));
             if (c->d_dbg) CK(cudaMemsetAsync(c->d_dbg, 0, MRZ_NDBG * 8, s));
         }
         CK(cudaMemcpyAsync(droot->d_desc, droot->h_mb->desc, sizeof(AutoDesc) * (size_t)m, cudaMemcpyHostToDevice, s));

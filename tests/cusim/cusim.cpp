@@ -62,6 +62,12 @@ void sync_grid() {
     yield_to_scheduler();
 }
 
+void *map_shared_rank(void *p, int rank) {
+    Block &b = *blkp;
+    Block &o = block_pool[b.cluster * b.csize + rank];
+    return (char *)o.smem + ((char *)p - (char *)b.smem);
+}
+
 void sync_cluster() {
     Fiber *f = cur;
     Block &b = *blkp;
@@ -148,6 +154,20 @@ static void run_resident(int nblocks, int nthreads) {
             fprintf(stderr, "\n  block-barrier-waiters:");
             for (int i = 0, c = 0; i < total && c < 40; i++) if (fiber_pool[i].status == 1) { fprintf(stderr, " %d", i); c++; }
             fprintf(stderr, "\n");
+            {   // who waits where: (status, source line of the rendezvous) -> number of fibers
+                int seen = 0;
+                for (int i = 0; i < total && seen < 12; i++) {
+                    if (fiber_pool[i].status == 3) continue;
+                    bool first = true;
+                    for (int q = 0; q < i; q++)
+                        if (fiber_pool[q].status == fiber_pool[i].status && fiber_pool[q].line == fiber_pool[i].line) { first = false; break; }
+                    if (!first) continue;
+                    int cnt = 0;
+                    for (int q = i; q < total; q++) cnt += fiber_pool[q].status == fiber_pool[i].status && fiber_pool[q].line == fiber_pool[i].line;
+                    fprintf(stderr, "  %d fiber(s) with status %d at source line %d (first: fiber %d)\n", cnt, fiber_pool[i].status, fiber_pool[i].line, i);
+                    seen++;
+                }
+            }
             abort();
         }
     }

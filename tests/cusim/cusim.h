@@ -92,6 +92,7 @@ struct Fiber {
     volatile unsigned *wait_addr; unsigned wait_old;   // status 5: waiting for *wait_addr != wait_old
     uint3_ tid;
     int lane, warp;
+    int line;            // source line of the last barrier / warp collective this fiber entered (deadlock reports)
 };
 struct WarpSlot {
     uint64_t in[32], out[32];
@@ -119,6 +120,7 @@ void sync_grid();                    // called by ONE thread of every block
 // thread-block clusters: consecutive groups of `cl` blocks, all resident; barrier.cluster == sync_cluster()
 void launch_cluster(dim3 grid, dim3 block, int cl, size_t smem_bytes, const std::function<void()> &body);
 void sync_cluster();                 // called by ONE thread of every block of the cluster
+void *map_shared_rank(void *p, int rank);   // address of the same dynamic-shared-memory object in the block of `rank` of this cluster
 static inline int cluster_rank() { return blkp->crank; }
 static inline int cluster_size() { return blkp->csize; }
 // spin-wait of a cooperative kernel: the fiber sleeps until *addr != old (polled by the scheduler, no busy switching)
@@ -161,36 +163,45 @@ static inline WarpSlot &warp_exchange(unsigned mask, uint64_t v, int p) {
 #define blockDim (cusim::blkp->bdim)
 #define gridDim (cusim::blkp->gdim)
 
-static inline void __syncthreads() { cusim::sync_block(); }
-static inline void __syncwarp(unsigned mask = 0xffffffffu) { cusim::warp_exchange(mask, 0, 0); }
-static inline unsigned __ballot_sync(unsigned mask, int pred) { return cusim::warp_exchange(mask, 0, pred).out_ballot & mask; }
-static inline int __any_sync(unsigned mask, int pred) { return __ballot_sync(mask, pred) != 0; }
-static inline int __all_sync(unsigned mask, int pred) { return __ballot_sync(mask, pred) == mask; }
+static inline void cusim__syncthreads() { cusim::sync_block(); }
+static inline void cusim__syncwarp(unsigned mask = 0xffffffffu) { cusim::warp_exchange(mask, 0, 0); }
+static inline unsigned cusim__ballot_sync(unsigned mask, int pred) { return cusim::warp_exchange(mask, 0, pred).out_ballot & mask; }
+static inline int __any_sync(unsigned mask, int pred) { return cusim__ballot_sync(mask, pred) != 0; }
+static inline int __all_sync(unsigned mask, int pred) { return cusim__ballot_sync(mask, pred) == mask; }
 
 template <class T> static inline uint64_t cusim_bits(T v) { uint64_t b = 0; memcpy(&b, &v, sizeof v); return b; }
 template <class T> static inline T cusim_val(uint64_t b) { T v; memcpy(&v, &b, sizeof v); return v; }
-template <class T> static inline T __shfl_sync(unsigned mask, T v, int src, int width = 32) {
+template <class T> static inline T cusim__shfl_sync(unsigned mask, T v, int src, int width = 32) {
     int lane = cusim::cur->lane;
     int s = (lane & ~(width - 1)) | (src & (width - 1));
     return cusim_val<T>(cusim::warp_exchange(mask, cusim_bits(v), 0).out[s]);
 }
-template <class T> static inline T __shfl_up_sync(unsigned mask, T v, unsigned d, int width = 32) {
+template <class T> static inline T cusim__shfl_up_sync(unsigned mask, T v, unsigned d, int width = 32) {
     int lane = cusim::cur->lane;
     cusim::WarpSlot &w = cusim::warp_exchange(mask, cusim_bits(v), 0);
     int s = lane - (int)d;
     return (s < (lane & ~(width - 1))) ? v : cusim_val<T>(w.out[s]);
 }
-template <class T> static inline T __shfl_down_sync(unsigned mask, T v, unsigned d, int width = 32) {
+template <class T> static inline T cusim__shfl_down_sync(unsigned mask, T v, unsigned d, int width = 32) {
     int lane = cusim::cur->lane;
     cusim::WarpSlot &w = cusim::warp_exchange(mask, cusim_bits(v), 0);
     int s = lane + (int)d;
     return (s > (lane | (width - 1))) ? v : cusim_val<T>(w.out[s]);
 }
-template <class T> static inline T __shfl_xor_sync(unsigned mask, T v, int x, int width = 32) {
+template <class T> static inline T cusim__shfl_xor_sync(unsigned mask, T v, int x, int width = 32) {
     int lane = cusim::cur->lane;
     (void)width;
     return cusim_val<T>(cusim::warp_exchange(mask, cusim_bits(v), 0).out[lane ^ x]);
 }
+
+// every rendezvous records its source line in the fiber, so that a deadlock report can say who waits where
+#define __syncthreads() (cusim::cur->line = __LINE__, cusim__syncthreads())
+#define __syncwarp(...) (cusim::cur->line = __LINE__, cusim__syncwarp(__VA_ARGS__))
+#define __ballot_sync(...) (cusim::cur->line = __LINE__, cusim__ballot_sync(__VA_ARGS__))
+#define __shfl_sync(...) (cusim::cur->line = __LINE__, cusim__shfl_sync(__VA_ARGS__))
+#define __shfl_up_sync(...) (cusim::cur->line = __LINE__, cusim__shfl_up_sync(__VA_ARGS__))
+#define __shfl_down_sync(...) (cusim::cur->line = __LINE__, cusim__shfl_down_sync(__VA_ARGS__))
+#define __shfl_xor_sync(...) (cusim::cur->line = __LINE__, cusim__shfl_xor_sync(__VA_ARGS__))
 
 // ---------------------------------------------------------------- intrinsics
 static inline int __ffs(int x) { return __builtin_ffs(x); }
