@@ -61,7 +61,7 @@ typedef struct {
     int32_t threads;          /* threads per CTA: 64..512, multiple of 32; 0 = 256 */
     int32_t filter_log2_words;/* tag filter size: 2^x 64-bit words, 16..26; 0 = 24 (128 MiB) */
     int32_t profile;          /* 1: collect the automaton's phase counters (mrz_get_profile) */
-    int32_t token_divisor;    /* initial token capacity = max_chunk / divisor (grown on demand); 0 = 128 */
+    int32_t token_divisor;    /* initial token capacity = max_chunk / divisor (a chunk that needs more is redone with 8x); 0 = 1024 */
     int32_t poison;           /* debugging: fill every work buffer with 0xA5 at creation instead of leaving it as allocated */
     int32_t reserved[2];
 } mrz_config;
@@ -78,6 +78,9 @@ void mrz_config_default(mrz_config *cfg);
 int mrz_ctx_create(int device, int64_t max_chunk, mrz_ctx **out);
 int mrz_ctx_create_ex(int device, int64_t max_chunk, const mrz_config *cfg, mrz_ctx **out);
 void mrz_ctx_destroy(mrz_ctx *ctx);
+/* Change mrz_config.cluster_size of a context (and of launches it leads) after creation: a host that keeps several
+ * chunks of one device in flight sizes the clusters so that all their automata are resident at once. */
+int mrz_ctx_set_cluster(mrz_ctx *ctx, int cluster_size);
 
 /* hash_search (rzip.c:507-667) for one chunk, host buffers in and out.
  * Copies the chunk H2D, runs the kernels, copies stream 0 / stream 1 D2H.

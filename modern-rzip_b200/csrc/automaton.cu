@@ -54,7 +54,7 @@
 #include "automaton.h"
 
 #define FULL 0xffffffffu
-#define LK_XCAP 2048       // a candidate still matching after this many bytes is extended by the whole CTA
+#define LK_XCAP 4096       // a candidate still matching after this many bytes is extended by the whole CTA
 #define LK_XCAP2 (1 << 20)  // ... unless more than two candidates are that long: then the warps go on in parallel up to here
 #define LK_CAP 256         // equal-tag entries the CTA-wide lookup collects; more: the warp walk
 #define FWD_ITERS 6        // forwarding rounds per conflict phase; later collisions are planned again after the cut
@@ -183,7 +183,7 @@ struct XRes {
     i64 e_scan;              // slots in [run.clean_ptr, e_scan) have been examined for the ring
     unsigned e_idx, e_cnt;   // ring counters (monotonic)
     int ended, jumped, nlog, pos_after;
-    int wlog[MRZ_WLOG_CAP];  // (slot << 1) | zeroed
+    int wlog[MRZ_WLOG_CAP];  // (slot << 2) | (overwrote an entry that was due for sweeping) << 1 | zeroed
 };
 // Replica of the automaton's scalars, one per CTA, in shared memory.
 struct Rep {
@@ -224,7 +224,7 @@ struct Smem {
     unsigned long long wsum[40];
     unsigned long long cbase, ctotal;
     i64 lgp;                // CTA-local minimum for xmin
-    int lk_fe, lk_n, lmin, lq, lchg, pad;
+    int lk_fe, lk_fe2, lk_n, lmin, lq, lchg;
     int lk_pos[LK_CAP];     // CTA-wide lookup: positions (relative to the primary slot) of equal tags, ascending
     i64 lk_len[LK_CAP], lk_rev[LK_CAP], lk_off[LK_CAP];   // match_len results per candidate
     i64 lk_f[LK_CAP], lk_r[LK_CAP];                       // capped forward / backward lengths (first pass)
@@ -290,6 +290,56 @@ __device__ __forceinline__ unsigned long long cluster_excl_scan(unsigned long lo
 }
 struct NoExtra { __device__ __forceinline__ void operator()(unsigned long long) const {} };
 
+// Byte compare by one warp: the first mismatch between buf[a0 + f ..] and buf[b0 + f ..] (fwd) or between the bytes
+// before a0 - f and b0 - f (backwards) within the next G * 256 bytes, limited to maxlen, as (8-byte unit << 3 | byte in
+// unit) relative to f, or 0x7fffffff.  All 2 * G loads of a lane are issued before the first compare (the loop is
+// unrolled and the compares come after it): one memory round trip per call.
+template <int G>
+__device__ __forceinline__ int warp_cmp(const u8 *buf, i64 a0, i64 b0, i64 f, i64 maxlen, bool fwd, int lane) {
+    u64 x[G];
+#pragma unroll
+    for (int c = 0; c < G; c++) {
+        const i64 k = f + (i64)(c * 32 + lane) * 8;
+        x[c] = 0;
+        if (k < maxlen) x[c] = fwd ? ld_u64_unaligned(buf, a0 + k) ^ ld_u64_unaligned(buf, b0 + k)
+                                   : ld_u64_unaligned(buf, a0 - 8 - k) ^ ld_u64_unaligned(buf, b0 - 8 - k);
+    }
+    int first = 0x7fffffff;
+#pragma unroll
+    for (int c = G - 1; c >= 0; c--)
+        if (x[c]) first = ((c * 32 + lane) << 3) | (fwd ? ((__ffsll((long long)x[c]) - 1) >> 3) : (__clzll((long long)x[c]) >> 3));
+    for (int o = 16; o; o >>= 1) {
+        const int u = __shfl_xor_sync(FULL, first, o);
+        first = u < first ? u : first;
+    }
+    return first;
+}
+// Both directions from (a0, b0) in ONE round trip: forward limited to maxf, backwards to maxb.
+template <int G>
+__device__ __forceinline__ void warp_cmp2(const u8 *buf, i64 a0, i64 b0, i64 maxf, i64 maxb, int lane, int &ff, int &fr) {
+    u64 xf[G], xb[G];
+#pragma unroll
+    for (int c = 0; c < G; c++) {
+        const i64 k = (i64)(c * 32 + lane) * 8;
+        xf[c] = xb[c] = 0;
+        if (k < maxf) xf[c] = ld_u64_unaligned(buf, a0 + k) ^ ld_u64_unaligned(buf, b0 + k);
+        if (k < maxb) xb[c] = ld_u64_unaligned(buf, a0 - 8 - k) ^ ld_u64_unaligned(buf, b0 - 8 - k);
+    }
+    ff = fr = 0x7fffffff;
+#pragma unroll
+    for (int c = G - 1; c >= 0; c--) {
+        if (xf[c]) ff = ((c * 32 + lane) << 3) | ((__ffsll((long long)xf[c]) - 1) >> 3);
+        if (xb[c]) fr = ((c * 32 + lane) << 3) | (__clzll((long long)xb[c]) >> 3);
+    }
+    for (int o = 16; o; o >>= 1) {
+        const int u = __shfl_xor_sync(FULL, ff, o), v = __shfl_xor_sync(FULL, fr, o);
+        ff = u < ff ? u : ff;
+        fr = v < fr ? v : fr;
+    }
+}
+#define CMP_G 8                       // 8 x 256 bytes per warp step
+#define CMP_STEP (CMP_G * 256)
+
 // ---- the exact executor: one warp runs one op on the live table with the reference semantics -----
 struct Warp {
     // constants
@@ -327,56 +377,45 @@ struct Warp {
         __syncwarp();
     }
     // table writes of the serial path: lane 0 stores, the write is logged, the summary follows
-    __device__ __forceinline__ void write_slot(i64 slot, i64 off, i64 tag) {
+    // elig: the slot held an entry due for sweeping (rzip.c:267-269) - the only kind of slot the sweep ring can hold
+    __device__ __forceinline__ void write_slot(i64 slot, i64 off, i64 tag, bool elig = false) {
         if (lane == 0) {
             __stcg(toff + slot, off);
             __stcg(ttag + slot, tag);
             sum_lower(gsum, slot >> GRP_SHIFT, tag ? tz1c(tag) : 0);
-            if (nlog < MRZ_WLOG_CAP) wlog[nlog] = (int)(slot << 1) | (tag ? 0 : 1);
+            if (nlog < MRZ_WLOG_CAP) wlog[nlog] = (int)(slot << 2) | (elig ? 2 : 0) | (tag ? 0 : 1);
         }
         nlog++;
         __syncwarp();
     }
 
     // rzip.c:372-397.  Longest common prefix of buf[a0..] / buf[b0..] (fwd) or longest common suffix of buf[..a0) /
-    // buf[..b0), at most maxlen bytes.  The first step compares 256 bytes (most candidates fail there); a match that
-    // survives it is extended 4 KiB per step - 16 independent 8-byte compares per lane in flight.
+    // buf[..b0), at most maxlen bytes; 2 KiB per step, the 16 loads of a lane in flight together (warp_cmp).
     __device__ __forceinline__ i64 extend(i64 a0, i64 b0, i64 maxlen, bool fwd) {
         i64 f = 0;
-        int K = 1;
         while (f < maxlen) {
-            int first = 0x7fffffff;            // (chunk index << 3 | byte) of my first mismatch in this step
-            for (int c = K - 1; c >= 0; c--) {
-                const i64 k = f + (i64)(c * 32 + lane) * 8;
-                u64 x = 0;
-                if (k < maxlen) x = fwd ? ld_u64_unaligned(buf, a0 + k) ^ ld_u64_unaligned(buf, b0 + k)
-                                        : ld_u64_unaligned(buf, a0 - 8 - k) ^ ld_u64_unaligned(buf, b0 - 8 - k);
-                if (x) {
-                    const int nb = fwd ? ((__ffsll((long long)x) - 1) >> 3) : (__clzll((long long)x) >> 3);
-                    first = ((c * 32 + lane) << 3) | nb;
-                }
-            }
-            for (int o = 16; o; o >>= 1) {
-                const int u = __shfl_xor_sync(FULL, first, o);
-                first = u < first ? u : first;
-            }
+            const int first = warp_cmp<CMP_G>(buf, a0, b0, f, maxlen, fwd, lane);
             if (first != 0x7fffffff) {
                 f += (i64)(first >> 3) * 8 + (first & 7);
                 break;
             }
-            f += (i64)K * 256;
-            K = 16;
+            f += CMP_STEP;
         }
         return f > maxlen ? maxlen : f;
     }
     __device__ __forceinline__ i64 match_len(i64 p0, i64 op, i64 &rev) {
         rev = 0;
         if (op >= p0) return 0;
-        const i64 f = extend(p0, op, end - p0, true);
         const i64 lo = last > 0 ? last : 0;
         i64 maxb = p0 - lo;
         if (op < maxb) maxb = op;
-        const i64 r = extend(p0, op, maxb, false);
+        const i64 maxf = end - p0;
+        int ff, fr;
+        warp_cmp2<CMP_G>(buf, p0, op, maxf, maxb, lane, ff, fr);
+        i64 f = ff != 0x7fffffff ? (i64)(ff >> 3) * 8 + (ff & 7) : (maxf > CMP_STEP ? CMP_STEP + extend(p0 + CMP_STEP, op + CMP_STEP, maxf - CMP_STEP, true) : maxf);
+        i64 r = fr != 0x7fffffff ? (i64)(fr >> 3) * 8 + (fr & 7) : (maxb > CMP_STEP ? CMP_STEP + extend(p0 - CMP_STEP, op - CMP_STEP, maxb - CMP_STEP, false) : maxb);
+        if (f > maxf) f = maxf;
+        if (r > maxb) r = maxb;
         rev = r;
         const i64 tot = f + r;
         return tot < MRZ_MIN_MATCH ? 0 : tot;
@@ -451,7 +490,7 @@ struct Warp {
             i64 h = ct & hmask, round = 0, victim_h = 0, target = 0;
             i64 btm = (min_mask << 1) | 1;
             int ctz = tz1(ct);
-            bool displaced = false;
+            bool displaced = false, over_elig = false;
             i64 otag = 0;
             for (;;) {
                 i64 et = __ldcg(ttag + ((h + lane) & hmask));
@@ -483,7 +522,7 @@ struct Warp {
                 round += ne;
                 if (s < 32) {
                     target = (h + s) & hmask;
-                    if ((mbm >> s) & 1u) count--;      // rzip.c:267-269: due for cleaning, overwrite
+                    if ((mbm >> s) & 1u) { count--; over_elig = true; }      // rzip.c:267-269: due for cleaning, overwrite
                     else if ((lsm >> s) & 1u) {        // rzip.c:275-277: re-insert the occupant first
                         displaced = true;
                         otag = __shfl_sync(FULL, et, s);
@@ -501,7 +540,7 @@ struct Warp {
                 ct = otag;
                 continue;
             }
-            write_slot(target, coff, ct);
+            write_slot(target, coff, ct, over_elig);
             break;
         }
         while (sp > 0) {
@@ -614,7 +653,7 @@ struct Warp {
             if (stg == 0 || (stg & btm) != btm) {
                 __syncwarp();                          // every lane has read the table before lane 0 writes it
                 if (stg != 0) count--;                 // rzip.c:267-269
-                write_slot(sl, coff, ct);
+                write_slot(sl, coff, ct, stg != 0);
                 while (sp > 0) {
                     sp--;
                     write_slot(stk[3 * sp], stk[3 * sp + 2], stk[3 * sp + 1]);
@@ -881,23 +920,6 @@ __device__ __forceinline__ void refill_queue(Shared *sh, Smem *S, const i64 *tta
     }
 }
 
-// After a serial op (one thread of rank 0): bring the ring back in step with what the op wrote.
-__device__ __forceinline__ void sync_queue(Shared *sh, XRes *x, const int *wlog, int nlog) {
-    for (int w = 0; w < nlog; w++) {
-        const int sl = wlog[w] >> 1;
-        if (wlog[w] & 1) {                       // zeroed by clean_one: consume the ring up to it
-            while (x->e_idx != x->e_cnt && LDG_(sh->E[x->e_idx & (MRZ_EQ_CAP - 1)]) <= sl) x->e_idx++;
-        } else if (sl < x->e_scan) {             // overwritten by an insert: if queued, cut the ring there
-            unsigned a = x->e_idx, b = x->e_cnt;
-            while (a != b) {
-                const unsigned m = a + (b - a) / 2;
-                if (LDG_(sh->E[m & (MRZ_EQ_CAP - 1)]) < sl) a = m + 1; else b = m;
-            }
-            if (a != x->e_cnt && LDG_(sh->E[a & (MRZ_EQ_CAP - 1)]) == sl) { x->e_cnt = a; x->e_scan = sl; }
-        }
-    }
-}
-
 // First ring index in [a, b) whose slot is >= key (b if none); 32-ary search by one warp over the ring in global memory.
 __device__ __forceinline__ unsigned ring_lower_bound(const Shared *sh, unsigned a, unsigned b, int key, int lane) {
     while (b - a > 32) {
@@ -918,6 +940,24 @@ __device__ __forceinline__ unsigned ring_lower_bound(const Shared *sh, unsigned 
     const int v = in ? LDG_(sh->E[(a + lane) & (MRZ_EQ_CAP - 1)]) : 0x7fffffff;
     const unsigned ge = __ballot_sync(FULL, in && v >= key);
     return ge ? a + (__ffs(ge) - 1) : b;
+}
+
+// After a serial op (warp 0 of rank 0, all lanes): bring the ring back in step with what the op wrote.  Only a
+// sweep step (zeroed) or an insert over an entry that was due for sweeping can touch a slot of the ring.
+__device__ __forceinline__ void sync_queue(Shared *sh, XRes *x, const int *wlog, int nlog, int lane) {
+    for (int w = 0; w < nlog; w++) {
+        const int e = wlog[w], sl = e >> 2;
+        unsigned e_idx = x->e_idx, e_cnt = x->e_cnt;
+        if (e & 1) {                             // zeroed by clean_one: consume the ring up to it
+            if (e_idx != e_cnt) e_idx = ring_lower_bound(sh, e_idx, e_cnt, sl + 1, lane);
+            if (lane == 0) x->e_idx = e_idx;
+        } else if ((e & 2) && sl < x->e_scan && e_idx != e_cnt) {   // overwritten by an insert: if queued, cut the ring there
+            const unsigned a = ring_lower_bound(sh, e_idx, e_cnt, sl, lane);
+            const bool hit = a != e_cnt && LDG_(sh->E[a & (MRZ_EQ_CAP - 1)]) == sl;
+            if (hit && lane == 0) { x->e_cnt = a; x->e_scan = sl; }
+        }
+        __syncwarp();
+    }
 }
 
 // First op index in [a, b) whose position is > p (b if none); 32-ary search by one warp over b_pos in global memory.
@@ -970,6 +1010,49 @@ __device__ __forceinline__ i64 cta_extend(Smem *S, const u8 *buf, i64 a0, i64 b0
         f += (i64)4 * T * 8;
     }
     return f > maxlen ? maxlen : f;
+}
+
+// single_match_len's two scans (rzip.c:372-397) for ONE candidate by the whole CTA, both directions at once: the lower
+// half of the threads compares forwards from (a0, b0), the upper half backwards, 16 * T bytes per direction and step,
+// all loads of a step in flight together; a step is one memory round trip and three block barriers.
+__device__ __forceinline__ void cta_cmp2(Smem *S, const u8 *buf, i64 a0, i64 b0, i64 maxf, i64 maxb, i64 &f_out, i64 &r_out) {
+    const int tid = threadIdx.x, T2 = blockDim.x >> 1;
+    const bool back = tid >= T2;
+    const int t = back ? tid - T2 : tid;
+    i64 f = 0, r = 0;
+    bool fdone = maxf <= 0, rdone = maxb <= 0;
+    while (!(fdone && rdone)) {
+        if (tid == 0) { S->lk_fe = 0x7fffffff; S->lk_fe2 = 0x7fffffff; }
+        __syncthreads();
+        const bool active = back ? !rdone : !fdone;
+        const i64 base = back ? r : f, lim = back ? maxb : maxf;
+        u64 x[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const i64 k = base + (i64)(c * T2 + t) * 8;
+            x[c] = 0;
+            if (active && k < lim) x[c] = back ? ld_u64_unaligned(buf, a0 - 8 - k) ^ ld_u64_unaligned(buf, b0 - 8 - k)
+                                              : ld_u64_unaligned(buf, a0 + k) ^ ld_u64_unaligned(buf, b0 + k);
+        }
+        int first = 0x7fffffff;
+#pragma unroll
+        for (int c = 3; c >= 0; c--)
+            if (x[c]) first = ((c * T2 + t) << 3) | (back ? (__clzll((long long)x[c]) >> 3) : ((__ffsll((long long)x[c]) - 1) >> 3));
+        if (first != 0x7fffffff) atomicMin(back ? &S->lk_fe2 : &S->lk_fe, first);
+        __syncthreads();
+        const int rf = S->lk_fe, rr = S->lk_fe2;
+        __syncthreads();
+        if (!fdone) {
+            if (rf != 0x7fffffff) { f += (i64)(rf >> 3) * 8 + (rf & 7); fdone = true; }
+            else { f += (i64)4 * T2 * 8; fdone = f >= maxf; }
+        }
+        if (!rdone) {
+            if (rr != 0x7fffffff) { r += (i64)(rr >> 3) * 8 + (rr & 7); rdone = true; }
+            else { r += (i64)4 * T2 * 8; rdone = r >= maxb; }
+        }
+    }
+    f_out = f > maxf ? maxf : f;
+    r_out = r > maxb ? maxb : r;
 }
 
 // The 64-bit tag of position p (rzip.c:348-358) from the bytes: two 256-bit loads, 31 look-ups in shared memory.
@@ -1183,6 +1266,9 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 x.gp = g;
             }
         }
+#ifdef MRZ_CUSIM
+        if (j == 0 && getenv("CUSIM_GATHER_LOG")) fprintf(stderr, "G %lld %lld %d %d %lld\n", (long long)lo, (long long)x.gp, nr, kgate, (long long)p_now);
+#endif
         if (nr == 0) { __syncthreads(); TICK(1); continue; }
         i64 my_pos = 0, my_tag = 0, prev1 = -1, prev2 = -1;
         if (j < nr) {
@@ -1230,6 +1316,10 @@ k_automaton(const AutoDesc *__restrict__ descs) {
         int pre0 = 0;                // the prefix sums in pre[] cover the ops of [pre0, nr)
         bool need_conflict = true;   // plans were made since the last round of claims
         bool batch_ended = false;
+#ifdef MRZ_CUSIM
+        const i64 dbg_nops0 = x.run.nops;   // emulator build: every op of the batch is accounted for exactly once
+        int dbg_done = 0, dbg_skip = 0;
+#endif
         int qacc = 0x7fffffff;       // smallest ring slot a committed plan overwrote (the ring is cut there at the end of the batch)
         i64 w_lo = x.run.clean_ptr, w_hi = steady ? x.e_scan : w_lo, s_safe = w_lo - 1;
         unsigned long long incl = 0;
@@ -1456,6 +1546,16 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 __stcg(toff + sl, (i64)0);
                 sum_lower(gsum, sl >> GRP_SHIFT, 0);
             }
+#ifdef MRZ_CUSIM
+            {   // debugging aid: CUSIM_OPLOG=<file> records the position of every op that runs (committed or executed)
+                static FILE *oplog = getenv("CUSIM_OPLOG") ? fopen(getenv("CUSIM_OPLOG"), "wb") : nullptr;
+                if (oplog && j >= pos && j < k) fwrite(&my_pos, 8, 1, oplog);
+                if (oplog && k_exact && k < nr && j == k) { fwrite(&my_pos, 8, 1, oplog); fflush(oplog); }
+            }
+            dbg_done += k - pos;
+            if (j == 0 && k > pos && (int)PK_V(d) != k - pos)
+                fprintf(stderr, "ACCOUNTING: commit [%d,%d) of nr %d counts %u ops (heavy %d pre0 %d)\n", pos, k, nr, PK_V(d), (int)heavy, pre0);
+#endif
             if (tid == 0 && k > pos) {           // every CTA applies the same update to its replica
                 x.run.count = Tk - cleans;
                 x.run.inserts += PK_I(d);
@@ -1483,121 +1583,152 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 // walked 4*T slots per step, equal tags are collected in slot order, and the warps share the match_len calls
                 if (rank == 0) {
                     int pre_n = -2;   // -2: the filter says no equal tag; -1: ask / walk on the warp; >= 0: candidates compared
+                    const i64 c_x0 = clock64();
                     const i64 tk = LDG_(sh->b_tag[k]), pk = LDG_(sh->b_pos[k]);
                     const i64 c_lk0 = clock64();
-                    if (filt_query(filt, tk)) {
-                        pre_n = -1;
+                    i64 c_lk1 = c_lk0, c_lk2 = c_lk0;
+                    if (dbg && tid == 0) dbg[53] += c_lk0 - c_x0;
+                    {
+                        // ONE round trip: the filter word and the first 4*T slots of the probe sequence, tags and offsets alike
                         const i64 h = tk & hmask;
-                        if (tid == 0) S->lk_fe = 0x7fffffff;
-                        __syncthreads();
-                        int n_tot = 0;
-                        bool found = false;
-                        for (int base = 0;; base += T * 4) {
-                            i64 et[4];
+                        u64 fw, fb;
+                        filt_hash(filt, tk, fw, fb);
+                        const u64 fword = __ldcg(filt.w + fw);
+                        i64 et[4], eo[4];
 #pragma unroll
-                            for (int q = 0; q < 4; q++) et[q] = __ldcg(ttag + ((h + base + tid * 4 + q) & hmask));
-                            unsigned eq4 = 0;
+                        for (int q = 0; q < 4; q++) et[q] = __ldcg(ttag + ((h + tid * 4 + q) & hmask));
 #pragma unroll
-                            for (int q = 0; q < 4; q++) {
-                                if (et[q] == 0) atomicMin(&S->lk_fe, base + tid * 4 + q);
-                                else if (et[q] == tk) eq4 |= 1u << q;
-                            }
+                        for (int q = 0; q < 4; q++) eo[q] = __ldcg(toff + ((h + tid * 4 + q) & hmask));
+                        if ((fword & fb) == fb) {
+                            pre_n = -1;
+                            if (tid == 0) S->lk_fe = 0x7fffffff;
                             __syncthreads();
-                            const int fe = S->lk_fe;
+                            int n_tot = 0;
+                            bool found = false;
+                            for (int base = 0;; base += T * 4) {
+                                if (base) {
 #pragma unroll
-                            for (int q = 0; q < 4; q++)
-                                if (base + tid * 4 + q >= fe) eq4 &= ~(1u << q);   // beyond the first empty slot: not on the walk
-                            unsigned long long total;
-                            int ex = (int)block_excl_scan((unsigned long long)__popc(eq4), S->wsum, total);
-                            for (int q = 0; q < 4; q++)
-                                if ((eq4 >> q) & 1u) {
-                                    if (n_tot + ex < LK_CAP) S->lk_pos[n_tot + ex] = base + tid * 4 + q;
-                                    ex++;
+                                    for (int q = 0; q < 4; q++) et[q] = __ldcg(ttag + ((h + base + tid * 4 + q) & hmask));
+#pragma unroll
+                                    for (int q = 0; q < 4; q++) eo[q] = __ldcg(toff + ((h + base + tid * 4 + q) & hmask));
                                 }
-                            n_tot += (int)total;
-                            found = fe != 0x7fffffff;
-                            if (found || n_tot > LK_CAP || base + T * 4 >= hsize) break;
-                        }
-                        __syncthreads();
-                        if (found && n_tot <= LK_CAP) {
-                            // single_match_len (rzip.c:372-397) per candidate: the warps share the candidates for the first
-                            // LK_XCAP bytes either side; whatever still matches there is extended by the whole CTA
-                            w.last = x.run.last;
-                            const i64 lo_m = w.last > 0 ? w.last : 0;
-                            const i64 maxf = end - pk;
-                            const int NW = T >> 5;
+                                unsigned eq4 = 0;
+#pragma unroll
+                                for (int q = 0; q < 4; q++) {
+                                    if (et[q] == 0) atomicMin(&S->lk_fe, base + tid * 4 + q);
+                                    else if (et[q] == tk) eq4 |= 1u << q;
+                                }
+                                __syncthreads();
+                                const int fe = S->lk_fe;
+#pragma unroll
+                                for (int q = 0; q < 4; q++)
+                                    if (base + tid * 4 + q >= fe) eq4 &= ~(1u << q);   // beyond the first empty slot: not on the walk
+                                unsigned long long total;
+                                int ex = (int)block_excl_scan((unsigned long long)__popc(eq4), S->wsum, total);
+#pragma unroll
+                                for (int q = 0; q < 4; q++)
+                                    if ((eq4 >> q) & 1u) {
+                                        if (n_tot + ex < LK_CAP) { S->lk_pos[n_tot + ex] = base + tid * 4 + q; S->lk_off[n_tot + ex] = eo[q]; }
+                                        ex++;
+                                    }
+                                n_tot += (int)total;
+                                found = fe != 0x7fffffff;
+                                if (found || n_tot > LK_CAP || base + T * 4 >= hsize) break;
+                            }
                             if (tid == 0) S->lk_n = 0;      // candidates still matching at the cap
                             __syncthreads();
-                            for (int q = wid; q < n_tot; q += NW) {
-                                const i64 off = __ldcg(toff + ((h + S->lk_pos[q]) & hmask));
-                                i64 f = 0, r = 0;
-                                if (off < pk) {
-                                    i64 maxb = pk - lo_m;
-                                    if (off < maxb) maxb = off;
-                                    const i64 mf = maxf < LK_XCAP ? maxf : LK_XCAP, mb = maxb < LK_XCAP ? maxb : LK_XCAP;
-                                    {   // the first 256 bytes of both directions in one round trip
-                                        const i64 kk = lane * 8;
-                                        u64 xf = 0, xb = 0;
-                                        if (kk < mf) xf = ld_u64_unaligned(buf, pk + kk) ^ ld_u64_unaligned(buf, off + kk);
-                                        if (kk < mb) xb = ld_u64_unaligned(buf, pk - 8 - kk) ^ ld_u64_unaligned(buf, off - 8 - kk);
-                                        unsigned mm = __ballot_sync(FULL, xf != 0);
-                                        if (mm) {
-                                            const int l = __ffs(mm) - 1;
-                                            int nb = xf ? ((__ffsll((long long)xf) - 1) >> 3) : 8;
-                                            nb = __shfl_sync(FULL, nb, l);
-                                            f = l * 8 + nb;
-                                        } else
-                                            f = mf > 256 ? 256 + w.extend(pk + 256, off + 256, mf - 256, true) : mf;
-                                        if (f > mf) f = mf;
-                                        mm = __ballot_sync(FULL, xb != 0);
-                                        if (mm) {
-                                            const int l = __ffs(mm) - 1;
-                                            int nb = xb ? (__clzll((long long)xb) >> 3) : 8;
-                                            nb = __shfl_sync(FULL, nb, l);
-                                            r = l * 8 + nb;
-                                        } else
-                                            r = mb > 256 ? 256 + w.extend(pk - 256, off - 256, mb - 256, false) : mb;
-                                        if (r > mb) r = mb;
+                            c_lk1 = c_lk2 = clock64();
+                            if (found && n_tot <= LK_CAP) {
+                                // single_match_len (rzip.c:372-397) per candidate: the warps share the candidates; the first 2 KiB of
+                                // both directions come in one round trip, LK_XCAP bytes either side by the warp; whatever still matches
+                                // there is extended by the whole CTA
+                                w.last = x.run.last;
+                                const i64 lo_m = w.last > 0 ? w.last : 0;
+                                const i64 maxf = end - pk;
+                                const int NW = T >> 5;
+                                if (n_tot <= NW) {
+                                    // few candidates (the usual case): one after the other, each by the whole CTA, complete
+                                    for (int q = 0; q < n_tot; q++) {
+                                        const i64 off = S->lk_off[q];
+                                        i64 f = 0, r = 0;
+                                        if (off < pk) {
+                                            i64 maxb = pk - lo_m;
+                                            if (off < maxb) maxb = off;
+                                            cta_cmp2(S, buf, pk, off, maxf, maxb, f, r);
+                                        }
+                                        if (tid == 0) { S->lk_len[q] = (off < pk && f + r >= MRZ_MIN_MATCH) ? f + r : 0; S->lk_rev[q] = r; }
                                     }
-                                    if (lane == 0 && ((f == LK_XCAP && maxf > LK_XCAP) || (r == LK_XCAP && maxb > LK_XCAP))) atomicAdd(&S->lk_n, 1);
-                                }
-                                if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; S->lk_off[q] = off; }
-                            }
-                            __syncthreads();
-                            // many long candidates (dense repeats, deep chains): the warps carry on in parallel, one candidate
-                            // each, up to LK_XCAP2; the whole CTA then only extends what is still matching there
-                            const i64 cap = S->lk_n > 2 ? (i64)LK_XCAP2 : (i64)LK_XCAP;
-                            if (cap != LK_XCAP) {
+                                    __syncthreads();
+                                    c_lk2 = clock64();
+                                } else {
                                 for (int q = wid; q < n_tot; q += NW) {
                                     const i64 off = S->lk_off[q];
-                                    if (off >= pk) continue;
-                                    i64 f = S->lk_f[q], r = S->lk_r[q];
-                                    i64 maxb = pk - lo_m;
-                                    if (off < maxb) maxb = off;
-                                    if (f == LK_XCAP && maxf > LK_XCAP) f += w.extend(pk + LK_XCAP, off + LK_XCAP, (maxf < cap ? maxf : cap) - LK_XCAP, true);
-                                    if (r == LK_XCAP && maxb > LK_XCAP) r += w.extend(pk - LK_XCAP, off - LK_XCAP, (maxb < cap ? maxb : cap) - LK_XCAP, false);
-                                    __syncwarp();
+                                    i64 f = 0, r = 0;
+                                    if (off < pk) {
+                                        i64 maxb = pk - lo_m;
+                                        if (off < maxb) maxb = off;
+                                        const i64 mf = maxf < LK_XCAP ? maxf : LK_XCAP, mb = maxb < LK_XCAP ? maxb : LK_XCAP;
+                                        int ff, fr;
+                                        warp_cmp2<CMP_G>(buf, pk, off, mf, mb, lane, ff, fr);
+                                        f = ff != 0x7fffffff ? (i64)(ff >> 3) * 8 + (ff & 7)
+                                                             : (mf > CMP_STEP ? CMP_STEP + w.extend(pk + CMP_STEP, off + CMP_STEP, mf - CMP_STEP, true) : mf);
+                                        r = fr != 0x7fffffff ? (i64)(fr >> 3) * 8 + (fr & 7)
+                                                             : (mb > CMP_STEP ? CMP_STEP + w.extend(pk - CMP_STEP, off - CMP_STEP, mb - CMP_STEP, false) : mb);
+                                        if (f > mf) f = mf;
+                                        if (r > mb) r = mb;
+                                        if (lane == 0 && ((f == LK_XCAP && maxf > LK_XCAP) || (r == LK_XCAP && maxb > LK_XCAP))) atomicAdd(&S->lk_n, 1);
+                                    }
                                     if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; }
                                 }
                                 __syncthreads();
-                            }
-                            for (int q = 0; q < n_tot; q++) {
-                                const i64 off = S->lk_off[q];
-                                i64 f = S->lk_f[q], r = S->lk_r[q], m = 0;
-                                if (off < pk) {
-                                    i64 maxb = pk - lo_m;
-                                    if (off < maxb) maxb = off;
-                                    if (f == cap && maxf > cap) f += cta_extend(S, buf, pk + cap, off + cap, maxf - cap, true);
-                                    if (r == cap && maxb > cap) r += cta_extend(S, buf, pk - cap, off - cap, maxb - cap, false);
-                                    m = f + r < MRZ_MIN_MATCH ? 0 : f + r;
+                                c_lk2 = clock64();
+                                // many long candidates (dense repeats, deep chains): the warps carry on in parallel, one candidate
+                                // each, up to LK_XCAP2; the whole CTA then only extends what is still matching there
+                                const i64 cap = S->lk_n > 2 ? (i64)LK_XCAP2 : (i64)LK_XCAP;
+                                if (cap != LK_XCAP) {
+                                    for (int q = wid; q < n_tot; q += NW) {
+                                        const i64 off = S->lk_off[q];
+                                        if (off >= pk) continue;
+                                        i64 f = S->lk_f[q], r = S->lk_r[q];
+                                        i64 maxb = pk - lo_m;
+                                        if (off < maxb) maxb = off;
+                                        if (f == LK_XCAP && maxf > LK_XCAP) f += w.extend(pk + LK_XCAP, off + LK_XCAP, (maxf < cap ? maxf : cap) - LK_XCAP, true);
+                                        if (r == LK_XCAP && maxb > LK_XCAP) r += w.extend(pk - LK_XCAP, off - LK_XCAP, (maxb < cap ? maxb : cap) - LK_XCAP, false);
+                                        __syncwarp();
+                                        if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; }
+                                    }
+                                    __syncthreads();
                                 }
-                                if (tid == 0) { S->lk_len[q] = m; S->lk_rev[q] = r; }
+                                if (S->lk_n == 0) {          // the usual case: nothing reaches the cap, no CTA-wide extension
+                                    for (int q = tid; q < n_tot; q += T) {
+                                        const i64 f = S->lk_f[q], r = S->lk_r[q];
+                                        S->lk_len[q] = (S->lk_off[q] < pk && f + r >= MRZ_MIN_MATCH) ? f + r : 0;
+                                        S->lk_rev[q] = r;
+                                    }
+                                } else
+                                for (int q = 0; q < n_tot; q++) {
+                                    const i64 off = S->lk_off[q];
+                                    i64 f = S->lk_f[q], r = S->lk_r[q], m = 0;
+                                    if (off < pk) {
+                                        i64 maxb = pk - lo_m;
+                                        if (off < maxb) maxb = off;
+                                        if (f == cap && maxf > cap) f += cta_extend(S, buf, pk + cap, off + cap, maxf - cap, true);
+                                        if (r == cap && maxb > cap) r += cta_extend(S, buf, pk - cap, off - cap, maxb - cap, false);
+                                        m = f + r < MRZ_MIN_MATCH ? 0 : f + r;
+                                    }
+                                    if (tid == 0) { S->lk_len[q] = m; S->lk_rev[q] = r; }
+                                }
+                                }
+                                __syncthreads();
+                                pre_n = n_tot;
                             }
-                            __syncthreads();
-                            pre_n = n_tot;
                         }
                     }
-                    if (dbg && tid == 0) { dbg[18] += clock64() - c_lk0; dbg[19] += pre_n != -2; }
+                    if (dbg && tid == 0) {
+                        const i64 c_now = clock64();
+                        dbg[18] += c_now - c_lk0; dbg[19] += pre_n != -2;
+                        dbg[50] += c_lk1 - c_lk0; dbg[51] += c_lk2 - c_lk1; dbg[52] += c_now - c_lk2;
+                    }
                     // ---- op k on the live table, reference semantics (warp 0), on the local replica
                     if (wid == 0) {
                         w.load(x.run);
@@ -1606,9 +1737,14 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                         if (steady) hint = (x.e_cnt != x.e_idx) ? (i64)LDG_(sh->E[x.e_idx & (MRZ_EQ_CAP - 1)]) : (x.e_scan > hint ? x.e_scan : hint);
                         w.clean_hint = hint;
                         w.p = pk;
+                        const i64 c_op0 = clock64();
                         const bool jumped = w.op(pk, tk, S->stk, pre_n, S->lk_len, S->lk_rev, S->lk_off, S->lk_pos);
+                        const i64 c_op1 = clock64();
                         w.clean_hint = 0;
                         w.store(x.run);
+#ifdef MRZ_CUSIM
+                        if (lane == 0 && getenv("CUSIM_GATHER_LOG")) fprintf(stderr, "X %lld %lld %d %lld %lld\n", (long long)pk, (long long)w.p, (int)jumped, (long long)w.min_mask, (long long)w.ins_mask);
+#endif
                         const bool mask_changed = w.min_mask != min_mask || w.ins_mask != ins_mask;
                         const bool overflow = w.nlog > MRZ_WLOG_CAP;
                         int kp = nr;
@@ -1616,24 +1752,24 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                         // plan's stop slot can spoil it): carry on with the first op past the jump
                         // (a short match can end BEFORE op k: p goes back, rzip.c:597: the batch ends)
                         if (jumped && !mask_changed && !overflow && !w.error && w.p >= pk) kp = pos_upper_bound(sh, k + 1, nr, w.p, lane);
+                        const bool ends = mask_changed || overflow || w.error || (jumped && kp >= nr);
                         if (lane == 0) {
                             x.jumped = jumped;
                             x.nlog = overflow ? 0 : w.nlog;
-                            if (mask_changed || overflow || w.error || (jumped && kp >= nr)) {
-                                x.ended = 1;
+                            x.ended = ends;
+                            if (ends) {
                                 x.e_idx = x.e_cnt = 0; x.e_scan = w.clean_ptr;    // rebuild the ring
                                 // what this batch had gathered behind p is gathered again (a jump past the batch keeps the cursor)
                                 if (w.p + 1 < x.gp) x.gp = w.p + 1;
-                            } else {
-                                x.ended = 0;
-                                if (steady) {
-                                    sync_queue(sh, &x, x.wlog, w.nlog);
-                                    if (x.e_cnt == x.e_idx && x.e_scan < w.clean_ptr) x.e_scan = w.clean_ptr;
-                                }
+                            } else
                                 x.pos_after = jumped ? kp : k + 1;
-                            }
                         }
                         __syncwarp();
+                        if (!ends && steady) {
+                            sync_queue(sh, &x, x.wlog, w.nlog, lane);
+                            if (lane == 0 && x.e_cnt == x.e_idx && x.e_scan < w.clean_ptr) x.e_scan = w.clean_ptr;
+                            __syncwarp();
+                        }
                         // the result goes into every other replica
                         const int nwords = (int)(sizeof(XRes) / 8);
                         const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&x);
@@ -1641,6 +1777,7 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                             volatile unsigned long long *dst = reinterpret_cast<volatile unsigned long long *>(remote_ptr(&x, r));
                             for (int q = lane; q < nwords; q += 32) dst[q] = src[q];
                         }
+                        if (dbg && lane == 0) { dbg[54] += c_op1 - c_op0; dbg[55] += clock64() - c_op1; }
                     }
                 }
                 csync(CL);
@@ -1650,6 +1787,9 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 // window this batch was planned with
                 if (steady && x.e_scan < w_hi) refill_queue(sh, S, ttag, btm, w_hi, MRZ_EQ_CAP, CL, rank, j, B);
                 const int npos = x.pos_after;   // k + 1, or the first op past an emission's jump (the ops in between never run)
+#ifdef MRZ_CUSIM
+                dbg_done += 1; dbg_skip += npos - k - 1;
+#endif
                 // later plans that read a slot this op wrote are no longer valid; nor is its twin's plan
                 if (j == npos && (pl.flags & F_FOLLOW)) pl.flags |= F_CONF;
                 if (j >= npos && j < nr)   // a plan forwarded over the claim of op k / of a skipped op assumed that op's planned write
@@ -1659,7 +1799,7 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 if (j >= npos && j < nr && !(pl.flags & (F_COMPLEX | F_CONF))) {
                     const int nl = x.nlog;
                     for (int q = 0; q < nl; q++) {
-                        const int sl = x.wlog[q] >> 1;
+                        const int sl = x.wlog[q] >> 2;
                         bool hit = sl == pl.w2_slot || ((pl.flags & F_W1) && sl == pl.w1_slot);
                         for (int dd = 0; dd < pl.ndep; dd++) hit = hit || sl == pl.dep_slot[dd];
                         if (hit) { pl.flags |= F_CONF; break; }
@@ -1688,6 +1828,16 @@ k_automaton(const AutoDesc *__restrict__ descs) {
         }
 #undef ZONE_CHECK
 #undef CLAIM
+#ifdef MRZ_CUSIM
+        if (j == 0 && !batch_ended && (dbg_done + dbg_skip != nr || x.run.nops - dbg_nops0 != dbg_done))
+            fprintf(stderr, "ACCOUNTING: batch of %d ops: %d done + %d skipped, n_ops grew by %lld\n", nr, dbg_done, dbg_skip, (long long)(x.run.nops - dbg_nops0));
+        if (j == 0 && batch_ended && x.run.nops - dbg_nops0 != dbg_done + 1)
+            fprintf(stderr, "ACCOUNTING: ended batch of %d ops: %d done + the cut op, n_ops grew by %lld\n", nr, dbg_done, (long long)(x.run.nops - dbg_nops0));
+        {   // between batches: no candidate may lie between the last position handled and the next batch's first
+            static i64 dbg_last_handled = -1;
+            if (j == 0) dbg_last_handled = batch_ended ? x.run.p : -1;
+        }
+#endif
         // ================================================================ batch epilogue
         // a committed plan overwrote a slot of the ring that the sweep had not reached: cut the ring there (every CTA, its replica)
         if (!batch_ended && steady && qacc != 0x7fffffff && wid == 0) {

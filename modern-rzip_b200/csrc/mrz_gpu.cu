@@ -26,6 +26,7 @@ size_t mrz_automaton_smem_bytes();
 int mrz_launch_automata(const AutoDesc *, int, int, int, cudaStream_t);
 int mrz_max_active_clusters(int, int);
 void mrz_crc_upload_consts(const void *, cudaStream_t);
+int mrz_crc_ensure_device(int, cudaStream_t);
 void mrz_launch_crc(const u8 *, i64, u32 *, u32 *, u32 *, cudaStream_t, int *);
 void mrz_launch_exclusive_scan(const i64 *, i64 *, i64, i64 *, i64 *, cudaStream_t, int *);
 void mrz_launch_item_sizes(const Token *, i64, i64, int, i64 *, i64 *, EmitTotals *, cudaStream_t);
@@ -168,6 +169,22 @@ static void crc_host_init() {
 #endif
 }
 
+// The CRC constants live in __constant__ memory: uploaded once per device, on a stream, complete before anyone launches.
+extern "C" int mrz_crc_ensure_device(int device, cudaStream_t s) {
+    crc_host_init();
+#ifndef MRZ_CUSIM
+    std::lock_guard<std::mutex> g(g_dev_mu);
+    if (g_crc_on_device[device & 63]) return 0;
+    mrz_crc_upload_consts(&g_crc, s);
+    if (cudaStreamSynchronize(s) != cudaSuccess) return MRZ_E_CUDA;
+    g_crc_on_device[device & 63] = true;
+#else
+    (void)device;
+    mrz_crc_upload_consts(&g_crc, s);
+#endif
+    return 0;
+}
+
 // ---- library -----------------------------------------------------------------------------------
 extern "C" const char *mrz_version(void) { return "mrz_gpu 0.2 (sm_100a, cluster automaton)"; }
 
@@ -273,7 +290,7 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk, const mrz_co
     if (c.threads < 32 || c.threads > MRZ_MAXT || (c.threads & 31)) { ctx->err = "mrz_config.threads must be a multiple of 32 in 32..512"; return MRZ_E_ARG; }
     if (c.filter_log2_words == 0) c.filter_log2_words = 24;
     if (c.filter_log2_words < 10 || c.filter_log2_words > 26) { ctx->err = "mrz_config.filter_log2_words must be in 10..26"; return MRZ_E_ARG; }
-    if (c.token_divisor == 0) c.token_divisor = 128;
+    if (c.token_divisor == 0) c.token_divisor = 1024;
     if (c.token_divisor < 31) { ctx->err = "mrz_config.token_divisor must be >= 31"; return MRZ_E_ARG; }
     {
         int sms = 0;
@@ -283,18 +300,7 @@ static int ctx_create_impl(mrz_ctx *ctx, int device, i64 max_chunk, const mrz_co
     crc_host_init();
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     for (auto &e : ctx->ev) CK(cudaEventCreate(&e));
-#ifndef MRZ_CUSIM
-    {   // the CRC constants live in __constant__ memory: once per device, on a stream, and complete before anyone launches
-        std::lock_guard<std::mutex> g(g_dev_mu);
-        if (!g_crc_on_device[device & 63]) {
-            mrz_crc_upload_consts(&g_crc, ctx->stream);
-            CK(cudaStreamSynchronize(ctx->stream));
-            g_crc_on_device[device & 63] = true;
-        }
-    }
-#else
-    mrz_crc_upload_consts(&g_crc, ctx->stream);
-#endif
+    if (mrz_crc_ensure_device(device, ctx->stream)) { ctx->err = "cannot upload the CRC tables"; return MRZ_E_CUDA; }
     if (parent) {
         ctx->d_buf_alloc = parent->d_buf_alloc; ctx->d_buf = parent->d_buf;
         ctx->d_bmap = parent->d_bmap; ctx->d_bsum = parent->d_bsum; ctx->d_hidx = parent->d_hidx;
@@ -361,6 +367,13 @@ extern "C" int mrz_ctx_create_ex(int device, int64_t max_chunk, const mrz_config
     *out = ctx;
     return 0;
 }
+extern "C" int mrz_ctx_set_cluster(mrz_ctx *ctx, int cluster_size) {
+    if (!ctx) return MRZ_E_ARG;
+    if (cluster_size != 0 && cluster_size != 1 && cluster_size != 2 && cluster_size != 4 && cluster_size != 8 && cluster_size != 16) return MRZ_E_ARG;
+    ctx->cfg.cluster_size = cluster_size;
+    return 0;
+}
+
 extern "C" int mrz_ctx_create(int device, int64_t max_chunk, mrz_ctx **out) { return mrz_ctx_create_ex(device, max_chunk, nullptr, out); }
 
 extern "C" int mrz_ctx_create_variant(mrz_ctx *parent, mrz_ctx **out) {

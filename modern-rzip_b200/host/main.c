@@ -7,7 +7,8 @@
  *   -w <n>        window, units of 100 MiB     -m <n>  ram size, units of 100 MiB    -U  unlimited window
  *   -p <n>        threads (accepted; forced to 1 for -n as in stream.c:737)
  *   -o <file> -O <dir> -S <suffix> -f -D -K -q -v -vv -V -h
- *   -g <dev>      CUDA device index (new)
+ *   -g <d,d,...>  CUDA devices to spread the chunks of a file over (new; default 0)
+ *   -G <n>        chunks kept in flight per device (new; default chosen from the chunk count)
  */
 #define _GNU_SOURCE
 #include <getopt.h>
@@ -24,7 +25,7 @@ static void usage(void) {
             "usage: mrzip -n [options] <file...>\n"
             "  -n  rzip pre-processing only (the only mode of this build; back-ends stay with the reference)\n"
             "  -L level  -R rzip-level  -w window(x100MB)  -m ram(x100MB)  -U  -p threads\n"
-            "  -o outfile  -O outdir  -S suffix  -f  -D  -K  -q  -v  -V  -g cuda-device\n");
+            "  -o outfile  -O outdir  -S suffix  -f  -D  -K  -q  -v  -V  -g cuda-devices(0,1,..)  -G chunks-in-flight-per-device\n");
 }
 
 int main(int argc, char *argv[]) {
@@ -43,7 +44,7 @@ int main(int argc, char *argv[]) {
         {"version", no_argument, 0, 'V'}, {"help", no_argument, 0, 'h'}, {"decompress", no_argument, 0, 'd'},
         {"test", no_argument, 0, 't'}, {"info", no_argument, 0, 'i'}, {0, 0, 0, 0}};
 
-    while ((c = getopt_long(argc, argv, "nL:R:w:m:Up:o:O:S:fDKqvVhdtig:", long_options, NULL)) != -1) {
+    while ((c = getopt_long(argc, argv, "nL:R:w:m:Up:o:O:S:fDKqvVhdtig:G:", long_options, NULL)) != -1) {
         switch (c) {
             case 'n': no_compress = true; control->flags |= FLAG_NO_COMPRESS; break;
             case 'L':
@@ -89,7 +90,21 @@ int main(int argc, char *argv[]) {
                 if (control->flags & FLAG_VERBOSE) control->flags |= FLAG_MAX_VERBOSE;
                 control->flags |= FLAG_VERBOSE;
                 break;
-            case 'g': control->device = (int)strtol(optarg, NULL, 10); break;
+            case 'g': { /* device list: -g 0,1,2,3 */
+                char *q = optarg;
+                control->n_devices = 0;
+                while (*q && control->n_devices < 16) {
+                    control->devices[control->n_devices++] = (int)strtol(q, &endptr, 10);
+                    if (endptr == q) fatal(control, "Bad device list '%s'\n", optarg);
+                    q = *endptr == ',' ? endptr + 1 : endptr;
+                    if (*endptr && *endptr != ',') fatal(control, "Bad device list '%s'\n", optarg);
+                }
+                break;
+            }
+            case 'G':
+                control->slots_per_device = (int)strtol(optarg, &endptr, 10);
+                if (*endptr || control->slots_per_device < 1 || control->slots_per_device > 16) fatal(control, "-G wants 1..16 chunks in flight per device\n");
+                break;
             case 'V': printf("modern-rzip (B200 rzip pre-processor) version 0.9.0\n"); return 0;
             case 'd': case 't': case 'i':
                 fatal(control, "This build implements the rzip pre-processor (-n) only; use the reference mrzip for -%c\n", c);
@@ -115,8 +130,7 @@ int main(int argc, char *argv[]) {
         struct stat istat;
         struct timeval t0, t1;
         rzip_control local = base;
-        local.gpu = control->gpu; local.gpu_cap = control->gpu_cap; local.pin_s0 = control->pin_s0; local.pin_s1 = control->pin_s1;
-        local.s0_cap = control->s0_cap; local.s1_cap = control->s1_cap;
+        local.engine = control->engine;
         local.infile = argv[i];
         if (stat(local.infile, &istat)) fatal(&local, "Failed to stat %s\n", local.infile);
         if (!S_ISREG(istat.st_mode)) fatal(&local, "mrzip only works directly on regular FILES.\n");
@@ -124,8 +138,7 @@ int main(int argc, char *argv[]) {
         gettimeofday(&t0, NULL);
         if (!compress_file(&local)) return -1;
         gettimeofday(&t1, NULL);
-        control->gpu = local.gpu; control->gpu_cap = local.gpu_cap; control->pin_s0 = local.pin_s0; control->pin_s1 = local.pin_s1;
-        control->s0_cap = local.s0_cap; control->s1_cap = local.s1_cap;
+        control->engine = local.engine;
         double tt = (t1.tv_sec - t0.tv_sec) + 1e-6 * (t1.tv_usec - t0.tv_usec);
         if (local.flags & FLAG_SHOW_PROGRESS)
             fprintf(stderr, "Total time: %02d:%02d:%05.2f\n", (int)tt / 3600, (int)(tt / 60) % 60, tt - (int)tt / 3600 * 3600 - (int)(tt / 60) % 60 * 60);

@@ -20,7 +20,9 @@ typedef unsigned char uchar;
 
 #define ONE_MB 1048576
 #define STREAM_BUFSIZE (ONE_MB * 10)      /* mrzip_private.h:27 */
+#ifndef CHUNK_MULTIPLE                  /* (tests/cusim builds a binary with tiny chunks to exercise the chunk scheduler on the CPU) */
 #define CHUNK_MULTIPLE (100 * (i64)ONE_MB) /* rzip.c:46 */
+#endif
 #define NUM_STREAMS 2
 #define MAGIC_LEN 20
 #define CTYPE_NONE 3
@@ -56,15 +58,14 @@ typedef struct rzip_control {
     int hash_code;               /* 1 = MD5 (main.c:583) */
     uchar hash_resblock[16];
     int fd_out;
-    int device;                  /* CUDA device for the hot path */
-    int n_devices;               /* >1: shard chunks over GPUs */
-    struct mrz_ctx *gpu;
-    i64 gpu_cap, s0_cap, s1_cap;  /* device context capacity; pinned staging for the two streams */
-    uchar *pin_s0, *pin_s1;
+    int devices[16];             /* -g: CUDA devices the chunks of a file are spread over (chunk k -> slot k mod slots) */
+    int n_devices;
+    int slots_per_device;        /* -G: chunks kept in flight per device (0 = chosen from the chunk count) */
+    void *engine;                /* the GPU engine of rzip_fd.c (slots, contexts, staging), kept across files */
     /* statistics as printed by rzip.c:1108-1115 */
     i64 matches, match_bytes, literals, literal_bytes, tag_hits, tag_misses, inserts;
     double gpu_ms, gpu_scan_ms, gpu_auto_ms, gpu_emit_ms;
-    i64 gpu_launches;
+    i64 gpu_launches, variant_launches;
 } rzip_control;
 
 #define NO_COMPRESS (control->flags & FLAG_NO_COMPRESS)
@@ -113,6 +114,7 @@ bool compress_file(rzip_control *control);
 /* the hot path's outer entry (include/rzip.h:25) */
 void rzip_fd(rzip_control *control, int fd_in, int fd_out);
 void rzip_release_gpu(rzip_control *control);
+i64 rzip_victim_round(void);     /* the process-lifetime static of insert_hash (rzip.c:259), for tests */
 bool initialise_control(rzip_control *control); /* mrzip.c:1362 */
 
 /* MD5 (RFC 1321) — the reference gets it from libgcrypt (rzip.c:495, :829) */

@@ -18,7 +18,7 @@ DECLARED_SYMBOLS = [
     "mrz_debug_tags", "mrz_debug_crc32", "mrz_debug_tokens",
     "mrz_ctx_create_variant", "mrz_run_automaton", "mrz_run_emit", "mrz_run_variants", "mrz_run_many",
     "mrz_config_default", "mrz_ctx_create_ex", "mrz_upload_part", "mrz_upload_wait", "mrz_upload_finish",
-    "mrz_download_part", "mrz_get_profile", "mrz_debug_tagmap",
+    "mrz_download_part", "mrz_get_profile", "mrz_debug_tagmap", "mrz_ctx_set_cluster",
 ]
 
 LEVELS = [(1, 4, 1), (2, 4, 2), (4, 4, 2), (8, 4, 2), (16, 4, 3), (32, 4, 4), (32, 2, 6), (64, 1, 16), (64, 1, 32), (64, 1, 128)]
@@ -109,6 +109,7 @@ def bind(path):
                                    C.POINTER(MrzResult)]
         L.mrz_config_default.argtypes = [C.POINTER(MrzConfig)]
         L.mrz_ctx_create_ex.argtypes = [C.c_int, C.c_int64, C.POINTER(MrzConfig), C.POINTER(C.c_void_p)]
+        L.mrz_ctx_set_cluster.argtypes = [C.c_void_p, C.c_int]
         L.mrz_upload_part.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
         L.mrz_upload_wait.argtypes = [C.c_void_p]
         L.mrz_upload_finish.argtypes = [C.c_void_p, C.c_int64]
@@ -280,3 +281,17 @@ class VariantSet:
         r = self.ctxs[v].run_emit()
         s0, s1 = self.ctxs[v].download(r, s0, s1)
         return r, s0, s1
+
+
+def run_many(ctxs, ns, params):
+    """mrz_run_many: the automata of several contexts (same device; chunks of different parents allowed) in ONE launch.
+    -> list of MrzResult (as mrz_run_automaton); emit each with ctx.run_emit()."""
+    m = len(ctxs)
+    hs = (C.c_void_p * m)(*[c.h for c in ctxs])
+    nn = (C.c_int64 * m)(*[int(x) for x in ns])
+    pp = (MrzParams * m)(*params)
+    res = (MrzResult * m)()
+    rc = ctxs[0].L.mrz_run_many(hs, m, nn, pp, res)
+    if rc:
+        raise MrzError("mrz_run_many rc=%d: %s" % (rc, ctxs[0].L.mrz_last_error(None).decode()))
+    return list(res)

@@ -2,6 +2,9 @@
 #include "rzip_oracle.h"
 #include <stdlib.h>
 #include <string.h>
+#include <stdio.h>
+#include <stdlib.h>
+static FILE *g_oplog;
 
 typedef int64_t i64;
 typedef uint8_t u8;
@@ -245,6 +248,7 @@ int orc_rzip_chunk(const u8 *buf, i64 n, const i64 hash_index[256], int level, i
     i64 p = 0, t = 0;
     struct { i64 p, ofs, len; } cur = {0, 0, 0};
     if (c.end > 0) t = full_tag(&c, 0);
+    g_oplog = getenv("ORC_OPLOG") ? fopen(getenv("ORC_OPLOG"), "wb") : NULL;
 
     while (p < c.end) {                                /* rzip.c:548-615 */
         ++p;
@@ -253,6 +257,7 @@ int orc_rzip_chunk(const u8 *buf, i64 n, const i64 hash_index[256], int level, i
 
         i64 best = 0, bofs = 0, brev = 0;              /* find_best_match rzip.c:426-462 */
         stats->lookups++;
+        if (g_oplog) fwrite(&p, 8, 1, g_oplog);      /* debugging aid: ORC_OPLOG=<file> records the position of every lookup */
         for (i64 h = t & c.hmask; c.tab[h].off | c.tab[h].tag; h = (h + 1) & c.hmask) {
             stats->slots_scanned++;
             if (c.tab[h].tag == t) {

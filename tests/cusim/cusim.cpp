@@ -1,9 +1,11 @@
 // cusim.cpp — TEST INFRASTRUCTURE: fiber scheduler of the CPU emulator in cusim.h.
 #include "cusim.h"
 
+#include <mutex>
 #include <sys/mman.h>
 
 namespace cusim {
+static std::mutex launch_mu;   // one kernel at a time across host threads: __shared__ variables are function-local statics here
 thread_local Fiber *cur = nullptr;
 thread_local Block *blkp = nullptr;
 static thread_local void *sched_sp = nullptr;
@@ -193,6 +195,7 @@ static void setup_block(Block *b, int bi, int first_fiber, uint3_ bid, dim3 grid
 }
 
 void launch(dim3 grid, dim3 block, const std::function<void()> &body) {
+    std::lock_guard<std::mutex> guard(launch_mu);
     int nthreads = (int)(block.x * block.y * block.z);
     if (nthreads < 1 || nthreads > kMaxThreads) { fprintf(stderr, "cusim: bad block size %d\n", nthreads); abort(); }
     ensure_pools();
@@ -209,6 +212,7 @@ void launch(dim3 grid, dim3 block, const std::function<void()> &body) {
 }
 
 void launch_cluster(dim3 grid, dim3 block, int cl, size_t smem_bytes, const std::function<void()> &body) {
+    std::lock_guard<std::mutex> guard(launch_mu);
     int nthreads = (int)(block.x * block.y * block.z);
     int nblocks = (int)grid.x;
     if (nthreads < 1 || nthreads > kMaxThreads || nblocks < 1 || nblocks > kMaxBlocks || nblocks * nthreads > kMaxFibers || cl < 1 ||
@@ -232,6 +236,7 @@ void launch_cluster(dim3 grid, dim3 block, int cl, size_t smem_bytes, const std:
 }
 
 void launch_coop(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()> &body) {
+    std::lock_guard<std::mutex> guard(launch_mu);
     int nthreads = (int)(block.x * block.y * block.z);
     int nblocks = (int)(grid.x * grid.y * grid.z);
     if (nthreads < 1 || nthreads > kMaxThreads || nblocks < 1 || nblocks > kMaxBlocks || nblocks * nthreads > kMaxFibers) {

@@ -28,7 +28,7 @@
 #define __shared__ static
 #define __constant__ static
 #define __launch_bounds__(...)
-#define __align__(n) alignas(n)
+#define __align__(n) __attribute__((aligned(n)))
 
 struct uint3_ { unsigned x, y, z; };
 struct dim3 {
@@ -79,6 +79,7 @@ static inline cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t) {
 static inline cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t a, cudaEvent_t b) { *ms = (float)(b->t - a->t); return 0; }
 static inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned = 0) { return 0; }
 #define cudaMemcpyToSymbol(sym, src, n) (memcpy(&(sym), (src), (n)), 0)
+#define cudaGetSymbolAddress(pp, sym) (*(pp) = (void *)(sym), 0)
 
 // ---------------------------------------------------------------- fibers
 namespace cusim {

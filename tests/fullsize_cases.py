@@ -21,5 +21,7 @@ CASES = {
     "dense4g_R9": dict(kind="dense", n=4 * GIB, seed=5, flags=("-m", "130", "-p", "1", "-R", "9")),
     # configs[2]: 32 GiB VM-image-like, -w 41 -> 8 chunks of 4,299,161,600 B; -w 10 -> 33 chunks
     "vm32g_w41": dict(kind="vm", n=32 * GIB, seed=3, flags=("-w", "41", "-m", "140", "-p", "1")),
+    # the multi-GPU weak-scaling input of bench.py: 8 tar-like pieces of one `-w 41` chunk each (piece k = seed 2 + k)
+    "tar32g_w41": dict(kind="tarchunks", n=32 * GIB, seed=2, flags=("-w", "41", "-m", "140", "-p", "1")),
     "vm32g_w10": dict(kind="vm", n=32 * GIB, seed=3, flags=("-w", "10", "-m", "140", "-p", "1")),
 }

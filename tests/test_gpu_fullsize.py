@@ -1,86 +1,118 @@
-"""`-m gpu` parity at BASELINE.json's sizes, through the reference binary where it finishes in seconds and through
-size-independent properties (replay of the token streams == input, CRC, counters) at the full 4 GiB of configs[1]."""
+"""`-m gpu` parity at BASELINE.json's sizes against golden vectors minted from the UNMODIFIED reference binary in the
+build container (tests/golden/fullsize_vectors.json, tests/golden/make_fullsize_golden.py): the product's `mrzip -n`
+archive must have the reference archive's SHA-256, chunk by chunk the reference's two streams, and its MD5 trailer.
+Inputs are regenerated from the seeds of tests/fullsize_cases.py with bench.py's generators.  Where the box allows it
+the reference binary also decodes our archive back (BLAKE2b of the decoded output == input's)."""
+import hashlib
+import json
 import os
+import subprocess
 import sys
-import zlib
+import tempfile
 
 import numpy as np
 import pytest
 
 import helpers as H
-from test_archive_parity import gpu_vs_reference
+from fullsize_cases import CASES
 
 ROOT = H.ROOT
 sys.path.insert(0, ROOT)
+GPU_BIN = os.path.join(ROOT, "modern-rzip_b200", "mrzip")
+GOLD = json.load(open(os.path.join(H.GOLDEN, "fullsize_vectors.json")))
+pytestmark = pytest.mark.gpu
 
 
-def replay(s0, s1, cb, n):
-    """Vectorised replay of a chunk's streams (runzip.c:120-207): literal runs are slice copies, matches are slice
-    copies repeated with period `dist` when they overlap their own output."""
-    out = np.empty(n, dtype=np.uint8)
-    s0 = np.asarray(s0)
-    i = j = p = 0
-    nmatch = 0
-    while True:
-        head, ln = int(s0[i]), int(s0[i + 1]) | (int(s0[i + 2]) << 8)
-        i += 3
-        if head == 0:
-            if ln == 0:
+def blake2b_file(path):
+    h = hashlib.blake2b()
+    with open(path, "rb") as f:
+        while True:
+            b = f.read(1 << 26)
+            if not b:
                 break
-            out[p:p + ln] = s1[j:j + ln]
-            j += ln
-            p += ln
-        else:
-            dist = int.from_bytes(bytes(s0[i:i + cb]), "little")
-            i += cb
-            assert 0 < dist <= p, "match reaches before the start of the chunk"
-            done = 0
-            while done < ln:   # period-dist copy
-                step = min(dist, ln - done)
-                out[p + done:p + done + step] = out[p + done - dist:p + done - dist + step]
-                done += step
-            p += ln
-            nmatch += 1
-    assert p == n and j == len(s1) and i + 4 == len(s0)
-    return out, int.from_bytes(bytes(s0[i:i + 4]), "big"), nmatch
+            h.update(b)
+    return h.hexdigest()
 
 
-@pytest.mark.gpu
-def test_config0_256m_random_repeats_vs_reference():
-    """configs[0]: 256 MiB uniform bytes with 2000 injected repeats, `mrzip -n`: archive byte-identical to the
-    reference's, and the reference decodes ours back to the input (BLAKE2b)."""
-    gpu_vs_reference(H.gen_random_repeats(256 << 20, 2000), ("-m", "40"))
-
-
-@pytest.mark.gpu
-def test_1gib_tar_like_single_chunk_vs_reference():
+def run_case(name, extra=(), decode=False):
     import bench
-    gpu_vs_reference(bench.gen_tar_like(1 << 30, seed=2), ("-m", "20"), expect_chunks=1)
-
-
-@pytest.mark.gpu
-@pytest.mark.parametrize("kind", ["tar", "vm"])
-def test_config1_4gib_round_trip_properties(kind):
-    """configs[1] at full size (4 GiB, one chunk, 5-byte distances): the streams replay to the input, the CRC in
-    stream 0 is the input's, the counters add up.  configs[2]'s data kind at the same size rides along."""
-    import bench
-    import mrz_py
     import psutil
-    n = 4 << 30
-    if psutil.virtual_memory().available < 4 * n:
-        n = 1 << 30
-    pin = mrz_py.PinnedBuffer(n)
-    data = pin.array
-    (bench.gen_vm_like if kind == "vm" else bench.gen_tar_like)(n, seed=2, out=data)
-    ctx = mrz_py.Context(0, n)
-    try:
-        cb = H.chunk_bytes(n)
-        res, s0, s1 = ctx.rzip_chunk(data, mrz_py.make_params(7, cb, H.hash_index(), 0))
-        assert res.match_bytes + res.literal_bytes == n
-        assert res.literal_bytes == len(s1)
-        out, crc, nmatch = replay(s0, s1, cb, n)
-        assert crc == res.crc32 == zlib.crc32(data)
-        assert nmatch >= res.matches          # matches longer than 65535 bytes are split into pieces (rzip.c:207-219)
-        assert np.array_equal(out, data)
-    finally:
-        ctx.close()
+    c, g = CASES[name], GOLD[name]
+    if psutil.virtual_memory().available < 2.6 * c["n"] + (8 << 30):
+        pytest.skip("not enough host memory for %s on this box" % name)
+    with tempfile.TemporaryDirectory(dir="/dev/shm") as d:
+        fin, fout = os.path.join(d, "in.bin"), os.path.join(d, "out.mar")
+        mm = np.memmap(fin, dtype=np.uint8, mode="w+", shape=(c["n"],))
+        bench.GENS[c["kind"]](c["n"], seed=c["seed"], out=mm)
+        mm.flush()
+        del mm
+        p = subprocess.run([GPU_BIN, "-n", "-vv", "-f", *c["flags"], *extra, "-o", fout, fin], env=dict(os.environ, MRZIP="NOCONFIG"),
+                           capture_output=True, text=True)
+        assert p.returncode == 0, p.stderr[-3000:]
+        assert os.path.getsize(fout) == g["archive_len"]
+        ar = H.parse_archive_hashed(fout)
+        assert len(ar["chunks"]) == len(g["chunks"])
+        for k, (a, b) in enumerate(zip(ar["chunks"], g["chunks"])):
+            for key in ("cb", "eof", "size", "s0_len", "s1_len", "s0_sha256", "s1_sha256", "n_blocks"):
+                assert a[key] == b[key], "chunk %d: %s differs from the reference's" % (k, key)
+        assert ar["trailer"].hex() == g["md5"]
+        assert H.sha256_file(fout) == g["archive_sha256"], "archive differs from the reference's"
+        err = p.stderr
+        for key, want in g["counters_u32"].items():        # the seven -vv counters (rzip.c:1108-1115, printed through (unsigned) casts)
+            assert ("%s=%d" % (key, want)) in err, key
+        if decode and H.have_ref():
+            back = os.path.join(d, "back.bin")
+            want = blake2b_file(fin)
+            os.unlink(fin)
+            subprocess.run([H.REF_BIN, "-d", "-q", "-f", "-o", back, fout], env=dict(os.environ, MRZIP="NOCONFIG"), check=True,
+                           capture_output=True)
+            assert blake2b_file(back) == want
+    return p.stderr
+
+
+def test_config1_tar_4gib_archive_equals_reference():
+    """configs[1]: 4 GiB tar-like, one chunk, 5-byte distances; the timed configuration of bench.py."""
+    run_case("tar4g", decode=True)
+
+
+def test_vm_4gib_archive_equals_reference():
+    run_case("vm4g")
+
+
+def test_config3_random_8gib_archive_equals_reference():
+    """configs[3]: 8 GiB incompressible; the sweeps reach mask 2047."""
+    assert GOLD["random8g"]["max_sweep_mask"] >= 1023
+    run_case("random8g")
+
+
+def test_config4_dense_4gib_R9_archive_equals_reference():
+    """configs[4]'s data at rzip level 9 (max_chain_len 128), 4 GiB."""
+    run_case("dense4g_R9")
+
+
+def test_config4_dense_16gib_R9_archive_equals_reference():
+    """configs[4] at its stated size: 16 GiB dense repeats, rzip level 9 (the rzip stage of `-L9`)."""
+    run_case("dense16g_R9")
+
+
+def test_config2_vm_32gib_w41_one_gpu_archive_equals_reference():
+    """configs[2]: 32 GiB VM-image-like, `-w 41` -> 8 chunks; chunks in flight side by side, each searched for all 16
+    values of victim_round_in, the chain resolved on the host (rzip_fd.c)."""
+    err = run_case("vm32g_w41", extra=("-G", "2"))
+    assert " 0 chunk(s) searched for every victim_round" not in err
+
+
+def test_config2_vm_32gib_w10_all_gpus_archive_equals_reference():
+    """configs[2] with `-w 10` -> 33 chunks, spread over every GPU of the box (`-g 0,1,..`)."""
+    import mrz_py
+    n = mrz_py.lib().mrz_device_count()
+    run_case("vm32g_w10", extra=("-g", ",".join(str(i) for i in range(max(1, n))), "-G", "4"))
+
+
+def test_tar_32gib_w41_archive_equals_reference():
+    """bench.py's multi-GPU weak-scaling input: 8 tar-like pieces of one `-w 41` chunk each."""
+    if "tar32g_w41" not in GOLD:
+        pytest.skip("golden vector not minted")
+    import mrz_py
+    n = mrz_py.lib().mrz_device_count()
+    run_case("tar32g_w41", extra=("-g", ",".join(str(i) for i in range(max(1, n))), "-G", "2"))
