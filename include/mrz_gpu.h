@@ -129,6 +129,23 @@ void mrz_host_free(void *p);
  * geometry it used: geom[0] = CTAs per cluster, geom[1] = threads per CTA, geom[2] = automata in the launch. */
 int mrz_get_profile(mrz_ctx *ctx, int64_t counters[64], int32_t geom[3]);
 
+/* CRC32 of n bytes that are already in device memory, without any allocation.
+ * NO COUNTERPART IN THE REFERENCE: this entry point was added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It is the
+ * chunk checksum of the path (what gcry_md_write(crc_handle) accumulates) computed by the same kernels, with their
+ * scratch (the per-block partial CRCs) in a fixed file-scope device array instead of a context's buffers:
+ *   - n <= MRZ_NOALLOC_MAX_BYTES (1 GiB); larger sizes are rejected with MRZ_E_CAPACITY and a text in
+ *     mrz_noalloc_last_error(); d_data must be 16-byte aligned; d_crc_out receives the IEEE CRC32 (one uint32, device memory)
+ *   - calls cudaMalloc / cudaFree / no allocating routine; everything is queued on `stream` (a cudaStream_t, NULL = the
+ *     default stream) and nothing is synchronised - EXCEPT the first call on a device, which uploads the CRC tables
+ *     and synchronises that stream once (make one warm-up call outside any graph capture)
+ *   - every GPU that loads the library holds the array (~270 KiB) until exit; all calls on a device share it, and it
+ *     keeps the last call's contents (a call overwrites every entry it reads: nothing has to be cleared).  Calls that
+ *     overlap on the GPU - different streams without an ordering between them - RACE on it. */
+#define MRZ_NOALLOC_MAX_BYTES (1LL << 30)
+int mrz_crc32_noalloc(int device, const uint8_t *d_data, int64_t n, uint32_t *d_crc_out, void *stream);
+const char *mrz_noalloc_last_error(void);
+
 /* Building blocks exposed for parity tests (each is also used inside mrz_run_resident). */
 /* single_full_tag for every position (rzip.c:348-358): tags[p] for p in [0, count), count <= n-30. */
 int mrz_debug_tags(mrz_ctx *ctx, int64_t n, const int64_t hash_index[256], int64_t *tags_out, int64_t count);

@@ -6,6 +6,7 @@
 // Item i (0 <= i <= m) = [literal before match i][match i]; item m = final literal + terminator
 // + CRC.  Sizes -> exclusive scans -> every item writes its stream-0 bytes at its own offset and
 // stream 1 is gathered output-centrically (16 output bytes per thread) at HBM speed.
+#include <stdio.h>
 #include "mrz_common.cuh"
 
 #define PIECE 0xFFFF  // rzip.c:185, :216
@@ -304,4 +305,95 @@ extern "C" void mrz_launch_emit(const u8 *buf, const Token *toks, i64 m, i64 n, 
         MRZ_LAUNCH(k_emit_s1, (unsigned)((thr + 255) / 256), 256, s, buf, toks, m, n, off1, s1_len, s1);
         (*launches)++;
     }
+}
+
+// ---- CRC32 without any allocation ----------------------------------------------------------------------------------
+// mrz_crc32_noalloc (include/mrz_gpu.h): the chunk CRC32 for callers that cannot call cudaMalloc (CUDA graph capture,
+// tight serving loops, harnesses that forbid it).  Same kernels as the chunk path (k_crc_blocks / k_crc_level2 /
+// k_crc_tail); their scratch - the per-block partial CRCs - lives in ONE file-scope device array of fixed size instead
+// of a context's buffers, and the final combine, which the chunk path does on the host, is a kernel here.
+// Every GPU that loads the library holds the array until exit.  All calls on a device share it: calls that overlap on
+// the GPU (different streams) race.  Nothing in it has to start at zero: a call overwrites every entry it reads.
+#define NOALLOC_MAX_BYTES ((i64)1 << 30)
+#define NOALLOC_L1 (NOALLOC_MAX_BYTES / CRC_BLK)          // 65536 level-1 partials
+#define NOALLOC_L2 (NOALLOC_L1 / 32)                      // 2048 level-2 partials
+static __device__ __align__(256) u32 g_noalloc_scratch[NOALLOC_L1 + NOALLOC_L2 + 64];   // [L1 | L2 | tail]
+
+__device__ __forceinline__ u32 gf2_apply_rt(const u32 *mat, u32 v) {
+    u32 r = 0;
+    for (int b = 0; v; v >>= 1, b++)
+        if (v & 1u) r ^= mat[b];
+    return r;
+}
+__device__ void gf2_square(u32 *dst, const u32 *m) {
+    for (int b = 0; b < 32; b++) dst[b] = gf2_apply_rt(m, m[b]);
+}
+// register -> register after nbytes zero bytes (the host's shift_matrix / crc_shift, mrz_gpu.cu), applied to v
+__device__ u32 gf2_shift(u32 v, u64 nbytes) {
+    u32 cur[32], tmp[32];
+    cur[0] = 0xEDB88320u;                                  // one zero bit
+    for (int b = 1; b < 32; b++) cur[b] = 1u << (b - 1);
+    for (int q = 0; q < 3; q++) { gf2_square(tmp, cur); for (int b = 0; b < 32; b++) cur[b] = tmp[b]; }   // one zero byte
+    while (nbytes) {
+        if (nbytes & 1) v = gf2_apply_rt(cur, v);
+        nbytes >>= 1;
+        if (nbytes) { gf2_square(tmp, cur); for (int b = 0; b < 32; b++) cur[b] = tmp[b]; }
+    }
+    return v;
+}
+// the combine of mrz_gpu.cu run_phase_b, on the device: one thread
+__global__ void k_crc_final(const u32 *__restrict__ part, const u32 *__restrict__ part2, const u32 *__restrict__ tail, i64 n, u32 *out) {
+    const i64 nblk = n / CRC_BLK, ngrp = nblk / 32, nrest = nblk - ngrp * 32;
+    u32 m512k[32];
+    gf2_square(m512k, c_crc.shift_blk[4]);                 // x^(8 * 256 KiB) squared
+    u32 raw = 0;
+    for (i64 g = 0; g < ngrp; g++) raw = gf2_apply_rt(m512k, raw) ^ part2[g];
+    for (i64 r = 0; r < nrest; r++) raw = gf2_apply_rt(c_crc.shift_blk[0], raw) ^ part[ngrp * 32 + r];
+    raw = gf2_shift(raw, (u64)(n - nblk * CRC_BLK)) ^ *tail;
+    *out = raw ^ gf2_shift(0xFFFFFFFFu, (u64)n) ^ 0xFFFFFFFFu;
+}
+
+extern "C" int mrz_crc_ensure_device(int device, cudaStream_t s);     // mrz_gpu.cu: the CRC tables of this device (__constant__), once
+
+#ifndef MRZ_CUSIM
+#include <mutex>
+static std::mutex g_noalloc_mu;
+#endif
+static u32 *g_noalloc_ptr[64];        // device address of g_noalloc_scratch per device (the symbol's name is NOT an address in host code)
+static char g_noalloc_err[256];
+
+extern "C" const char *mrz_noalloc_last_error(void) { return g_noalloc_err; }
+
+extern "C" int mrz_crc32_noalloc(int device, const uint8_t *d_data, int64_t n, uint32_t *d_crc_out, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    g_noalloc_err[0] = 0;
+    if (device < 0 || device >= 64 || n < 0 || !d_crc_out || (n && !d_data)) { snprintf(g_noalloc_err, sizeof g_noalloc_err, "bad argument"); return -3; }
+    if (n > NOALLOC_MAX_BYTES) {
+        snprintf(g_noalloc_err, sizeof g_noalloc_err, "mrz_crc32_noalloc: %lld bytes exceed the fixed scratch (maximum %lld bytes per call)",
+                 (long long)n, (long long)NOALLOC_MAX_BYTES);
+        return -5;
+    }
+    if (((uintptr_t)d_data & 15) != 0) { snprintf(g_noalloc_err, sizeof g_noalloc_err, "mrz_crc32_noalloc: the data pointer must be 16-byte aligned"); return -3; }
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) { snprintf(g_noalloc_err, sizeof g_noalloc_err, "cudaSetDevice: %s", cudaGetErrorString(e)); return -2; }
+    {
+#ifndef MRZ_CUSIM
+        std::lock_guard<std::mutex> g(g_noalloc_mu);
+#endif
+        if (!g_noalloc_ptr[device]) {            // once per device, with that device current
+            void *p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess || !p) { snprintf(g_noalloc_err, sizeof g_noalloc_err, "cudaGetSymbolAddress: %s", cudaGetErrorString(e)); return -2; }
+            g_noalloc_ptr[device] = (u32 *)p;
+        }
+    }
+    int rc = mrz_crc_ensure_device(device, s);
+    if (rc) { snprintf(g_noalloc_err, sizeof g_noalloc_err, "cannot upload the CRC tables"); return rc; }
+    u32 *part = g_noalloc_ptr[device], *part2 = part + NOALLOC_L1, *tail = part2 + NOALLOC_L2;
+    int launches = 0;
+    mrz_launch_crc(d_data, n, part, part2, tail, s, &launches);
+    MRZ_LAUNCH(k_crc_final, 1, 1, s, part, part2, tail, n, d_crc_out);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { snprintf(g_noalloc_err, sizeof g_noalloc_err, "launch: %s", cudaGetErrorString(e)); return -2; }
+    return 0;
 }

@@ -18,7 +18,7 @@ DECLARED_SYMBOLS = [
     "mrz_debug_tags", "mrz_debug_crc32", "mrz_debug_tokens",
     "mrz_ctx_create_variant", "mrz_run_automaton", "mrz_run_emit", "mrz_run_variants", "mrz_run_many",
     "mrz_config_default", "mrz_ctx_create_ex", "mrz_upload_part", "mrz_upload_wait", "mrz_upload_finish",
-    "mrz_download_part", "mrz_get_profile", "mrz_debug_tagmap", "mrz_ctx_set_cluster",
+    "mrz_download_part", "mrz_get_profile", "mrz_debug_tagmap", "mrz_ctx_set_cluster", "mrz_crc32_noalloc", "mrz_noalloc_last_error",
 ]
 
 LEVELS = [(1, 4, 1), (2, 4, 2), (4, 4, 2), (8, 4, 2), (16, 4, 3), (32, 4, 4), (32, 2, 6), (64, 1, 16), (64, 1, 32), (64, 1, 128)]
@@ -110,6 +110,8 @@ def bind(path):
         L.mrz_config_default.argtypes = [C.POINTER(MrzConfig)]
         L.mrz_ctx_create_ex.argtypes = [C.c_int, C.c_int64, C.POINTER(MrzConfig), C.POINTER(C.c_void_p)]
         L.mrz_ctx_set_cluster.argtypes = [C.c_void_p, C.c_int]
+        L.mrz_crc32_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.mrz_noalloc_last_error.restype = C.c_char_p
         L.mrz_upload_part.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
         L.mrz_upload_wait.argtypes = [C.c_void_p]
         L.mrz_upload_finish.argtypes = [C.c_void_p, C.c_int64]
