@@ -232,6 +232,13 @@ struct Smem {
 extern "C" size_t mrz_automaton_smem_bytes() { return sizeof(Smem); }
 
 #ifdef MRZ_CUSIM
+// Emulator build only (tests/cusim): self-checks of the automaton's bookkeeping against the table itself, once per batch.
+// tests/test_sim_parity.py turns them on and asserts that none fired.
+static bool g_selfcheck_on = false;
+static int g_selfcheck_failures = 0;
+static unsigned g_selfcheck_tick = 0;
+extern "C" void mrz_sim_selfcheck(int on) { g_selfcheck_on = on != 0; g_selfcheck_failures = 0; }
+extern "C" int mrz_sim_selfcheck_failures() { return g_selfcheck_failures; }
 #define MRZ_SMEM_PTR(T, name) T *name = reinterpret_cast<T *>(cusim::dyn_smem())
 #else
 #define MRZ_SMEM_PTR(T, name) extern __shared__ __align__(16) unsigned char name##_raw[]; T *name = reinterpret_cast<T *>(name##_raw)
@@ -290,55 +297,121 @@ __device__ __forceinline__ unsigned long long cluster_excl_scan(unsigned long lo
 }
 struct NoExtra { __device__ __forceinline__ void operator()(unsigned long long) const {} };
 
-// Byte compare by one warp: the first mismatch between buf[a0 + f ..] and buf[b0 + f ..] (fwd) or between the bytes
-// before a0 - f and b0 - f (backwards) within the next G * 256 bytes, limited to maxlen, as (8-byte unit << 3 | byte in
-// unit) relative to f, or 0x7fffffff.  All 2 * G loads of a lane are issued before the first compare (the loop is
-// unrolled and the compares come after it): one memory round trip per call.
-template <int G>
-__device__ __forceinline__ int warp_cmp(const u8 *buf, i64 a0, i64 b0, i64 f, i64 maxlen, bool fwd, int lane) {
-    u64 x[G];
-#pragma unroll
-    for (int c = 0; c < G; c++) {
-        const i64 k = f + (i64)(c * 32 + lane) * 8;
-        x[c] = 0;
-        if (k < maxlen) x[c] = fwd ? ld_u64_unaligned(buf, a0 + k) ^ ld_u64_unaligned(buf, b0 + k)
-                                   : ld_u64_unaligned(buf, a0 - 8 - k) ^ ld_u64_unaligned(buf, b0 - 8 - k);
-    }
-    int first = 0x7fffffff;
-#pragma unroll
-    for (int c = G - 1; c >= 0; c--)
-        if (x[c]) first = ((c * 32 + lane) << 3) | (fwd ? ((__ffsll((long long)x[c]) - 1) >> 3) : (__clzll((long long)x[c]) >> 3));
-    for (int o = 16; o; o >>= 1) {
-        const int u = __shfl_xor_sync(FULL, first, o);
-        first = u < first ? u : first;
-    }
-    return first;
+// ---- byte compares with aligned 128-bit loads ---------------------------------------------------------------------
+// match_len (rzip.c:372-397) compares two byte streams of the chunk from an arbitrary pair of positions.  Stream A is
+// read on its own 16-byte grid (the grid starts up to 15 bytes before the first byte that counts; those bytes are
+// masked), stream B wherever that puts it: two aligned vectors and a funnel shift per unit.  A thread that handles G
+// consecutive units issues 2G+1 LDG.128 for 16G bytes (the 8-byte unaligned compare it replaces: 4 LDG.64 per 8 bytes).
+__device__ __forceinline__ void funnel16(const uint4 v0, const uint4 v1, int sb, u64 &lo, u64 &hi) {
+    u64 w0 = (u64)v0.x | ((u64)v0.y << 32), w1 = (u64)v0.z | ((u64)v0.w << 32);
+    u64 w2 = (u64)v1.x | ((u64)v1.y << 32), w3 = (u64)v1.z | ((u64)v1.w << 32);
+    if (sb >= 8) { w0 = w1; w1 = w2; w2 = w3; sb -= 8; }
+    const int s = sb * 8;
+    if (s == 0) { lo = w0; hi = w1; }
+    else { lo = (w0 >> s) | (w1 << (64 - s)); hi = (w1 >> s) | (w2 << (64 - s)); }
 }
-// Both directions from (a0, b0) in ONE round trip: forward limited to maxf, backwards to maxb.
+// XOR of units [u, u+G) of A (Abase 16-aligned) and B (Bbase any alignment): x[2c] = low 8 bytes, x[2c+1] = high 8 bytes
 template <int G>
-__device__ __forceinline__ void warp_cmp2(const u8 *buf, i64 a0, i64 b0, i64 maxf, i64 maxb, int lane, int &ff, int &fr) {
-    u64 xf[G], xb[G];
+__device__ __forceinline__ void xor_units(const u8 *Abase, const u8 *Bbase, i64 u, u64 (&x)[2 * G]) {
+    const uint4 *pa = reinterpret_cast<const uint4 *>(Abase + 16 * u);
+    const uintptr_t bb = (uintptr_t)(Bbase + 16 * u);
+    const uint4 *pb = reinterpret_cast<const uint4 *>(bb & ~(uintptr_t)15);
+    const int sb = (int)(bb & 15);
+    uint4 va[G], vb[G + 1];
+#pragma unroll
+    for (int c = 0; c < G; c++) va[c] = __ldg(pa + c);
+#pragma unroll
+    for (int c = 0; c <= G; c++) vb[c] = __ldg(pb + c);
 #pragma unroll
     for (int c = 0; c < G; c++) {
-        const i64 k = (i64)(c * 32 + lane) * 8;
-        xf[c] = xb[c] = 0;
-        if (k < maxf) xf[c] = ld_u64_unaligned(buf, a0 + k) ^ ld_u64_unaligned(buf, b0 + k);
-        if (k < maxb) xb[c] = ld_u64_unaligned(buf, a0 - 8 - k) ^ ld_u64_unaligned(buf, b0 - 8 - k);
+        u64 bl, bh;
+        funnel16(vb[c], vb[c + 1], sb, bl, bh);
+        x[2 * c] = ((u64)va[c].x | ((u64)va[c].y << 32)) ^ bl;
+        x[2 * c + 1] = ((u64)va[c].z | ((u64)va[c].w << 32)) ^ bh;
     }
-    ff = fr = 0x7fffffff;
+}
+// One thread's share of a compare step.  A step covers S units (16 S bytes); this thread handles units
+// [step * S + tu * G, + G).  Forward: the streams start at a0 / b0; returns the byte index (relative to the step's first
+// unit) of the thread's first mismatch at or behind a0, or 0x7fffffff.  `skip` = a0 & 15 bytes before a0 on the grid.
+#define CMP_G 2
+template <bool FWD>
+__device__ __forceinline__ int cmp_thread(const u8 *buf, i64 a0, i64 b0, i64 maxlen, i64 step, int S, int tu) {
+    const i64 u = step * S + (i64)tu * CMP_G;             // first unit of this thread, counted from the grid origin
+    u64 x[2 * CMP_G];
+    if (FWD) {
+        const int skip = (int)((uintptr_t)(buf + a0) & 15);
+        if (16 * u - skip >= maxlen) return 0x7fffffff;   // nothing of these units counts
+        xor_units<CMP_G>(buf + a0 - skip, buf + b0 - skip, u, x);
+        if (u == 0 && skip) {                             // bytes before a0
+            if (skip >= 8) { x[0] = 0; x[1] &= ~(((u64)1 << ((skip - 8) * 8)) - 1); }
+            else x[0] &= ~(((u64)1 << (skip * 8)) - 1);
+        }
+        int first = 0x7fffffff;
 #pragma unroll
-    for (int c = G - 1; c >= 0; c--) {
-        if (xf[c]) ff = ((c * 32 + lane) << 3) | ((__ffsll((long long)xf[c]) - 1) >> 3);
-        if (xb[c]) fr = ((c * 32 + lane) << 3) | (__clzll((long long)xb[c]) >> 3);
+        for (int c = 2 * CMP_G - 1; c >= 0; c--)
+            if (x[c]) first = (tu * CMP_G * 16) + c * 8 + ((__ffsll((long long)x[c]) - 1) >> 3);
+        return first;
+    } else {
+        // backwards: the grid origin is the first 16-byte boundary at or behind a0; unit u covers the 16 bytes that end
+        // 16 u bytes before it; `skip` bytes between a0 and the origin do not count
+        const int skip = (int)((16 - ((uintptr_t)(buf + a0) & 15)) & 15);
+        if (16 * u - skip >= maxlen) return 0x7fffffff;
+        // units are stored descending in memory: the thread's G units are [origin - 16 (u + G), origin - 16 u)
+        xor_units<CMP_G>(buf + a0 + skip - 16 * (u + CMP_G), buf + b0 + skip - 16 * (u + CMP_G), 0, x);
+        // x[2 * CMP_G - 1] holds the bytes nearest to the origin
+        if (u == 0 && skip) {                             // bytes at or behind a0
+            if (skip > 8) { x[2 * CMP_G - 1] = 0; x[2 * CMP_G - 2] &= (((u64)1 << ((16 - skip) * 8)) - 1); }
+            else if (skip == 8) x[2 * CMP_G - 1] = 0;
+            else x[2 * CMP_G - 1] &= (((u64)1 << ((8 - skip) * 8)) - 1);
+        }
+        int first = 0x7fffffff;                           // distance from the step's origin of the nearest mismatch
+#pragma unroll
+        for (int c = 0; c < 2 * CMP_G; c++)
+            if (x[c]) first = (tu * CMP_G * 16) + (2 * CMP_G - 1 - c) * 8 + (__clzll((long long)x[c]) >> 3);
+        return first;
     }
+}
+
+// The same compare by ONE warp (many candidates: a warp each): 1 KiB per step and direction.
+// Longest common prefix of buf[a0..] / buf[b0..] (FWD) or longest common suffix of buf[..a0) / buf[..b0), at most maxlen.
+template <bool FWD>
+__device__ __forceinline__ i64 warp_extend(const u8 *buf, i64 a0, i64 b0, i64 maxlen, int lane) {
+    if (maxlen <= 0) return 0;
+    const int skip = FWD ? (int)((uintptr_t)(buf + a0) & 15) : (int)((16 - ((uintptr_t)(buf + a0) & 15)) & 15);
+    const int S = 32 * CMP_G;
+    for (i64 step = 0;; step++) {
+        int first = cmp_thread<FWD>(buf, a0, b0, maxlen, step, S, lane);
+        for (int o = 16; o; o >>= 1) {
+            const int u = __shfl_xor_sync(FULL, first, o);
+            first = u < first ? u : first;
+        }
+        if (first != 0x7fffffff) {
+            const i64 k = 16 * step * S + first - skip;
+            return k > maxlen ? maxlen : k;
+        }
+        if (16 * (step + 1) * S - skip >= maxlen) return maxlen;
+    }
+}
+// Both directions, the first step of each in ONE round trip.
+__device__ __forceinline__ void warp_cmp2(const u8 *buf, i64 a0, i64 b0, i64 maxf, i64 maxb, int lane, i64 &f, i64 &r) {
+    const int S = 32 * CMP_G;
+    const int skf = (int)((uintptr_t)(buf + a0) & 15), skb = (int)((16 - ((uintptr_t)(buf + a0) & 15)) & 15);
+    int ff = maxf > 0 ? cmp_thread<true>(buf, a0, b0, maxf, 0, S, lane) : 0x7fffffff;
+    int fr = maxb > 0 ? cmp_thread<false>(buf, a0, b0, maxb, 0, S, lane) : 0x7fffffff;
     for (int o = 16; o; o >>= 1) {
         const int u = __shfl_xor_sync(FULL, ff, o), v = __shfl_xor_sync(FULL, fr, o);
         ff = u < ff ? u : ff;
         fr = v < fr ? v : fr;
     }
+    if (maxf <= 0) f = 0;
+    else if (ff != 0x7fffffff) { f = ff - skf; if (f > maxf) f = maxf; }
+    else if (16 * S - skf >= maxf) f = maxf;
+    else { const i64 done = 16 * S - skf; f = done + warp_extend<true>(buf, a0 + done, b0 + done, maxf - done, lane); }
+    if (maxb <= 0) r = 0;
+    else if (fr != 0x7fffffff) { r = fr - skb; if (r > maxb) r = maxb; }
+    else if (16 * S - skb >= maxb) r = maxb;
+    else { const i64 done = 16 * S - skb; r = done + warp_extend<false>(buf, a0 - done, b0 - done, maxb - done, lane); }
 }
-#define CMP_G 8                       // 8 x 256 bytes per warp step
-#define CMP_STEP (CMP_G * 256)
 
 // ---- the exact executor: one warp runs one op on the live table with the reference semantics -----
 struct Warp {
@@ -390,18 +463,9 @@ struct Warp {
     }
 
     // rzip.c:372-397.  Longest common prefix of buf[a0..] / buf[b0..] (fwd) or longest common suffix of buf[..a0) /
-    // buf[..b0), at most maxlen bytes; 2 KiB per step, the 16 loads of a lane in flight together (warp_cmp).
+    // buf[..b0), at most maxlen bytes; 1 KiB per step, aligned 128-bit loads (cmp_thread).
     __device__ __forceinline__ i64 extend(i64 a0, i64 b0, i64 maxlen, bool fwd) {
-        i64 f = 0;
-        while (f < maxlen) {
-            const int first = warp_cmp<CMP_G>(buf, a0, b0, f, maxlen, fwd, lane);
-            if (first != 0x7fffffff) {
-                f += (i64)(first >> 3) * 8 + (first & 7);
-                break;
-            }
-            f += CMP_STEP;
-        }
-        return f > maxlen ? maxlen : f;
+        return fwd ? warp_extend<true>(buf, a0, b0, maxlen, lane) : warp_extend<false>(buf, a0, b0, maxlen, lane);
     }
     __device__ __forceinline__ i64 match_len(i64 p0, i64 op, i64 &rev) {
         rev = 0;
@@ -410,12 +474,8 @@ struct Warp {
         i64 maxb = p0 - lo;
         if (op < maxb) maxb = op;
         const i64 maxf = end - p0;
-        int ff, fr;
-        warp_cmp2<CMP_G>(buf, p0, op, maxf, maxb, lane, ff, fr);
-        i64 f = ff != 0x7fffffff ? (i64)(ff >> 3) * 8 + (ff & 7) : (maxf > CMP_STEP ? CMP_STEP + extend(p0 + CMP_STEP, op + CMP_STEP, maxf - CMP_STEP, true) : maxf);
-        i64 r = fr != 0x7fffffff ? (i64)(fr >> 3) * 8 + (fr & 7) : (maxb > CMP_STEP ? CMP_STEP + extend(p0 - CMP_STEP, op - CMP_STEP, maxb - CMP_STEP, false) : maxb);
-        if (f > maxf) f = maxf;
-        if (r > maxb) r = maxb;
+        i64 f, r;
+        warp_cmp2(buf, p0, op, maxf, maxb, lane, f, r);
         rev = r;
         const i64 tot = f + r;
         return tot < MRZ_MIN_MATCH ? 0 : tot;
@@ -1013,42 +1073,33 @@ __device__ __forceinline__ i64 cta_extend(Smem *S, const u8 *buf, i64 a0, i64 b0
 }
 
 // single_match_len's two scans (rzip.c:372-397) for ONE candidate by the whole CTA, both directions at once: the lower
-// half of the threads compares forwards from (a0, b0), the upper half backwards, 16 * T bytes per direction and step,
-// all loads of a step in flight together; a step is one memory round trip and three block barriers.
+// half of the threads compares forwards from (a0, b0), the upper half backwards, 16 * T bytes per direction and step
+// (aligned 128-bit loads, cmp_thread); a step is one memory round trip and three block barriers.
 __device__ __forceinline__ void cta_cmp2(Smem *S, const u8 *buf, i64 a0, i64 b0, i64 maxf, i64 maxb, i64 &f_out, i64 &r_out) {
     const int tid = threadIdx.x, T2 = blockDim.x >> 1;
     const bool back = tid >= T2;
     const int t = back ? tid - T2 : tid;
+    const int SU = T2 * CMP_G;                            // units per step and direction
+    const int skf = (int)((uintptr_t)(buf + a0) & 15), skb = (int)((16 - ((uintptr_t)(buf + a0) & 15)) & 15);
     i64 f = 0, r = 0;
     bool fdone = maxf <= 0, rdone = maxb <= 0;
-    while (!(fdone && rdone)) {
+    for (i64 step = 0; !(fdone && rdone); step++) {
         if (tid == 0) { S->lk_fe = 0x7fffffff; S->lk_fe2 = 0x7fffffff; }
         __syncthreads();
-        const bool active = back ? !rdone : !fdone;
-        const i64 base = back ? r : f, lim = back ? maxb : maxf;
-        u64 x[4];
-#pragma unroll
-        for (int c = 0; c < 4; c++) {
-            const i64 k = base + (i64)(c * T2 + t) * 8;
-            x[c] = 0;
-            if (active && k < lim) x[c] = back ? ld_u64_unaligned(buf, a0 - 8 - k) ^ ld_u64_unaligned(buf, b0 - 8 - k)
-                                              : ld_u64_unaligned(buf, a0 + k) ^ ld_u64_unaligned(buf, b0 + k);
-        }
         int first = 0x7fffffff;
-#pragma unroll
-        for (int c = 3; c >= 0; c--)
-            if (x[c]) first = ((c * T2 + t) << 3) | (back ? (__clzll((long long)x[c]) >> 3) : ((__ffsll((long long)x[c]) - 1) >> 3));
+        if (back) { if (!rdone) first = cmp_thread<false>(buf, a0, b0, maxb, step, SU, t); }
+        else if (!fdone) first = cmp_thread<true>(buf, a0, b0, maxf, step, SU, t);
         if (first != 0x7fffffff) atomicMin(back ? &S->lk_fe2 : &S->lk_fe, first);
         __syncthreads();
         const int rf = S->lk_fe, rr = S->lk_fe2;
         __syncthreads();
         if (!fdone) {
-            if (rf != 0x7fffffff) { f += (i64)(rf >> 3) * 8 + (rf & 7); fdone = true; }
-            else { f += (i64)4 * T2 * 8; fdone = f >= maxf; }
+            if (rf != 0x7fffffff) { f = 16 * step * SU + rf - skf; fdone = true; }
+            else if (16 * (step + 1) * SU - skf >= maxf) { f = maxf; fdone = true; }
         }
         if (!rdone) {
-            if (rr != 0x7fffffff) { r += (i64)(rr >> 3) * 8 + (rr & 7); rdone = true; }
-            else { r += (i64)4 * T2 * 8; rdone = r >= maxb; }
+            if (rr != 0x7fffffff) { r = 16 * step * SU + rr - skb; rdone = true; }
+            else if (16 * (step + 1) * SU - skb >= maxb) { r = maxb; rdone = true; }
         }
     }
     f_out = f > maxf ? maxf : f;
@@ -1227,6 +1278,31 @@ k_automaton(const AutoDesc *__restrict__ descs) {
         }
         // ================================================================ sweep ring
         if (steady) refill_queue(sh, S, ttag, btm, hsize, B, CL, rank, j, B);
+#ifdef MRZ_CUSIM
+        if (j == 0 && g_selfcheck_on && (g_selfcheck_tick++ & 63) == 0) {   // emulator self-check (every 64th batch): hash_count and the ring against the table itself
+            i64 used = 0;
+            for (i64 sl = 0; sl < hsize; sl++) used += ttag[sl] != 0 || toff[sl] != 0;
+            if (used != x.run.count) {
+                g_selfcheck_failures++;
+                fprintf(stderr, "SELFCHECK count: batch after p=%lld: the table holds %lld entries, hash_count says %lld\n", (long long)p_now, (long long)used, (long long)x.run.count);
+            }
+            unsigned q = x.e_idx;
+            i64 bad = -1;
+            for (i64 sl = x.run.clean_ptr; steady && sl < x.e_scan; sl++) {   // the ring lists exactly the eligible slots of [clean_ptr, e_scan)
+                const i64 t = ttag[sl];
+                if (t != 0 && (t & btm) != btm) {
+                    if (q == x.e_cnt || sh->E[q & (MRZ_EQ_CAP - 1)] != (int)sl) { bad = sl; break; }
+                    q++;
+                }
+            }
+            if (steady && bad < 0 && q != x.e_cnt) bad = -2;
+            if (bad != -1) {
+                g_selfcheck_failures++;
+                fprintf(stderr, "SELFCHECK ring: batch after p=%lld: slot %lld (clean_ptr %lld e_scan %lld e_idx %u e_cnt %u)\n", (long long)p_now, (long long)bad,
+                        (long long)x.run.clean_ptr, (long long)x.e_scan, x.e_idx, x.e_cnt);
+            }
+        }
+#endif
         TICK(0);
         // ================================================================ gather the next candidates from the map
         // thread j looks at the s = 2^kgate positions [a, a + s): one candidate expected.  One cluster-wide prefix sum
@@ -1266,9 +1342,6 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 x.gp = g;
             }
         }
-#ifdef MRZ_CUSIM
-        if (j == 0 && getenv("CUSIM_GATHER_LOG")) fprintf(stderr, "G %lld %lld %d %d %lld\n", (long long)lo, (long long)x.gp, nr, kgate, (long long)p_now);
-#endif
         if (nr == 0) { __syncthreads(); TICK(1); continue; }
         i64 my_pos = 0, my_tag = 0, prev1 = -1, prev2 = -1;
         if (j < nr) {
@@ -1386,7 +1459,10 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                         // a follower's plan builds on its leader's write: only older claims conflict, and the leader must not have moved
                         const int before = (pl.flags & F_FOLLOW) ? j - 1 : j;
                         int why = 0;
-                        if ((pl.flags & F_FOLLOW) && j - 1 >= pos && LDG_(sh->pl_w2[j - 1]) != lead_w2) { bad = true; why = 33; }
+                        // (a leader that was planned again may keep its slot and yet displace the occupant now: its second write
+                        // can land on the slot this plan found free)
+                        if ((pl.flags & F_FOLLOW) && j - 1 >= pos &&
+                            (LDG_(sh->pl_w2[j - 1]) != lead_w2 || (LDG_(sh->pl_fl[j - 1]) & (F_W1 | F_COMPLEX | F_INSERT)) != F_INSERT)) { bad = true; why = 33; }
                         for (int d = 0; d < pl.ndep && !bad; d++) {   // slots I walked past on the strength of an earlier op's claim
                             const unsigned o = __ldcg(claim + pl.dep_slot[d]);
                             const int oi = KEY_IDX(o);
@@ -1547,14 +1623,9 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 sum_lower(gsum, sl >> GRP_SHIFT, 0);
             }
 #ifdef MRZ_CUSIM
-            {   // debugging aid: CUSIM_OPLOG=<file> records the position of every op that runs (committed or executed)
-                static FILE *oplog = getenv("CUSIM_OPLOG") ? fopen(getenv("CUSIM_OPLOG"), "wb") : nullptr;
-                if (oplog && j >= pos && j < k) fwrite(&my_pos, 8, 1, oplog);
-                if (oplog && k_exact && k < nr && j == k) { fwrite(&my_pos, 8, 1, oplog); fflush(oplog); }
-            }
             dbg_done += k - pos;
             if (j == 0 && k > pos && (int)PK_V(d) != k - pos)
-                fprintf(stderr, "ACCOUNTING: commit [%d,%d) of nr %d counts %u ops (heavy %d pre0 %d)\n", pos, k, nr, PK_V(d), (int)heavy, pre0);
+                g_selfcheck_failures++, fprintf(stderr, "ACCOUNTING: commit [%d,%d) of nr %d counts %u ops (heavy %d pre0 %d)\n", pos, k, nr, PK_V(d), (int)heavy, pre0);
 #endif
             if (tid == 0 && k > pos) {           // every CTA applies the same update to its replica
                 x.run.count = Tk - cleans;
@@ -1668,14 +1739,7 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                                         i64 maxb = pk - lo_m;
                                         if (off < maxb) maxb = off;
                                         const i64 mf = maxf < LK_XCAP ? maxf : LK_XCAP, mb = maxb < LK_XCAP ? maxb : LK_XCAP;
-                                        int ff, fr;
-                                        warp_cmp2<CMP_G>(buf, pk, off, mf, mb, lane, ff, fr);
-                                        f = ff != 0x7fffffff ? (i64)(ff >> 3) * 8 + (ff & 7)
-                                                             : (mf > CMP_STEP ? CMP_STEP + w.extend(pk + CMP_STEP, off + CMP_STEP, mf - CMP_STEP, true) : mf);
-                                        r = fr != 0x7fffffff ? (i64)(fr >> 3) * 8 + (fr & 7)
-                                                             : (mb > CMP_STEP ? CMP_STEP + w.extend(pk - CMP_STEP, off - CMP_STEP, mb - CMP_STEP, false) : mb);
-                                        if (f > mf) f = mf;
-                                        if (r > mb) r = mb;
+                                        warp_cmp2(buf, pk, off, mf, mb, lane, f, r);
                                         if (lane == 0 && ((f == LK_XCAP && maxf > LK_XCAP) || (r == LK_XCAP && maxb > LK_XCAP))) atomicAdd(&S->lk_n, 1);
                                     }
                                     if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; }
@@ -1742,9 +1806,6 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                         const i64 c_op1 = clock64();
                         w.clean_hint = 0;
                         w.store(x.run);
-#ifdef MRZ_CUSIM
-                        if (lane == 0 && getenv("CUSIM_GATHER_LOG")) fprintf(stderr, "X %lld %lld %d %lld %lld\n", (long long)pk, (long long)w.p, (int)jumped, (long long)w.min_mask, (long long)w.ins_mask);
-#endif
                         const bool mask_changed = w.min_mask != min_mask || w.ins_mask != ins_mask;
                         const bool overflow = w.nlog > MRZ_WLOG_CAP;
                         int kp = nr;
@@ -1830,13 +1891,9 @@ k_automaton(const AutoDesc *__restrict__ descs) {
 #undef CLAIM
 #ifdef MRZ_CUSIM
         if (j == 0 && !batch_ended && (dbg_done + dbg_skip != nr || x.run.nops - dbg_nops0 != dbg_done))
-            fprintf(stderr, "ACCOUNTING: batch of %d ops: %d done + %d skipped, n_ops grew by %lld\n", nr, dbg_done, dbg_skip, (long long)(x.run.nops - dbg_nops0));
+            g_selfcheck_failures++, fprintf(stderr, "ACCOUNTING: batch of %d ops: %d done + %d skipped, n_ops grew by %lld\n", nr, dbg_done, dbg_skip, (long long)(x.run.nops - dbg_nops0));
         if (j == 0 && batch_ended && x.run.nops - dbg_nops0 != dbg_done + 1)
-            fprintf(stderr, "ACCOUNTING: ended batch of %d ops: %d done + the cut op, n_ops grew by %lld\n", nr, dbg_done, (long long)(x.run.nops - dbg_nops0));
-        {   // between batches: no candidate may lie between the last position handled and the next batch's first
-            static i64 dbg_last_handled = -1;
-            if (j == 0) dbg_last_handled = batch_ended ? x.run.p : -1;
-        }
+            g_selfcheck_failures++, fprintf(stderr, "ACCOUNTING: ended batch of %d ops: %d done + the cut op, n_ops grew by %lld\n", nr, dbg_done, (long long)(x.run.nops - dbg_nops0));
 #endif
         // ================================================================ batch epilogue
         // a committed plan overwrote a slot of the ring that the sweep had not reached: cut the ring there (every CTA, its replica)

@@ -465,7 +465,8 @@ static int pick_cluster(const mrz_ctx *ctx, int count) {
 #ifdef MRZ_CUSIM
     return count > 2 ? 1 : 2;
 #else
-    for (int cl = 16; cl > 1; cl >>= 1) {
+    // measured on B200 (profiles/r2_geometry_*.txt): 8 CTAs x 256 threads beats 16 x 128 / 16 x 256 / 8 x 512 for one automaton
+    for (int cl = 8; cl > 1; cl >>= 1) {
         int m = mrz_max_active_clusters(cl, ctx->cfg.threads);
         if (m >= count) return cl;
     }

@@ -226,7 +226,7 @@ static void *worker(void *argp) {
                 pthread_mutex_unlock(&job->mu);
             }
             prm.victim_round_in = vr;
-            mrz_ctx_set_cluster(s->ctx[0], spd == 1 ? 0 : pow2_floor(148 / spd > 16 ? 16 : 148 / spd));
+            mrz_ctx_set_cluster(s->ctx[0], spd == 1 ? 0 : pow2_floor(148 / spd > 8 ? 8 : 148 / spd));
             rc = mrz_run_automaton(s->ctx[0], n, &prm, &res[0]);
             if (rc) fatal(control, "GPU rzip failed (%d): %s\n", rc, mrz_last_error(s->ctx[0]));
             vr = res[0].victim_round_out;
@@ -234,7 +234,7 @@ static void *worker(void *argp) {
             /* the predecessor is still being searched: every victim_round_in at once, one launch */
             ensure_variants(control, s, job->nvar);
             int cl = 148 / (spd * job->nvar);
-            mrz_ctx_set_cluster(s->ctx[0], cl < 1 ? 1 : pow2_floor(cl > 16 ? 16 : cl));
+            mrz_ctx_set_cluster(s->ctx[0], cl < 1 ? 1 : pow2_floor(cl > 8 ? 8 : cl));
             rc = mrz_run_variants(s->ctx, job->nvar, n, &prm, res);
             if (rc) fatal(control, "GPU rzip (variants) failed (%d): %s\n", rc, mrz_last_error(NULL));
             pthread_mutex_lock(&job->mu);
