@@ -63,7 +63,8 @@ typedef struct {
     int32_t profile;          /* 1: collect the automaton's phase counters (mrz_get_profile) */
     int32_t token_divisor;    /* initial token capacity = max_chunk / divisor (a chunk that needs more is redone with 8x); 0 = 1024 */
     int32_t poison;           /* debugging: fill every work buffer with 0xA5 at creation instead of leaving it as allocated */
-    int32_t reserved[2];
+    int32_t l2_policy;        /* 0 = when ONE automaton runs, ask for its hash table to persist in L2 (access-policy window on the launch); 1 = off */
+    int32_t reserved[1];
 } mrz_config;
 
 /* library / device ------------------------------------------------------------------------------ */

@@ -50,6 +50,7 @@
 #include <mutex>
 #endif
 #include <string.h>
+#include <stddef.h>
 #include "mrz_common.cuh"
 #include "automaton.h"
 
@@ -334,6 +335,7 @@ __device__ __forceinline__ void xor_units(const u8 *Abase, const u8 *Bbase, i64 
 // [step * S + tu * G, + G).  Forward: the streams start at a0 / b0; returns the byte index (relative to the step's first
 // unit) of the thread's first mismatch at or behind a0, or 0x7fffffff.  `skip` = a0 & 15 bytes before a0 on the grid.
 #define CMP_G 2
+#define CMP_LONG 4          // steps per round trip of a long compare (cta_cmp2)
 template <bool FWD>
 __device__ __forceinline__ int cmp_thread(const u8 *buf, i64 a0, i64 b0, i64 maxlen, i64 step, int S, int tu) {
     const i64 u = step * S + (i64)tu * CMP_G;             // first unit of this thread, counted from the grid origin
@@ -1008,10 +1010,15 @@ __device__ __forceinline__ void sync_queue(Shared *sh, XRes *x, const int *wlog,
     for (int w = 0; w < nlog; w++) {
         const int e = wlog[w], sl = e >> 2;
         unsigned e_idx = x->e_idx, e_cnt = x->e_cnt;
-        if (e & 1) {                             // zeroed by clean_one: consume the ring up to it
-            if (e_idx != e_cnt) e_idx = ring_lower_bound(sh, e_idx, e_cnt, sl + 1, lane);
+        const i64 e_scan = x->e_scan;
+        __syncwarp();                            // every lane has read the counters before lane 0 updates them
+        if (e & 1) {                             // zeroed by clean_one: consume the ring up to it (usually just its head)
+            if (e_idx != e_cnt) {
+                if (e_cnt - e_idx > 1 && LDG_(sh->E[e_idx & (MRZ_EQ_CAP - 1)]) == sl && LDG_(sh->E[(e_idx + 1) & (MRZ_EQ_CAP - 1)]) > sl) e_idx++;
+                else e_idx = ring_lower_bound(sh, e_idx, e_cnt, sl + 1, lane);
+            }
             if (lane == 0) x->e_idx = e_idx;
-        } else if ((e & 2) && sl < x->e_scan && e_idx != e_cnt) {   // overwritten by an insert: if queued, cut the ring there
+        } else if ((e & 2) && sl < e_scan && e_idx != e_cnt) {   // overwritten by an insert: if queued, cut the ring there
             const unsigned a = ring_lower_bound(sh, e_idx, e_cnt, sl, lane);
             const bool hit = a != e_cnt && LDG_(sh->E[a & (MRZ_EQ_CAP - 1)]) == sl;
             if (hit && lane == 0) { x->e_cnt = a; x->e_scan = sl; }
@@ -1083,23 +1090,35 @@ __device__ __forceinline__ void cta_cmp2(Smem *S, const u8 *buf, i64 a0, i64 b0,
     const int skf = (int)((uintptr_t)(buf + a0) & 15), skb = (int)((16 - ((uintptr_t)(buf + a0) & 15)) & 15);
     i64 f = 0, r = 0;
     bool fdone = maxf <= 0, rdone = maxb <= 0;
-    for (i64 step = 0; !(fdone && rdone); step++) {
+    // the first round trip covers one step; a match that survives it is long (tar-like bodies: tens of KiB to MiB) and
+    // goes on CMP_LONG steps per round trip (that many independent load groups in flight per thread)
+    for (i64 step = 0, ks = 1; !(fdone && rdone); step += ks, ks = CMP_LONG) {
         if (tid == 0) { S->lk_fe = 0x7fffffff; S->lk_fe2 = 0x7fffffff; }
         __syncthreads();
         int first = 0x7fffffff;
-        if (back) { if (!rdone) first = cmp_thread<false>(buf, a0, b0, maxb, step, SU, t); }
-        else if (!fdone) first = cmp_thread<true>(buf, a0, b0, maxf, step, SU, t);
+        if (ks == 1) {
+            if (back) { if (!rdone) first = cmp_thread<false>(buf, a0, b0, maxb, step, SU, t); }
+            else if (!fdone) first = cmp_thread<true>(buf, a0, b0, maxf, step, SU, t);
+        } else {
+#pragma unroll
+            for (int q = CMP_LONG - 1; q >= 0; q--) {
+                int v = 0x7fffffff;
+                if (back) { if (!rdone) v = cmp_thread<false>(buf, a0, b0, maxb, step + q, SU, t); }
+                else if (!fdone) v = cmp_thread<true>(buf, a0, b0, maxf, step + q, SU, t);
+                if (v != 0x7fffffff) first = q * 16 * SU + v;
+            }
+        }
         if (first != 0x7fffffff) atomicMin(back ? &S->lk_fe2 : &S->lk_fe, first);
         __syncthreads();
         const int rf = S->lk_fe, rr = S->lk_fe2;
         __syncthreads();
         if (!fdone) {
             if (rf != 0x7fffffff) { f = 16 * step * SU + rf - skf; fdone = true; }
-            else if (16 * (step + 1) * SU - skf >= maxf) { f = maxf; fdone = true; }
+            else if (16 * (step + ks) * SU - skf >= maxf) { f = maxf; fdone = true; }
         }
         if (!rdone) {
             if (rr != 0x7fffffff) { r = 16 * step * SU + rr - skb; rdone = true; }
-            else if (16 * (step + 1) * SU - skb >= maxb) { r = maxb; rdone = true; }
+            else if (16 * (step + ks) * SU - skb >= maxb) { r = maxb; rdone = true; }
         }
     }
     f_out = f > maxf ? maxf : f;
@@ -1350,6 +1369,11 @@ k_automaton(const AutoDesc *__restrict__ descs) {
             if (j > 1) prev2 = LDG_(sh->b_pos[j - 2]);
             my_tag = tag_at(buf, S->hx, my_pos);
             STG_(sh->b_tag[j], my_tag);
+            // the plan's first reads (filter word, first group of tags, its summary) miss L2 when the table is larger
+            // than L2: start the last two now, they arrive while the filter word is on its way
+            const i64 h0 = my_tag & hmask;
+            prefetch_l2(ttag + h0);
+            prefetch_l2(gsum + ((((h0 >> GRP_SHIFT) + 1) >> 3) << 2));
         }
         TICK(1);
         if (dbg && j == 0) { dbg[16] += nr; dbg[17] += 1; }
@@ -1637,10 +1661,12 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                     x.run.clean_ptr = LDG_(sh->E[(e_idx0 + (unsigned)cleans - 1) & (MRZ_EQ_CAP - 1)]);   // pointer stays on the last zeroed slot
                 }
             }
-            __syncthreads();
-            if (tid < CL) push_to(&S->rep.qmin[rank], tid, S->lq);
-            csync(CL);
-            for (int r = 0; r < CL; r++) qacc = S->rep.qmin[r] < qacc ? S->rep.qmin[r] : qacc;
+            if (k > pos) {       // (nothing committed - an exact op right behind another one: no writes to publish, no hop)
+                __syncthreads();
+                if (tid < CL) push_to(&S->rep.qmin[rank], tid, S->lq);
+                csync(CL);
+                for (int r = 0; r < CL; r++) qacc = S->rep.qmin[r] < qacc ? S->rep.qmin[r] : qacc;
+            }
             TICK(4);
             if (k >= nr) break;
             if (dbg && j == k) {   // why does this op cut the batch?
@@ -1795,6 +1821,7 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                     }
                     // ---- op k on the live table, reference semantics (warp 0), on the local replica
                     if (wid == 0) {
+                        const i64 c_pre0 = clock64();
                         w.load(x.run);
                         w.nlog = 0;
                         i64 hint = w.clean_ptr;
@@ -1826,19 +1853,31 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                                 x.pos_after = jumped ? kp : k + 1;
                         }
                         __syncwarp();
+                        const i64 c_sq0 = clock64();
                         if (!ends && steady) {
                             sync_queue(sh, &x, x.wlog, w.nlog, lane);
                             if (lane == 0 && x.e_cnt == x.e_idx && x.e_scan < w.clean_ptr) x.e_scan = w.clean_ptr;
                             __syncwarp();
                         }
-                        // the result goes into every other replica
-                        const int nwords = (int)(sizeof(XRes) / 8);
+                        if (dbg && lane == 0) {
+                            const i64 c_end = clock64();
+                            dbg[54] += c_op1 - c_op0; dbg[55] += c_end - c_op1;
+                            dbg[56] += c_op0 - c_pre0; dbg[57] += c_end - c_sq0;
+                        }
+                    }
+                    // the result goes into every other replica: one destination CTA per warp (a remote store costs the issuing
+                    // warp ~200 clk; one warp pushing to 7 CTAs in turn was 1.5k clk of every exact op).  The write log is the
+                    // tail of XRes: only its used part travels - usually one store per lane.
+                    if (CL > 1) {
+                        __syncthreads();
+                        const i64 c_pu0 = clock64();
+                        const int nwords = (int)((offsetof(XRes, wlog) + 4 * (size_t)(x.nlog > 0 ? x.nlog : 0) + 7) / 8);
                         const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&x);
-                        for (int r = 1; r < CL; r++) {
+                        for (int r = 1 + wid; r < CL; r += T >> 5) {
                             volatile unsigned long long *dst = reinterpret_cast<volatile unsigned long long *>(remote_ptr(&x, r));
                             for (int q = lane; q < nwords; q += 32) dst[q] = src[q];
                         }
-                        if (dbg && lane == 0) { dbg[54] += c_op1 - c_op0; dbg[55] += clock64() - c_op1; }
+                        if (dbg && tid == 0) dbg[58] += clock64() - c_pu0;
                     }
                 }
                 csync(CL);
@@ -1937,6 +1976,13 @@ static int set_attributes_once() {
     if (e != cudaSuccess) return (int)e;
     e = cudaFuncSetAttribute(k_automaton, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     if (e != cudaSuccess) return (int)e;
+    // room for a persisting window over one automaton's hash table (mrz_launch_automata); failure is not an error
+    {
+        int maxp = 0;
+        if (cudaDeviceGetAttribute(&maxp, cudaDevAttrMaxPersistingL2CacheSize, dev) == cudaSuccess && maxp > 0)
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)maxp);
+        cudaGetLastError();
+    }
     set_for[dev & 63] = true;
     return 0;
 }
@@ -1969,7 +2015,9 @@ extern "C" int mrz_max_active_clusters(int CL, int T) {
 }
 
 // nclusters automata (descs[0..nclusters)), CL CTAs of T threads each, one launch.
-extern "C" int mrz_launch_automata(const AutoDesc *descs, int nclusters, int CL, int T, cudaStream_t s) {
+// hot / hot_bytes: a range the launch asks L2 to keep (the hash table of a lone automaton: every walk of the plan phase and
+// of the exact executor is a chain of dependent reads of it, 375 clk from L2 against 1334 clk from HBM); 0 bytes = none.
+extern "C" int mrz_launch_automata(const AutoDesc *descs, int nclusters, int CL, int T, cudaStream_t s, const void *hot, size_t hot_bytes) {
 #ifndef MRZ_CUSIM
     cudaError_t e;
     {
@@ -1977,11 +2025,29 @@ extern "C" int mrz_launch_automata(const AutoDesc *descs, int nclusters, int CL,
         if (rc) return rc;
     }
     cudaLaunchConfig_t cfg;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     cluster_config(cfg, at, nclusters, CL, T, s);
+    if (hot && hot_bytes) {
+        int dev = 0, maxw = 0, maxp = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&maxw, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+        cudaDeviceGetAttribute(&maxp, cudaDevAttrMaxPersistingL2CacheSize, dev);
+        if (maxw > 0 && maxp > 0) {
+            const size_t nb = hot_bytes < (size_t)maxw ? hot_bytes : (size_t)maxw;
+            at[1].id = cudaLaunchAttributeAccessPolicyWindow;
+            at[1].val.accessPolicyWindow.base_ptr = const_cast<void *>(hot);
+            at[1].val.accessPolicyWindow.num_bytes = nb;
+            at[1].val.accessPolicyWindow.hitRatio = (size_t)maxp >= nb ? 1.0f : (float)((double)maxp / (double)nb);
+            at[1].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+            at[1].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+            cfg.numAttrs = 2;
+        }
+        cudaGetLastError();
+    }
     e = cudaLaunchKernelEx(&cfg, k_automaton, descs);
     return (int)e;
 #else
+    (void)hot; (void)hot_bytes;
     MRZ_LAUNCH_CLUSTER(k_automaton, nclusters * CL, CL, T, sizeof(Smem), s, descs);
     return 0;
 #endif

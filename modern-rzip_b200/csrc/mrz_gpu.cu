@@ -23,7 +23,7 @@ void mrz_launch_tagmap(const u8 *, const i64 *, i64, u8 *, u8 *, int, cudaStream
 void mrz_launch_debug_tags(const u8 *, const i64 *, i64, i64 *, cudaStream_t);
 size_t mrz_shared_bytes();
 size_t mrz_automaton_smem_bytes();
-int mrz_launch_automata(const AutoDesc *, int, int, int, cudaStream_t);
+int mrz_launch_automata(const AutoDesc *, int, int, int, cudaStream_t, const void *, size_t);
 int mrz_max_active_clusters(int, int);
 void mrz_crc_upload_consts(const void *, cudaStream_t);
 int mrz_crc_ensure_device(int, cudaStream_t);
@@ -517,7 +517,10 @@ static int run_phase_a_many(mrz_ctx *const *ctxs, int count, const i64 *ns, cons
         bool any = false;
         for (int q = 0; q < m; q++) any = any || !droot->h_mb->st[q].done;
         if (any) {
-            int lrc = mrz_launch_automata(droot->d_desc, m, CL, T, s);
+            // a lone automaton: its table (tags, then offsets) should stay in L2
+            mrz_ctx *c0 = ctxs[todo[0]];
+            const bool pin = m == 1 && ctx->cfg.l2_policy == 0;
+            int lrc = mrz_launch_automata(droot->d_desc, m, CL, T, s, pin ? c0->d_tab : nullptr, pin ? (size_t)(c0->tab_slots + 32) * 16 : 0);
             if (lrc) CK((cudaError_t)lrc);
             launches++;
         }

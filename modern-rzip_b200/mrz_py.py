@@ -52,7 +52,7 @@ def chunk_bytes(n):
 
 class MrzConfig(C.Structure):
     _fields_ = [("cluster_size", C.c_int32), ("threads", C.c_int32), ("filter_log2_words", C.c_int32),
-                ("profile", C.c_int32), ("token_divisor", C.c_int32), ("poison", C.c_int32), ("reserved", C.c_int32 * 2)]
+                ("profile", C.c_int32), ("token_divisor", C.c_int32), ("poison", C.c_int32), ("l2_policy", C.c_int32), ("reserved", C.c_int32 * 1)]
 
 
 class MrzParams(C.Structure):

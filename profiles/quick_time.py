@@ -12,7 +12,7 @@ import numpy as np
 import bench
 import mrz_py
 
-NAMES = {50: "lk:walk", 51: "lk:warp_cmp", 52: "lk:cta_ext", 53: "x:load_op", 54: "x:op()", 55: "x:after_op", 18: "cta_lookup_cycles", 19: "cta_lookups", 0: "ring", 1: "gather", 2: "plan", 3: "conflict", 4: "cut+commit", 5: "executor", 6: "replan", 7: "epilogue", 10: "exact_ops", 11: "rounds",
+NAMES = {56: "x:pre_op", 57: "x:sync_queue", 58: "x:push", 50: "lk:walk", 51: "lk:warp_cmp", 52: "lk:cta_ext", 53: "x:load_op", 54: "x:op()", 55: "x:after_op", 18: "cta_lookup_cycles", 19: "cta_lookups", 0: "ring", 1: "gather", 2: "plan", 3: "conflict", 4: "cut+commit", 5: "executor", 6: "replan", 7: "epilogue", 10: "exact_ops", 11: "rounds",
          16: "ops", 17: "batches", 21: "cut:filter+", 22: "cut:twin", 23: "cut:insert-complex", 24: "cut:conflict", 25: "cut:exact-other",
          30: "replans", 31: "forwarded", 32: "zone", 33: "giveup:follower", 34: "giveup:dep", 35: "giveup:w1owner", 36: "giveup:equal",
          37: "giveup:lesser", 38: "giveup:limits", 39: "giveup:w1claimed", 42: "x:lookup", 43: "x:lookup_n", 44: "x:insert_fast", 45: "x:insert_fast_n",

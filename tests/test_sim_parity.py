@@ -71,11 +71,12 @@ def test_other_cluster_geometries(sim_ctx, config):
     """One CTA, and clusters of 4 and 8 CTAs, on inputs with matches, sweeps, victims and twins; a tiny tag filter
     (many false positives: every such op takes the exact executor)."""
     ctx = _sim_ctx(**config)
+    k = 4 if "filter_log2_words" in config else 1      # with the tiny filter every op is serial: smaller inputs
     try:
-        check(ctx, H.gen_random_repeats(2 << 20, 30, lo=2048, hi=65536))
-        check(ctx, H.gen_motif(1 << 20, 2000), level=1)
-        check(ctx, H.gen_random(4 << 20, seed=21), level=2)
-        check(ctx, H.gen_vm_like(1 << 20, seed=13), level=6)
+        check(ctx, H.gen_random_repeats((2 << 20) // k, 30, lo=2048, hi=65536))
+        check(ctx, H.gen_motif((1 << 20) // k, 2000), level=1)
+        check(ctx, H.gen_random((4 << 20) // k, seed=21), level=2)
+        check(ctx, H.gen_vm_like((1 << 20) // k, seed=13), level=6)
     finally:
         ctx.close()
 
