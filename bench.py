@@ -621,6 +621,7 @@ def vm32_cli(args, rank, world):
     archive compared with the reference's.  Scope E: process wall clock, whole-file MD5 (one thread) included."""
     if rank != 0:
         return 0
+    world = max(world, args.gpus)      # ONE process drives all the GPUs (`-g 0,1,..`): no torchrun needed for this mode
     import helpers as H
     name = "vm32g_w%d" % args.window
     g = golden(name)

@@ -335,7 +335,8 @@ __device__ __forceinline__ void xor_units(const u8 *Abase, const u8 *Bbase, i64 
 // [step * S + tu * G, + G).  Forward: the streams start at a0 / b0; returns the byte index (relative to the step's first
 // unit) of the thread's first mismatch at or behind a0, or 0x7fffffff.  `skip` = a0 & 15 bytes before a0 on the grid.
 #define CMP_G 2
-#define CMP_LONG 4          // steps per round trip of a long compare (cta_cmp2)
+#define CMP_LONG 4          // steps per round trip of a long compare (cta_cmp2) ...
+#define CMP_LONG_AFTER 16   // ... once this many single steps (64 KiB at 256 threads) have matched
 template <bool FWD>
 __device__ __forceinline__ int cmp_thread(const u8 *buf, i64 a0, i64 b0, i64 maxlen, i64 step, int S, int tu) {
     const i64 u = step * S + (i64)tu * CMP_G;             // first unit of this thread, counted from the grid origin
@@ -1090,9 +1091,10 @@ __device__ __forceinline__ void cta_cmp2(Smem *S, const u8 *buf, i64 a0, i64 b0,
     const int skf = (int)((uintptr_t)(buf + a0) & 15), skb = (int)((16 - ((uintptr_t)(buf + a0) & 15)) & 15);
     i64 f = 0, r = 0;
     bool fdone = maxf <= 0, rdone = maxb <= 0;
-    // the first round trip covers one step; a match that survives it is long (tar-like bodies: tens of KiB to MiB) and
-    // goes on CMP_LONG steps per round trip (that many independent load groups in flight per thread)
-    for (i64 step = 0, ks = 1; !(fdone && rdone); step += ks, ks = CMP_LONG) {
+    // one step per round trip at first (most candidates differ within it; VM-like and dense matches end within tens of
+    // KiB, and a wider trip costs them more than it saves: measured); a match that has survived CMP_LONG_AFTER steps is a
+    // long one (tar-like bodies: MiB) and goes on CMP_LONG steps per round trip
+    for (i64 step = 0, ks = 1; !(fdone && rdone); step += ks, ks = step >= CMP_LONG_AFTER ? CMP_LONG : 1) {
         if (tid == 0) { S->lk_fe = 0x7fffffff; S->lk_fe2 = 0x7fffffff; }
         __syncthreads();
         int first = 0x7fffffff;
@@ -1516,7 +1518,10 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                                 why = 39;
                             }
                         }
-                        if (bad) { pl.flags |= F_CONF; chg = true; if (dbg) atomicAdd((unsigned long long *)&dbg[why], 1ULL); }
+                        // an earlier op of the batch inserts an EQUAL tag (or is this plan's moved leader): planned again, the filter
+                        // would find that op's entry and send this op to the exact executor anyway - send it there right away and
+                        // save the round of planning and claims in between
+                        if (bad) { pl.flags |= (why == 36 || why == 33) ? F_COMPLEX : F_CONF; chg = true; if (dbg) atomicAdd((unsigned long long *)&dbg[why], 1ULL); }
                         if (chg) { STG_(sh->pl_fl[j], pl.flags); S->lchg = 1; }
                     }
                     const unsigned ep2 = epoch++;

@@ -95,10 +95,25 @@ struct md5_job {
 };
 static void *md5_file_thread(void *arg) {
     struct md5_job *j = arg;
+    /* MD5 is one serial chain over the whole input (~0.7 GB/s on one core): this thread bounds `mrzip -n` on large files,
+     * so it hashes straight from the page cache through 256 MiB mappings (no copy); pread is the fallback */
+    const i64 win = 256 << 20;
+    i64 done = 0;
+    while (done < j->len) {
+        i64 want = j->len - done < win ? j->len - done : win;
+        void *m = mmap(NULL, (size_t)want, PROT_READ, MAP_SHARED, j->fd, (off_t)done);
+        if (m == MAP_FAILED) break;
+        madvise(m, (size_t)want, MADV_SEQUENTIAL);
+        madvise(m, (size_t)want, MADV_WILLNEED);
+        md5_update(j->ctx, m, (size_t)want);
+        munmap(m, (size_t)want);
+        done += want;
+    }
+    if (done >= j->len) return NULL;
     const i64 step = 8 << 20;
     uchar *buf = malloc((size_t)step);
     if (!buf) fatal(j->control, "Failed to allocate the checksum buffer\n");
-    for (i64 o = 0; o < j->len;) {
+    for (i64 o = done; o < j->len;) {
         i64 want = j->len - o < step ? j->len - o : step;
         ssize_t r = pread(j->fd, buf, (size_t)want, o);
         if (r < 0 && errno == EINTR) continue;
