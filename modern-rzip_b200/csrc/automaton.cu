@@ -1007,7 +1007,10 @@ __device__ __forceinline__ unsigned ring_lower_bound(const Shared *sh, unsigned 
 
 // After a serial op (warp 0 of rank 0, all lanes): bring the ring back in step with what the op wrote.  Only a
 // sweep step (zeroed) or an insert over an entry that was due for sweeping can touch a slot of the ring.
-__device__ __forceinline__ void sync_queue(Shared *sh, XRes *x, const int *wlog, int nlog, int lane) {
+// head0 / head1: the first two slots of the ring as read BEFORE the op (-1: not read): the usual sweep step zeroes head0
+// and the ring advances by one without another look at it.
+__device__ __forceinline__ void sync_queue(Shared *sh, XRes *x, const int *wlog, int nlog, int lane, int head0, int head1) {
+    bool fresh = head1 >= 0;                     // the ring is still as it was when head0 / head1 were read
     for (int w = 0; w < nlog; w++) {
         const int e = wlog[w], sl = e >> 2;
         unsigned e_idx = x->e_idx, e_cnt = x->e_cnt;
@@ -1015,14 +1018,17 @@ __device__ __forceinline__ void sync_queue(Shared *sh, XRes *x, const int *wlog,
         __syncwarp();                            // every lane has read the counters before lane 0 updates them
         if (e & 1) {                             // zeroed by clean_one: consume the ring up to it (usually just its head)
             if (e_idx != e_cnt) {
-                if (e_cnt - e_idx > 1 && LDG_(sh->E[e_idx & (MRZ_EQ_CAP - 1)]) == sl && LDG_(sh->E[(e_idx + 1) & (MRZ_EQ_CAP - 1)]) > sl) e_idx++;
+                if (fresh && head0 == sl && head1 > sl) e_idx++;
+                else if (e_cnt - e_idx > 1 && LDG_(sh->E[e_idx & (MRZ_EQ_CAP - 1)]) == sl && LDG_(sh->E[(e_idx + 1) & (MRZ_EQ_CAP - 1)]) > sl) e_idx++;
                 else e_idx = ring_lower_bound(sh, e_idx, e_cnt, sl + 1, lane);
             }
+            fresh = false;
             if (lane == 0) x->e_idx = e_idx;
         } else if ((e & 2) && sl < e_scan && e_idx != e_cnt) {   // overwritten by an insert: if queued, cut the ring there
             const unsigned a = ring_lower_bound(sh, e_idx, e_cnt, sl, lane);
             const bool hit = a != e_cnt && LDG_(sh->E[a & (MRZ_EQ_CAP - 1)]) == sl;
             if (hit && lane == 0) { x->e_cnt = a; x->e_scan = sl; }
+            fresh = false;
         }
         __syncwarp();
     }
@@ -1539,6 +1545,9 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 TICK(3);
             }
             // ---------------------------------------------------------------- [prefix over the valid plans of [pos, nr)] and the cut
+            // (what the commit will ask about the next op's plan is fetched now: the latency hides behind the cut's hop)
+            int nx_fl = 0, nx_w2 = -1;
+            if (j >= pos && j + 1 < nr && (pl.flags & (F_INSERT | F_COMPLEX | F_CONF)) == F_INSERT) { nx_fl = LDG_(sh->pl_fl[j + 1]); nx_w2 = LDG_(sh->pl_w2[j + 1]); }
             const i64 cnt0 = x.run.count;
             const unsigned e_idx0 = x.e_idx;
             const int avail = (int)(x.e_cnt - e_idx0);
@@ -1634,7 +1643,7 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                     if (steady && (pl.flags & F_W1ELIG) && s1 >= w_lo && s1 < w_hi) atomicMin(&S->lq, s1);   // a ring slot the sweep does not reach in this batch
                 }
                 // a twin that overwrites its leader's entry in the same commit must win the slot
-                const bool overwritten = j + 1 < k && (LDG_(sh->pl_fl[j + 1]) & F_FOLLOW) && LDG_(sh->pl_w2[j + 1]) == pl.w2_slot;
+                const bool overwritten = j + 1 < k && (nx_fl & F_FOLLOW) && nx_w2 == pl.w2_slot;
                 int s2 = pl.w2_slot; CHK(sh, x, 4, s2, hsize);
                 if (!overwritten) {
                     __stcg(toff + s2, my_pos);
@@ -1830,7 +1839,13 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                         w.load(x.run);
                         w.nlog = 0;
                         i64 hint = w.clean_ptr;
-                        if (steady) hint = (x.e_cnt != x.e_idx) ? (i64)LDG_(sh->E[x.e_idx & (MRZ_EQ_CAP - 1)]) : (x.e_scan > hint ? x.e_scan : hint);
+                        int head0 = -1, head1 = -1;              // the ring's first two slots, read in one round trip
+                        if (steady && x.e_cnt != x.e_idx) {
+                            head0 = LDG_(sh->E[x.e_idx & (MRZ_EQ_CAP - 1)]);
+                            if (x.e_cnt - x.e_idx > 1) head1 = LDG_(sh->E[(x.e_idx + 1) & (MRZ_EQ_CAP - 1)]);
+                            hint = head0;
+                        } else if (steady)
+                            hint = x.e_scan > hint ? x.e_scan : hint;
                         w.clean_hint = hint;
                         w.p = pk;
                         const i64 c_op0 = clock64();
@@ -1860,7 +1875,7 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                         __syncwarp();
                         const i64 c_sq0 = clock64();
                         if (!ends && steady) {
-                            sync_queue(sh, &x, x.wlog, w.nlog, lane);
+                            sync_queue(sh, &x, x.wlog, w.nlog, lane, head0, head1);
                             if (lane == 0 && x.e_cnt == x.e_idx && x.e_scan < w.clean_ptr) x.e_scan = w.clean_ptr;
                             __syncwarp();
                         }
