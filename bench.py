@@ -429,6 +429,9 @@ def main():
         if with_copies:
             for vs, ch in zip(sets, my):
                 vs.upload(ch["pin"].array)
+        else:       # resident inputs: the tag map and the CRC are part of the step, not leftovers of the upload
+            for vs, ch in zip(sets, my):
+                vs.parent.invalidate_map(ch["n"])
         if C == 1:
             vs, ch = sets[0], my[0]
             outs = [vs.run(ch["n"], mrz_py.make_params(args.level, ch["cb"], hidx, 0), nvar)]

@@ -21,7 +21,7 @@ __device__ __forceinline__ i64 full_tag64(const u8 *buf, const i64 *hidx, i64 p)
     return t;
 }
 
-__global__ void __launch_bounds__(MAP_THREADS)
+__global__ void __launch_bounds__(MAP_THREADS, 3)
 k_tagmap(const u8 *__restrict__ buf, const i64 *__restrict__ hidx, i64 n, u8 *__restrict__ bmap, u8 *__restrict__ bsum,
          i64 ntiles) {
     __shared__ u32 lut[256 * 32];
@@ -52,15 +52,36 @@ k_tagmap(const u8 *__restrict__ buf, const i64 *__restrict__ hidx, i64 n, u8 *__
         for (int i = 0; i < MRZ_MIN_MATCH; i++) t ^= h[i];
         u32 o[8];
         int mx = 0;
+        if (a + MAP_RUN - 1 <= end) {           // the whole run carries tags (all but the last thread of a chunk)
+            bool wide = false;                  // some tag has >= 32 trailing ones (one in 2^32): redone below
 #pragma unroll
-        for (int i = 0; i < MAP_RUN; i++) {
-            const u32 x = ~t;
-            int z = x ? (__ffs((int)x) - 1) : 32;
-            if (a + i > end) z = 0;
-            else if (z == 32) z = tz1(full_tag64(buf, hidx, a + i));   // >= 32 trailing ones: count in 64 bits
-            mx = z > mx ? z : mx;
-            if ((i & 3) == 0) o[i >> 2] = (u32)z; else o[i >> 2] |= (u32)z << ((i & 3) * 8);
-            if (i + 1 < MAP_RUN) t ^= h[i] ^ h[i + MRZ_MIN_MATCH];
+            for (int i = 0; i < MAP_RUN; i++) {
+                const int z = __ffs((int)~t) - 1;          // -1 when the low word is all ones
+                wide = wide || z < 0;
+                mx = z > mx ? z : mx;
+                const u32 zb = (u32)z & 255u;              // 255 marks a wide tag
+                if ((i & 3) == 0) o[i >> 2] = zb; else o[i >> 2] |= zb << ((i & 3) * 8);
+                if (i + 1 < MAP_RUN) t ^= h[i] ^ h[i + MRZ_MIN_MATCH];
+            }
+            if (wide) {
+                for (int i = 0; i < MAP_RUN; i++)
+                    if (((o[i >> 2] >> ((i & 3) * 8)) & 255u) == 255u) {
+                        const int z = tz1(full_tag64(buf, hidx, a + i));   // count in 64 bits
+                        o[i >> 2] = (o[i >> 2] & ~(255u << ((i & 3) * 8))) | ((u32)z << ((i & 3) * 8));
+                        mx = z > mx ? z : mx;
+                    }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < MAP_RUN; i++) {
+                const u32 x = ~t;
+                int z = x ? (__ffs((int)x) - 1) : 32;
+                if (a + i > end) z = 0;
+                else if (z == 32) z = tz1(full_tag64(buf, hidx, a + i));   // >= 32 trailing ones: count in 64 bits
+                mx = z > mx ? z : mx;
+                if ((i & 3) == 0) o[i >> 2] = (u32)z; else o[i >> 2] |= (u32)z << ((i & 3) * 8);
+                if (i + 1 < MAP_RUN) t ^= h[i] ^ h[i + MRZ_MIN_MATCH];
+            }
         }
         uint4 *dst = reinterpret_cast<uint4 *>(bmap + a);
         dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
@@ -81,7 +102,7 @@ extern "C" i64 mrz_tagmap_tiles(i64 n) { return (n + MAP_TILE - 1) / MAP_TILE + 
 
 extern "C" void mrz_launch_tagmap(const u8 *buf, const i64 *hidx, i64 n, u8 *bmap, u8 *bsum, int sms, cudaStream_t s) {
     const i64 ntiles = mrz_tagmap_tiles(n);
-    i64 grid = (i64)sms * 2;
+    i64 grid = (i64)sms * 3;    // 80 registers, 32 KiB of shared memory: three CTAs per SM
     if (grid > ntiles) grid = ntiles;
     MRZ_LAUNCH(k_tagmap, (unsigned)grid, MAP_THREADS, s, buf, hidx, n, bmap, bsum, ntiles);
 }

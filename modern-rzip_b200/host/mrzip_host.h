@@ -98,8 +98,16 @@ struct stream_info {
     i64 bufsize, size, cur_pos, initial_pos;
     int chunks;
     char chunk_bytes;
+    /* positional mode (open_stream_out_at): every write is a pwrite at fpos, the shared file offset is never used, so
+     * several chunks of one archive can be written at the same time */
+    int positional, eof;
+    i64 fpos, expect_end;   /* expect_end != 0: close_stream_out checks the chunk ended there */
 };
 void *open_stream_out(rzip_control *control, int f, unsigned int n, i64 chunk_limit, char cbytes);
+/* the same sink for a chunk whose first byte goes to file offset `start` (eof: this is the archive's last chunk) */
+void *open_stream_out_at(rzip_control *control, int f, unsigned int n, i64 chunk_limit, char cbytes, i64 start, int eof);
+/* bytes the chunk will occupy on disk (headers and blocks), known from the stream lengths alone */
+i64 stream_out_chunk_size(const struct stream_info *sinfo, i64 s0_len, i64 s1_len);
 void write_stream(rzip_control *control, void *ss, int streamno, const uchar *p, i64 len);
 void flush_buffer(rzip_control *control, struct stream_info *sinfo, int streamno);
 int close_stream_out(rzip_control *control, void *ss);

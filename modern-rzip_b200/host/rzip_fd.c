@@ -77,7 +77,8 @@ struct job {
     pthread_mutex_t mu;
     pthread_cond_t cv;
     int next_chunk;   /* next chunk to hand out */
-    int write_turn;   /* next chunk to write */
+    int place_turn;   /* next chunk to be given its place in the archive */
+    i64 next_pos;     /* file offset of that chunk */
     i64 *vr_in;       /* vr_in[k]: victim_round entering chunk k, valid when vr_known[k] */
     char *vr_known;
     struct engine *eng;
@@ -270,21 +271,30 @@ static void *worker(void *argp) {
         mrz_result r;
         rc = mrz_run_emit(chosen, &r);
         if (rc) fatal(control, "GPU emission failed (%d): %s\n", rc, mrz_last_error(chosen));
+        /* A chunk's place in the archive follows from the stream LENGTHS of the chunks before it (rzip.c:763-792 writes
+         * chunk after chunk): places are handed out strictly in chunk order, then every worker downloads and writes its
+         * own chunk with positional writes - several chunks are on their way to the file at the same time. */
+        pthread_mutex_lock(&job->mu);
+        while (job->place_turn != k) pthread_cond_wait(&job->cv, &job->mu);
+        const int last = k == job->n_chunks - 1;
+        if (last) control->eof = 1; /* rzip.c:1049 */
+        if (MAX_VERBOSE) fprintf(stderr, "Chunk size: %lld\nByte width: %d\n", (long long)n, chunk_bytes);
+        struct stream_info *ss = open_stream_out_at(control, job->fd_out, NUM_STREAMS, n, (char)chunk_bytes, job->next_pos, last);
+        if (!ss) fatal(control, "Failed to open streams in rzip_chunk\n");
+        const i64 chunk_end = job->next_pos + stream_out_chunk_size(ss, r.s0_len, r.s1_len);
+        job->next_pos = chunk_end;
+        job->place_turn = k + 1;
+        pthread_cond_broadcast(&job->cv);
+        pthread_mutex_unlock(&job->mu);
+
         ensure_host(control, &s->s0, &s->s0_cap, r.s0_len + 64);
         ensure_host(control, &s->s1, &s->s1_cap, r.s1_len + 64);
         download_stream(control, s, chosen, 0, s->s0, r.s0_len);
         download_stream(control, s, chosen, 1, s->s1, r.s1_len);
-
-        /* the writer: strictly in chunk order (rzip.c:763-792 per chunk) */
-        pthread_mutex_lock(&job->mu);
-        while (job->write_turn != k) pthread_cond_wait(&job->cv, &job->mu);
-        pthread_mutex_unlock(&job->mu);
-        if (k == job->n_chunks - 1) control->eof = 1; /* rzip.c:1049 */
-        if (MAX_VERBOSE) fprintf(stderr, "Chunk size: %lld\nByte width: %d\n", (long long)n, chunk_bytes);
-        void *ss = open_stream_out(control, job->fd_out, NUM_STREAMS, n, (char)chunk_bytes);
-        if (!ss) fatal(control, "Failed to open streams in rzip_chunk\n");
         replay_streams(control, ss, s->s0, r.s0_len, s->s1, r.s1_len, chunk_bytes);
+        ss->expect_end = chunk_end;
         if (close_stream_out(control, ss)) fatal(control, "Failed to flush/close streams in rzip_chunk\n");
+        pthread_mutex_lock(&job->mu);
         control->matches += r.matches;
         control->match_bytes += r.match_bytes;
         control->literals += r.literals;
@@ -297,9 +307,6 @@ static void *worker(void *argp) {
         control->gpu_auto_ms += r.ms_automaton;
         control->gpu_emit_ms += r.ms_emit;
         control->gpu_launches += r.gpu_launches;
-        pthread_mutex_lock(&job->mu);
-        job->write_turn = k + 1;
-        pthread_cond_broadcast(&job->cv);
         pthread_mutex_unlock(&job->mu);
     }
     return NULL;
@@ -390,6 +397,8 @@ void rzip_fd(rzip_control *control, int fd_in, int fd_out) {
     job.vr_known = calloc((size_t)job.n_chunks + 2, 1);
     job.vr_in[0] = victim_round; /* carried over from the previous file of this process */
     job.vr_known[0] = 1;
+    job.next_pos = lseek(fd_out, 0, SEEK_CUR); /* the first chunk starts where the container header ended */
+    if (job.next_pos == -1) fatal(control, "Failed to get the position of the first chunk\n");
     pthread_mutex_init(&job.mu, NULL);
     pthread_cond_init(&job.cv, NULL);
     if (VERBOSE) fprintf(stderr, job.n_chunks == 1 ? "Will take 1 pass\n" : "Will take %d passes\n", job.n_chunks);
@@ -421,7 +430,8 @@ void rzip_fd(rzip_control *control, int fd_in, int fd_out) {
     free(job.vr_in);
     free(job.vr_known);
 
-    /* hash trailer, rzip.c:1069-1091 */
+    /* hash trailer, rzip.c:1069-1091: behind the last chunk (the chunks were written with positional writes) */
+    if (lseek(fd_out, job.next_pos, SEEK_SET) == -1) fatal(control, "Failed to seek to the end of the chunks\n");
     md5_final(&md5, control->hash_resblock);
     if (MAX_VERBOSE) {
         fprintf(stderr, "MD5: ");

@@ -17,27 +17,32 @@
 /* stream.c:68-70: decided once per process */
 static i64 stream_bufsize = 0;
 
-static void write_all(rzip_control *control, int fd, const void *p, i64 len) {
+static void write_all(rzip_control *control, struct stream_info *sinfo, const void *p, i64 len) {
     const uchar *b = p;
     while (len > 0) {
         i64 n = len > (1 << 30) ? (1 << 30) : len; /* write_1g, stream.c:519 */
-        ssize_t r = write(fd, b, (size_t)n);
+        ssize_t r = sinfo->positional ? pwrite(sinfo->fd, b, (size_t)n, (off_t)sinfo->fpos) : write(sinfo->fd, b, (size_t)n);
         if (r < 0) {
             if (errno == EINTR) continue;
             fatal(control, "Failed to write %lld bytes: %s\n", (long long)n, strerror(errno));
         }
         b += r;
         len -= r;
+        sinfo->fpos += r;
     }
 }
 
-static void write_val(rzip_control *control, int fd, i64 v, int len) {
+static void write_val(rzip_control *control, struct stream_info *sinfo, i64 v, int len) {
     uchar b[8];
     for (int i = 0; i < 8; i++) b[i] = (uchar)((uint64_t)v >> (8 * i)); /* htole64, low `len` bytes */
-    write_all(control, fd, b, len);
+    write_all(control, sinfo, b, len);
 }
 
 static void seekto(rzip_control *control, struct stream_info *sinfo, i64 pos) {
+    if (sinfo->positional) {
+        sinfo->fpos = sinfo->initial_pos + pos;
+        return;
+    }
     if (lseek(sinfo->fd, sinfo->initial_pos + pos, SEEK_SET) == -1) fatal(control, "Failed to seek in stream writer\n");
 }
 
@@ -85,34 +90,58 @@ void *open_stream_out(rzip_control *control, int f, unsigned int n, i64 chunk_li
 static void write_block(rzip_control *control, struct stream_info *sinfo, int streamno, const uchar *data, i64 len) {
     int wl = sinfo->chunk_bytes;
     if (!sinfo->chunks++) {
-        uchar b2[2] = {(uchar)sinfo->chunk_bytes, (uchar)control->eof};
-        write_all(control, sinfo->fd, b2, 2);
-        write_val(control, sinfo->fd, sinfo->size, wl);
-        sinfo->initial_pos = lseek(sinfo->fd, 0, SEEK_CUR);
-        if (sinfo->initial_pos == -1) fatal(control, "Failed to get position of chunk header\n");
+        uchar b2[2] = {(uchar)sinfo->chunk_bytes, (uchar)(sinfo->positional ? sinfo->eof : control->eof)};
+        write_all(control, sinfo, b2, 2);
+        write_val(control, sinfo, sinfo->size, wl);
+        if (sinfo->positional)
+            sinfo->initial_pos = sinfo->fpos;
+        else {
+            sinfo->initial_pos = lseek(sinfo->fd, 0, SEEK_CUR);
+            if (sinfo->initial_pos == -1) fatal(control, "Failed to get position of chunk header\n");
+        }
         for (int j = 0; j < sinfo->num_streams; j++) {
             uchar t = CTYPE_NONE;
             sinfo->s[j].last_head = sinfo->cur_pos + 1 + (wl * 2);
-            write_all(control, sinfo->fd, &t, 1);
-            write_val(control, sinfo->fd, 0, wl);
-            write_val(control, sinfo->fd, 0, wl);
-            write_val(control, sinfo->fd, 0, wl);
+            write_all(control, sinfo, &t, 1);
+            write_val(control, sinfo, 0, wl);
+            write_val(control, sinfo, 0, wl);
+            write_val(control, sinfo, 0, wl);
             sinfo->cur_pos += 1 + (wl * 3);
         }
     }
     /* link the previous header of this stream to the new block */
     seekto(control, sinfo, sinfo->s[streamno].last_head);
-    write_val(control, sinfo->fd, sinfo->cur_pos, wl);
+    write_val(control, sinfo, sinfo->cur_pos, wl);
     sinfo->s[streamno].last_head = sinfo->cur_pos + 1 + (wl * 2);
     seekto(control, sinfo, sinfo->cur_pos);
     uchar t = CTYPE_NONE;
-    write_all(control, sinfo->fd, &t, 1);
-    write_val(control, sinfo->fd, len, wl); /* c_len */
-    write_val(control, sinfo->fd, len, wl); /* s_len */
-    write_val(control, sinfo->fd, 0, wl);   /* next_head, patched later */
+    write_all(control, sinfo, &t, 1);
+    write_val(control, sinfo, len, wl); /* c_len */
+    write_val(control, sinfo, len, wl); /* s_len */
+    write_val(control, sinfo, 0, wl);   /* next_head, patched later */
     sinfo->cur_pos += 1 + (wl * 3);
-    write_all(control, sinfo->fd, data, len);
+    write_all(control, sinfo, data, len);
     sinfo->cur_pos += len;
+}
+
+/* What write_block will have written for a chunk, from the stream lengths alone: the chunk header (2 + wl bytes), one
+ * initial header per stream, then per stream floor(len / bufsize) full blocks and the final flush (close_stream_out writes
+ * a block for every stream, even an empty one), each with a 1 + 3 wl header. */
+i64 stream_out_chunk_size(const struct stream_info *sinfo, i64 s0_len, i64 s1_len) {
+    const i64 wl = sinfo->chunk_bytes, hdr = 1 + 3 * wl;
+    const i64 lens[2] = {s0_len, s1_len};
+    i64 total = 2 + wl + (i64)sinfo->num_streams * hdr;
+    for (int i = 0; i < sinfo->num_streams && i < 2; i++) total += (lens[i] / sinfo->bufsize + 1) * hdr + lens[i];
+    return total;
+}
+
+void *open_stream_out_at(rzip_control *control, int f, unsigned int n, i64 chunk_limit, char cbytes, i64 start, int eof) {
+    struct stream_info *sinfo = open_stream_out(control, f, n, chunk_limit, cbytes);
+    if (!sinfo) return NULL;
+    sinfo->positional = 1;
+    sinfo->eof = eof;
+    sinfo->fpos = start;
+    return sinfo;
 }
 
 void flush_buffer(rzip_control *control, struct stream_info *sinfo, int streamno) {
@@ -162,8 +191,11 @@ int close_stream_out(rzip_control *control, void *ss) {
         if (sinfo->s[i].buf) free(sinfo->s[i].buf - 16);
         sinfo->s[i].buf = NULL;
     }
-    /* leave the fd at the end of the chunk for the next chunk / the hash trailer */
+    /* leave the fd at the end of the chunk for the next chunk / the hash trailer (positional mode: the caller seeks) */
     seekto(control, sinfo, sinfo->cur_pos);
+    if (sinfo->positional && sinfo->expect_end && sinfo->fpos != sinfo->expect_end)
+        fatal(control, "stream writer: the chunk ends at %lld, its place was computed as ending at %lld\n", (long long)sinfo->fpos,
+              (long long)sinfo->expect_end);
     free(sinfo);
     return 0;
 }

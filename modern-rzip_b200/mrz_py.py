@@ -189,6 +189,10 @@ class Context:
         arr = np.ascontiguousarray(arr, dtype=np.uint8)
         self._check(self.L.mrz_upload(self.h, arr.ctypes.data if arr.size else None, arr.size), "mrz_upload")
 
+    def invalidate_map(self, n):
+        """The resident chunk counts as uploaded anew: the next run recomputes its tag map and CRC (mrz_upload_finish)."""
+        self._check(self.L.mrz_upload_finish(self.h, n), "mrz_upload_finish")
+
     def run_resident(self, n, params):
         res = MrzResult()
         self._check(self.L.mrz_run_resident(self.h, n, C.byref(params), C.byref(res)), "mrz_run_resident")

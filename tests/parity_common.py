@@ -36,3 +36,35 @@ def check(ctx, data, level=7, vr_in=0, cb=None):
     if hasattr(ctx.L, "mrz_sim_selfcheck_failures"):   # emulator build: its per-batch self-checks (table vs hash_count, ring) stayed quiet
         assert ctx.L.mrz_sim_selfcheck_failures() == 0
     return res, ref
+
+
+def check_tagmap(ctx, data, hidx):
+    """tagmap.cu against an independent restatement: tag[p] = X[p+31] ^ X[p] over a prefix-XOR of hash_index[buf[i]]."""
+    import numpy as np
+    data = H.as_u8(data)
+    ctx.upload(data)
+    bmap, bsum = ctx.debug_tagmap(data.size, hidx)
+    h = hidx[data]
+    x = np.concatenate([[0], np.bitwise_xor.accumulate(h)])
+    tags = x[31:] ^ x[:-31]
+    tz = np.zeros(tags.size, dtype=np.int64)
+    t = tags.astype(np.uint64)
+    for i in range(64):
+        tz += ((t & np.uint64(1)) == 1) & (tz == i)
+        t >>= np.uint64(1)
+    want = np.zeros(data.size, dtype=np.uint8)
+    want[:tags.size] = tz
+    assert np.array_equal(bmap, want)
+    ws = np.zeros((data.size + 63) // 64 * 64, dtype=np.uint8)
+    ws[:data.size] = want
+    assert np.array_equal(bsum, ws.reshape(-1, 64).max(axis=1))
+    return want
+
+
+def wide_hash_index(seed=5):
+    """A hash_index whose every tag has >= 32 trailing one bits (31 values XORed, low words all ones): the map's rare
+    64-bit path on every position."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    hi = rng.integers(0, 1 << 31, size=256, dtype=np.int64)
+    return ((hi << 32) | 0xffffffff).astype(np.int64)

@@ -165,23 +165,11 @@ def test_cluster_geometries(config):
         ctx.close()
 
 
-def test_tagmap_matches_prefix_xor(gpu_ctx):
-    """tagmap.cu against an independent restatement: tag[p] = X[p+31] ^ X[p] over a prefix-XOR of hash_index[buf[i]]."""
+@pytest.mark.parametrize("kind", ["glibc", "wide"])
+def test_tagmap_matches_prefix_xor(gpu_ctx, kind):
+    """tagmap.cu against an independent restatement; "wide": every tag has >= 32 trailing ones (the 64-bit path)."""
+    from parity_common import check_tagmap, wide_hash_index
     data = H.gen_random((3 << 20) + 12345, seed=78)
-    hidx = H.hash_index()
-    gpu_ctx.upload(data)
-    bmap, bsum = gpu_ctx.debug_tagmap(data.size, hidx)
-    h = hidx[data]
-    x = np.concatenate([[0], np.bitwise_xor.accumulate(h)])
-    tags = x[31:] ^ x[:-31]
-    tz = np.zeros(tags.size, dtype=np.int64)
-    t = tags.copy()
-    for i in range(48):
-        tz += ((t & 1) == 1) & (tz == i)
-        t >>= 1
-    want = np.zeros(data.size, dtype=np.uint8)
-    want[:tags.size] = tz
-    assert np.array_equal(bmap, want)
-    ws = np.zeros((data.size + 63) // 64 * 64, dtype=np.uint8)
-    ws[:data.size] = want
-    assert np.array_equal(bsum, ws.reshape(-1, 64).max(axis=1))
+    want = check_tagmap(gpu_ctx, data, H.hash_index() if kind == "glibc" else wide_hash_index())
+    if kind == "wide":
+        assert want[: data.size - 30].min() >= 32

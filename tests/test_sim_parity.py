@@ -56,6 +56,16 @@ def test_degenerate(sim_ctx):
     check(sim_ctx, np.tile(H.gen_random(4099, seed=9), 100))
 
 
+@pytest.mark.parametrize("kind", ["glibc", "wide"])
+def test_tagmap_matches_prefix_xor(sim_ctx, kind):
+    """tagmap.cu on the emulator against an independent restatement; "wide": every tag has >= 32 trailing ones."""
+    from parity_common import check_tagmap, wide_hash_index
+    data = H.gen_random((1 << 18) + 345, seed=78)
+    want = check_tagmap(sim_ctx, data, H.hash_index() if kind == "glibc" else wide_hash_index())
+    if kind == "wide":
+        assert want[: data.size - 30].min() >= 32
+
+
 def _sim_ctx(**config):
     """A separate emulator context with its own launch geometry (mrz_config)."""
     import os
