@@ -28,6 +28,7 @@ extern "C" {
 #define MRZ_E_NOMEM (-4)      /* device or pinned-host allocation failed */
 #define MRZ_E_CAPACITY (-5)   /* caller's output buffer too small */
 #define MRZ_E_INTERNAL (-6)   /* device automaton reported an inconsistency */
+#define MRZ_E_DATA (-7)       /* mrz_runzip_chunk: the streams are inconsistent or the chunk's checksum does not match */
 
 typedef struct mrz_ctx mrz_ctx;
 
@@ -121,6 +122,25 @@ int mrz_run_automaton(mrz_ctx *ctx, int64_t n, const mrz_params *prm, mrz_result
 int mrz_run_emit(mrz_ctx *ctx, mrz_result *res);
 int mrz_run_variants(mrz_ctx *const *ctxs, int nvar, int64_t n, const mrz_params *prm, mrz_result *res);
 int mrz_run_many(mrz_ctx *const *ctxs, int count, const int64_t *n, const mrz_params *prms, mrz_result *res);
+
+/* The way back: runzip_chunk (runzip.c:226-327) for one chunk of an uncompressed archive.
+ * s0 / s1 are the chunk's two streams as the archive holds them (what mrz_rzip_chunk produced): stream 0 is walked on the
+ * host (unzip headers, runzip.c:112-118), the literal runs (unzip_literal, runzip.c:120-147) are scattered and the
+ * matches (unzip_match, runzip.c:159-207, `n = MIN(len, offset)` repeated) copied on the device, and the chunk's CRC32 is
+ * checked against the four bytes behind stream 0's terminator (rzip.c:662-665; the reference checks it at
+ * runzip.c:310-322 only for archives without MD5 - here always): a mismatch returns MRZ_E_DATA with the reference's
+ * "Bad checksum" text in mrz_last_error.  out receives the chunk (out_cap >= its size, which is at most the context's
+ * max_chunk); the context must be a root context.  The resident chunk of the context is replaced by the result. */
+typedef struct mrz_unzip_result {
+    int64_t out_len;          /* bytes of the chunk */
+    int64_t literals, matches;/* headers of each kind in stream 0 */
+    int64_t waves;            /* groups of independent matches (one kernel launch each) */
+    uint32_t crc32, crc32_stored;
+    float ms_kernels;
+    int32_t gpu_launches;
+} mrz_unzip_result;
+int mrz_runzip_chunk(mrz_ctx *ctx, const uint8_t *s0, int64_t s0_len, const uint8_t *s1, int64_t s1_len, int chunk_bytes,
+                     uint8_t *out, int64_t out_cap, mrz_unzip_result *res);
 
 /* Pinned host memory for the e2e path (cudaHostAlloc); optional. */
 void *mrz_host_alloc(int64_t bytes);

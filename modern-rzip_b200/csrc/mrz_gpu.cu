@@ -24,6 +24,9 @@ void mrz_launch_debug_tags(const u8 *, const i64 *, i64, i64 *, cudaStream_t);
 size_t mrz_shared_bytes();
 size_t mrz_automaton_smem_bytes();
 int mrz_launch_automata(const AutoDesc *, int, int, int, cudaStream_t, const void *, size_t);
+struct UnzipItem { i64 dst, src, len; };   // unzip.cu
+void mrz_launch_unzip_literals(const UnzipItem *, i64, const u8 *, u8 *, int, cudaStream_t);
+void mrz_launch_unzip_matches(const UnzipItem *, i64, i64, u8 *, int, cudaStream_t);
 int mrz_max_active_clusters(int, int);
 void mrz_crc_upload_consts(const void *, cudaStream_t);
 int mrz_crc_ensure_device(int, cudaStream_t);
@@ -418,6 +421,30 @@ extern "C" int mrz_upload(mrz_ctx *ctx, const uint8_t *chunk, int64_t n) {
     return mrz_upload_finish(ctx, n);
 }
 
+// The chunk CRC32 from the partial CRCs the CRC kernels left in the root's buffers (mrz_launch_crc): drains the stream.
+static int combine_crc(mrz_ctx *ctx, i64 n, cudaStream_t s, u32 *crc_out) {
+    i64 nblk = n / 16384, ngrp = nblk / 32, nrest = nblk - ngrp * 32;
+    u32 &tailcrc = ctx->h_mb->tailcrc;
+    tailcrc = 0;
+    if (ngrp) CK(cudaMemcpyAsync(ctx->h_crc, ctx->d_crc_part2, (size_t)ngrp * 4, cudaMemcpyDeviceToHost, s));
+    if (nrest)
+        CK(cudaMemcpyAsync(ctx->h_crc + ngrp, ctx->d_crc_part + ngrp * 32, (size_t)nrest * 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(&tailcrc, ctx->d_crc_misc, 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    u32 raw = 0;
+    {
+        u32 m512k[32], m16k[32];
+        shift_matrix(m512k, 512 * 1024);
+        shift_matrix(m16k, 16384);
+        for (i64 g = 0; g < ngrp; g++) raw = h_apply(m512k, raw) ^ ctx->h_crc[g];
+        for (i64 r = 0; r < nrest; r++) raw = h_apply(m16k, raw) ^ ctx->h_crc[ngrp + r];
+        i64 tl = n - nblk * 16384;
+        raw = crc_shift(raw, (u64)tl) ^ tailcrc;
+    }
+    *crc_out = raw ^ crc_shift(0xFFFFFFFFu, (u64)n) ^ 0xFFFFFFFFu;
+    return 0;
+}
+
 static mrz_ctx *root_of(mrz_ctx *c) { return c->parent ? c->parent : c; }
 
 // tag map + CRC of the resident chunk of `root`, unless they are already valid for (upload, n, hash_index)
@@ -623,25 +650,8 @@ static int run_phase_b(mrz_ctx *ctx, mrz_result *res) {
     CK(cudaMemcpyAsync(&totals[0], ctx->d_off0 + items, 8, cudaMemcpyDeviceToHost, s));
     CK(cudaMemcpyAsync(&totals[1], ctx->d_off1 + items, 8, cudaMemcpyDeviceToHost, s));
     // CRC partials -> host combine
-    i64 nblk = n / 16384, ngrp = nblk / 32, nrest = nblk - ngrp * 32;
-    u32 &tailcrc = ctx->h_mb->tailcrc;
-    tailcrc = 0;
-    if (ngrp) CK(cudaMemcpyAsync(ctx->h_crc, ctx->d_crc_part2, (size_t)ngrp * 4, cudaMemcpyDeviceToHost, s));
-    if (nrest)
-        CK(cudaMemcpyAsync(ctx->h_crc + ngrp, ctx->d_crc_part + ngrp * 32, (size_t)nrest * 4, cudaMemcpyDeviceToHost, s));
-    CK(cudaMemcpyAsync(&tailcrc, ctx->d_crc_misc, 4, cudaMemcpyDeviceToHost, s));
-    CK(cudaStreamSynchronize(s));
-    u32 raw = 0;
-    {
-        u32 m512k[32], m16k[32];
-        shift_matrix(m512k, 512 * 1024);
-        shift_matrix(m16k, 16384);
-        for (i64 g = 0; g < ngrp; g++) raw = h_apply(m512k, raw) ^ ctx->h_crc[g];
-        for (i64 r = 0; r < nrest; r++) raw = h_apply(m16k, raw) ^ ctx->h_crc[ngrp + r];
-        i64 tl = n - nblk * 16384;
-        raw = crc_shift(raw, (u64)tl) ^ tailcrc;
-    }
-    const u32 crc = raw ^ crc_shift(0xFFFFFFFFu, (u64)n) ^ 0xFFFFFFFFu;
+    u32 crc = 0;
+    if ((rc = combine_crc(ctx, n, s, &crc))) return rc;
     ctx->h_mb->crc = crc;
     CK(cudaMemcpyAsync(ctx->d_crc_misc + 1, &ctx->h_mb->crc, 4, cudaMemcpyHostToDevice, s));
     if ((rc = ensure_s0(ctx, totals[0]))) return rc;
@@ -745,6 +755,112 @@ extern "C" int mrz_get_profile(mrz_ctx *ctx, int64_t counters[64], int32_t geom[
     if (!ctx) return MRZ_E_ARG;
     if (counters) memcpy(counters, ctx->h_dbg, sizeof ctx->h_dbg);
     if (geom) { geom[0] = ctx->geom[0]; geom[1] = ctx->geom[1]; geom[2] = ctx->geom[2]; }
+    return 0;
+}
+
+// ---- runzip_chunk on the device (runzip.c:226-327): the two streams in, the chunk out ------------------------------
+// The header list (stream 0) is walked on the host - a header's size depends on its first byte - into literal runs and
+// matches with their places in the chunk; the literal runs are scattered by one kernel, the matches copied in stream
+// order, wave by wave (a wave: consecutive matches none of which reads a byte another match of the wave writes).
+extern "C" int mrz_runzip_chunk(mrz_ctx *ctx, const uint8_t *s0, int64_t s0_len, const uint8_t *s1, int64_t s1_len, int chunk_bytes,
+                                uint8_t *out, int64_t out_cap, mrz_unzip_result *res) {
+    if (!ctx || ctx->parent || !res || !s0 || s0_len < 7 || s1_len < 0 || (s1_len && !s1) || chunk_bytes < 1 || chunk_bytes > 8)
+        return MRZ_E_ARG;
+    memset(res, 0, sizeof *res);
+    CK(cudaSetDevice(ctx->device));
+    std::vector<UnzipItem> lits, mats;
+    std::vector<i64> wave_first;        // index of the first match of every wave
+    i64 i = 0, j = 0, pos = 0;
+    bool ended = false;
+    while (i + 3 <= s0_len) {
+        const int head = s0[i];
+        const i64 len = (i64)s0[i + 1] | ((i64)s0[i + 2] << 8);
+        if (head == 0) {                // runzip.c:120-147 unzip_literal
+            i += 3;
+            if (len == 0) { ended = true; break; }      // the loop condition of runzip.c:276
+            if (j + len > s1_len) { ctx->err = "stream 1 is shorter than the literal headers say"; return MRZ_E_DATA; }
+            lits.push_back(UnzipItem{pos, j, len});
+            j += len;
+        } else {                        // runzip.c:159-207 unzip_match
+            if (i + 3 + chunk_bytes > s0_len) break;
+            i64 ofs = 0;
+            for (int b = 0; b < chunk_bytes; b++) ofs |= (i64)s0[i + 3 + b] << (8 * b);
+            i += 3 + chunk_bytes;
+            if (len < 1 || ofs < 1 || ofs > pos) { ctx->err = "a match reaches in front of the chunk (corrupt archive)"; return MRZ_E_DATA; }
+            // does it read what a match of the current wave writes?  (their destinations ascend)
+            const i64 rd_lo = pos - ofs, rd_hi = rd_lo + (len < ofs ? len : ofs);
+            const i64 w0 = wave_first.empty() ? 0 : wave_first.back();
+            bool clash = wave_first.empty();
+            if (!clash) {
+                i64 lo = w0, hi = (i64)mats.size();     // first match of the wave whose end is behind rd_lo
+                while (lo < hi) {
+                    const i64 mid = (lo + hi) >> 1;
+                    if (mats[(size_t)mid].dst + mats[(size_t)mid].len > rd_lo) hi = mid; else lo = mid + 1;
+                }
+                clash = lo < (i64)mats.size() && mats[(size_t)lo].dst < rd_hi;
+            }
+            if (clash) wave_first.push_back((i64)mats.size());
+            mats.push_back(UnzipItem{pos, rd_lo, len});
+        }
+        pos += len;
+        if (pos > ctx->max_chunk) { ctx->err = "the streams describe a chunk larger than this context"; return MRZ_E_CAPACITY; }
+    }
+    if (!ended || i + 4 > s0_len) { ctx->err = "stream 0 ends without terminator and checksum"; return MRZ_E_DATA; }
+    if (j != s1_len) { ctx->err = "stream 1 is longer than the literal headers say"; return MRZ_E_DATA; }
+    const u32 stored = ((u32)s0[i] << 24) | ((u32)s0[i + 1] << 16) | ((u32)s0[i + 2] << 8) | (u32)s0[i + 3];   // rzip.c:662-665
+    const i64 n = pos;
+    if (n > out_cap) return MRZ_E_CAPACITY;
+    cudaStream_t s = ctx->stream;
+    UnzipItem *d_items = nullptr;
+    const size_t nl = lits.size(), nm = mats.size();
+    if (nl + nm) {
+        if (cudaMalloc((void **)&d_items, (nl + nm) * sizeof(UnzipItem)) != cudaSuccess) { cudaGetLastError(); ctx->err = "cudaMalloc of the item table failed"; return MRZ_E_NOMEM; }
+    }
+    int launches = 0;
+    cudaError_t e = cudaSuccess;
+    auto step = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+    if (nl) step(cudaMemcpyAsync(d_items, lits.data(), nl * sizeof(UnzipItem), cudaMemcpyHostToDevice, s));
+    if (nm) step(cudaMemcpyAsync(d_items + nl, mats.data(), nm * sizeof(UnzipItem), cudaMemcpyHostToDevice, s));
+    if (s1_len) step(cudaMemcpyAsync(ctx->d_s1, s1, (size_t)s1_len, cudaMemcpyHostToDevice, s));
+    step(cudaEventRecord(ctx->ev[0], s));
+    if (e == cudaSuccess) {
+        if (nl) { mrz_launch_unzip_literals(d_items, (i64)nl, ctx->d_s1, ctx->d_buf, ctx->sms, s); launches++; }
+        for (size_t w = 0; w < wave_first.size(); w++) {
+            const i64 a = wave_first[w], b = w + 1 < wave_first.size() ? wave_first[w + 1] : (i64)nm;
+            mrz_launch_unzip_matches(d_items + nl, a, b - a, ctx->d_buf, ctx->sms, s);
+            launches++;
+        }
+        step(cudaMemsetAsync(ctx->d_buf + n, 0, MRZ_PAD + 64, s));
+        mrz_launch_crc(ctx->d_buf, n, ctx->d_crc_part, ctx->d_crc_part2, ctx->d_crc_misc, s, &launches);
+        step(cudaEventRecord(ctx->ev[1], s));
+        step(cudaGetLastError());
+    }
+    u32 crc = 0;
+    int rc = 0;
+    if (e == cudaSuccess) rc = combine_crc(ctx, n, s, &crc);
+    if (e == cudaSuccess && !rc && n) step(cudaMemcpyAsync(out, ctx->d_buf, (size_t)n, cudaMemcpyDeviceToHost, s));
+    step(cudaStreamSynchronize(s));
+    if (d_items) cudaFree(d_items);
+    ctx->upload_gen++;                  // the resident chunk changed: its tag map is stale
+    ctx->have_tokens = false;
+    CK(e);
+    if (rc) return rc;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+    res->out_len = n;
+    res->literals = (i64)nl;
+    res->matches = (i64)nm;
+    res->waves = (i64)wave_first.size();
+    res->crc32 = crc;
+    res->crc32_stored = stored;
+    res->ms_kernels = ms;
+    res->gpu_launches = launches;
+    if (crc != stored) {
+        char b[128];
+        snprintf(b, sizeof b, "Bad checksum: 0x%08x - expected: 0x%08x", crc, stored);   // runzip.c:319
+        ctx->err = b;
+        return MRZ_E_DATA;
+    }
     return 0;
 }
 

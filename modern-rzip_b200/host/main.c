@@ -2,7 +2,8 @@
  * src/main.c (option table :252-303, parsing :356-569, defaults :575-583, per-file loop :651-747).
  * Same flags and meanings for the subset that shapes an `-n` archive; the back-end compressors,
  * decompression and info stay with the reference's host code and are refused here with a message.
- *   -n            rzip pre-processing only (required in this build)
+ *   -n            rzip pre-processing only (required in this build to compress)
+ *   -d            decompress an rzip-only archive (the device token replay of runzip_fd.c)
  *   -L/-R <1-9>   compression level / rzip level (levels[] row, rzip.c:65-73, :896)
  *   -w <n>        window, units of 100 MiB     -m <n>  ram size, units of 100 MiB    -U  unlimited window
  *   -p <n>        threads (accepted; forced to 1 for -n as in stream.c:737)
@@ -22,7 +23,7 @@
 static void usage(void) {
     fprintf(stderr,
             "mrzip (B200 rzip pre-processor build) 0.9.0\n"
-            "usage: mrzip -n [options] <file...>\n"
+            "usage: mrzip -n [options] <file...>   |   mrzip -d [options] <archive...>\n"
             "  -n  rzip pre-processing only (the only mode of this build; back-ends stay with the reference)\n"
             "  -L level  -R rzip-level  -w window(x100MB)  -m ram(x100MB)  -U  -p threads\n"
             "  -o outfile  -O outdir  -S suffix  -f  -D  -K  -q  -v  -V  -g cuda-devices(0,1,..)  -G chunks-in-flight-per-device\n");
@@ -33,7 +34,7 @@ int main(int argc, char *argv[]) {
     int c;
     char *endptr;
     initialise_control(control);
-    bool no_compress = false;
+    bool no_compress = false, decompress = false;
 
     static const struct option long_options[] = {
         {"no-compress", no_argument, 0, 'n'}, {"level", required_argument, 0, 'L'}, {"rzip-level", required_argument, 0, 'R'},
@@ -106,15 +107,16 @@ int main(int argc, char *argv[]) {
                 if (*endptr || control->slots_per_device < 1 || control->slots_per_device > 16) fatal(control, "-G wants 1..16 chunks in flight per device\n");
                 break;
             case 'V': printf("modern-rzip (B200 rzip pre-processor) version 0.9.0\n"); return 0;
-            case 'd': case 't': case 'i':
-                fatal(control, "This build implements the rzip pre-processor (-n) only; use the reference mrzip for -%c\n", c);
+            case 'd': decompress = true; break;
+            case 't': case 'i':
+                fatal(control, "This build implements the rzip pre-processor (-n) and its inverse (-d); use the reference mrzip for -%c\n", c);
                 break;
             case 'h': default: usage(); return c == 'h' ? 0 : 1;
         }
     }
     argc -= optind;
     argv += optind;
-    if (!no_compress)
+    if (!no_compress && !decompress)
         fatal(control, "This build accelerates the rzip pre-processor only: pass -n (the back-end compressors stay on the host in the reference build)\n");
     if (!control->rzip_compression_level) control->rzip_compression_level = control->compression_level; /* main.c:575 */
     if (control->outname && argc > 1) fatal(control, "Cannot specify output filename with more than 1 file\n");
@@ -136,7 +138,10 @@ int main(int argc, char *argv[]) {
         if (!S_ISREG(istat.st_mode)) fatal(&local, "mrzip only works directly on regular FILES.\n");
         setup_ram(&local);
         gettimeofday(&t0, NULL);
-        if (!compress_file(&local)) return -1;
+        if (decompress) {
+            if (!decompress_file(&local)) return -1;
+        } else if (!compress_file(&local))
+            return -1;
         gettimeofday(&t1, NULL);
         control->engine = local.engine;
         double tt = (t1.tv_sec - t0.tv_sec) + 1e-6 * (t1.tv_usec - t0.tv_usec);

@@ -121,6 +121,9 @@ bool compress_file(rzip_control *control);
 
 /* the hot path's outer entry (include/rzip.h:25) */
 void rzip_fd(rzip_control *control, int fd_in, int fd_out);
+/* the way back for rzip-only archives (runzip_fd.c): include/runzip.h runzip_fd, mrzip.c decompress_file */
+i64 runzip_fd(rzip_control *control, int fd_in, int fd_out, i64 first_chunk, i64 expected_size, int has_md5);
+bool decompress_file(rzip_control *control);
 void rzip_release_gpu(rzip_control *control);
 i64 rzip_victim_round(void);     /* the process-lifetime static of insert_hash (rzip.c:259), for tests */
 bool initialise_control(rzip_control *control); /* mrzip.c:1362 */

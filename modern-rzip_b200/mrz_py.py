@@ -18,7 +18,7 @@ DECLARED_SYMBOLS = [
     "mrz_debug_tags", "mrz_debug_crc32", "mrz_debug_tokens",
     "mrz_ctx_create_variant", "mrz_run_automaton", "mrz_run_emit", "mrz_run_variants", "mrz_run_many",
     "mrz_config_default", "mrz_ctx_create_ex", "mrz_upload_part", "mrz_upload_wait", "mrz_upload_finish",
-    "mrz_download_part", "mrz_get_profile", "mrz_debug_tagmap", "mrz_ctx_set_cluster", "mrz_crc32_noalloc", "mrz_noalloc_last_error",
+    "mrz_download_part", "mrz_get_profile", "mrz_debug_tagmap", "mrz_ctx_set_cluster", "mrz_crc32_noalloc", "mrz_noalloc_last_error", "mrz_runzip_chunk",
 ]
 
 LEVELS = [(1, 4, 1), (2, 4, 2), (4, 4, 2), (8, 4, 2), (16, 4, 3), (32, 4, 4), (32, 2, 6), (64, 1, 16), (64, 1, 32), (64, 1, 128)]
@@ -53,6 +53,11 @@ def chunk_bytes(n):
 class MrzConfig(C.Structure):
     _fields_ = [("cluster_size", C.c_int32), ("threads", C.c_int32), ("filter_log2_words", C.c_int32),
                 ("profile", C.c_int32), ("token_divisor", C.c_int32), ("poison", C.c_int32), ("l2_policy", C.c_int32), ("reserved", C.c_int32 * 1)]
+
+
+class MrzUnzipResult(C.Structure):
+    _fields_ = [("out_len", C.c_int64), ("literals", C.c_int64), ("matches", C.c_int64), ("waves", C.c_int64),
+                ("crc32", C.c_uint32), ("crc32_stored", C.c_uint32), ("ms_kernels", C.c_float), ("gpu_launches", C.c_int32)]
 
 
 class MrzParams(C.Structure):
@@ -115,6 +120,8 @@ def bind(path):
         L.mrz_upload_part.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
         L.mrz_upload_wait.argtypes = [C.c_void_p]
         L.mrz_upload_finish.argtypes = [C.c_void_p, C.c_int64]
+        L.mrz_runzip_chunk.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64,
+                                       C.POINTER(MrzUnzipResult)]
         L.mrz_download_part.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_int64]
         L.mrz_get_profile.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
         L.mrz_debug_tagmap.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]
@@ -188,6 +195,17 @@ class Context:
     def upload(self, arr):
         arr = np.ascontiguousarray(arr, dtype=np.uint8)
         self._check(self.L.mrz_upload(self.h, arr.ctypes.data if arr.size else None, arr.size), "mrz_upload")
+
+    def runzip_chunk(self, s0, s1, chunk_bytes, out_cap):
+        """mrz_runzip_chunk: the two streams of a chunk -> (MrzUnzipResult, the chunk's bytes).  Raises MrzError on a corrupt
+        stream or a checksum mismatch."""
+        s0 = np.ascontiguousarray(s0, dtype=np.uint8)
+        s1 = np.ascontiguousarray(s1, dtype=np.uint8)
+        out = np.empty(max(1, out_cap), dtype=np.uint8)
+        res = MrzUnzipResult()
+        self._check(self.L.mrz_runzip_chunk(self.h, s0.ctypes.data, s0.size, s1.ctypes.data if s1.size else None, s1.size, chunk_bytes,
+                                            out.ctypes.data, out_cap, C.byref(res)), "mrz_runzip_chunk")
+        return res, out[:res.out_len]
 
     def invalidate_map(self, n):
         """The resident chunk counts as uploaded anew: the next run recomputes its tag map and CRC (mrz_upload_finish)."""

@@ -33,6 +33,12 @@ def check(ctx, data, level=7, vr_in=0, cb=None):
     assert res.final_min_mask == ref["stats"]["final_min_mask"]
     assert res.n_ops == ref["stats"]["lookups"]
     assert res.gpu_launches > 0
+    # and back: the device token replay (mrz_runzip_chunk, runzip.c:226-327) rebuilds the chunk from the two streams and
+    # finds the checksum the encoder stored
+    ures, back = ctx.runzip_chunk(s0, s1, cb, data.size)
+    assert ures.out_len == data.size and ures.crc32 == ures.crc32_stored == res.crc32
+    assert back.tobytes() == data.tobytes()
+    assert ures.matches >= res.matches and ures.literals >= (1 if res.literal_bytes else 0)
     if hasattr(ctx.L, "mrz_sim_selfcheck_failures"):   # emulator build: its per-batch self-checks (table vs hash_count, ring) stayed quiet
         assert ctx.L.mrz_sim_selfcheck_failures() == 0
     return res, ref
@@ -68,3 +74,30 @@ def wide_hash_index(seed=5):
     rng = np.random.default_rng(seed)
     hi = rng.integers(0, 1 << 31, size=256, dtype=np.int64)
     return ((hi << 32) | 0xffffffff).astype(np.int64)
+
+
+def check_runzip_rejects_corruption(ctx):
+    """mrz_runzip_chunk refuses what runzip_chunk would refuse (runzip.c:178 corrupt history, :317-320 bad checksum)."""
+    import numpy as np
+    import mrz_py
+    data = H.as_u8(H.gen_random_repeats(1 << 20, 12, lo=2048, hi=32768))
+    cb = H.chunk_bytes(data.size)
+    res, s0, s1 = ctx.rzip_chunk(data, mrz_py.make_params(7, cb, H.hash_index(), 0))
+    assert res.matches > 0
+    _, back = ctx.runzip_chunk(s0, s1, cb, data.size)
+    assert back.tobytes() == data.tobytes()
+    bad1 = s1.copy()
+    bad1[bad1.size // 2] ^= 0x40                      # one literal byte differs: the chunk's CRC32 no longer matches
+    with pytest.raises(mrz_py.MrzError, match="Bad checksum"):
+        ctx.runzip_chunk(s0, bad1, cb, data.size)
+    with pytest.raises(mrz_py.MrzError):              # the terminator and checksum are cut off
+        ctx.runzip_chunk(s0[:-5], s1, cb, data.size)
+    with pytest.raises(mrz_py.MrzError):              # stream 1 shorter than the headers say
+        ctx.runzip_chunk(s0, s1[:-1], cb, data.size)
+    first_match = np.array([1, 40, 0] + [0xff] * cb, dtype=np.uint8)   # a match as the first token: nothing to copy from
+    with pytest.raises(mrz_py.MrzError, match="corrupt"):
+        ctx.runzip_chunk(np.concatenate([first_match, s0]), s1, cb, data.size + 40)
+    with pytest.raises(mrz_py.MrzError):              # caller's buffer too small
+        ctx.runzip_chunk(s0, s1, cb, data.size - 1)
+    _, back = ctx.runzip_chunk(s0, s1, cb, data.size)   # the context is still good
+    assert back.tobytes() == data.tobytes()

@@ -80,6 +80,50 @@ def gpu_vs_reference(data, flags, expect_chunks=None):
         subprocess.run([H.REF_BIN, "-d", "-q", "-f", "-o", os.path.join(d, "back.bin"), os.path.join(d, "gpu.mar")],
                        env=dict(os.environ, MRZIP="NOCONFIG"), check=True, capture_output=True)
         assert H.blake2b(open(os.path.join(d, "back.bin"), "rb").read()) == H.blake2b(H.as_u8(data).tobytes())
+        # and the product's own way back (host/runzip_fd.c + mrz_runzip_chunk) decodes its archive and the reference's
+        for arc in ("gpu.mar", "ref.mar"):
+            assert decode(GPU_BIN, os.path.join(d, arc), os.path.join(d, "back2.bin")) == H.as_u8(data).tobytes()
+
+
+def decode(binary, farc, fout, expect_ok=True):
+    env = dict(os.environ, MRZIP="NOCONFIG", CUSIM_SEED="7")
+    p = subprocess.run([binary, "-d", "-q", "-f", "-o", fout, farc], env=env, capture_output=True, text=True)
+    if not expect_ok:
+        return p
+    assert p.returncode == 0, p.stderr[-2000:]
+    return open(fout, "rb").read()
+
+
+@pytest.mark.parametrize("name", ["survey650", "pattern0", "pattern31", "random100003", "repeats1m", "dense_R3"])
+def test_sim_decode_roundtrip(sim_bin, name):
+    """`mrzip -d` of this build (stream read side + device token replay, runzip.c:226-327) gives the input back, from its
+    own archive and - when the reference binary is here - from the reference's."""
+    data, flags = CASES[name]
+    with tempfile.TemporaryDirectory() as d:
+        fin = os.path.join(d, "in.bin")
+        H.as_u8(data).tofile(fin)
+        run(sim_bin, fin, os.path.join(d, "o.mar"), flags)
+        assert decode(sim_bin, os.path.join(d, "o.mar"), os.path.join(d, "back.bin")) == H.as_u8(data).tobytes()
+        if H.have_ref():
+            H.run_reference(fin, os.path.join(d, "ref.mar"), flags)
+            assert decode(sim_bin, os.path.join(d, "ref.mar"), os.path.join(d, "back2.bin")) == H.as_u8(data).tobytes()
+
+
+def test_sim_decode_refuses_a_damaged_archive(sim_bin):
+    data = H.gen_random_repeats(1 << 20, 12, lo=2048, hi=32768)
+    with tempfile.TemporaryDirectory() as d:
+        fin = os.path.join(d, "in.bin")
+        H.as_u8(data).tofile(fin)
+        raw = bytearray(run(sim_bin, fin, os.path.join(d, "o.mar")))
+        raw[len(raw) // 2] ^= 0x10                                    # a literal byte
+        open(os.path.join(d, "bad.mar"), "wb").write(raw)
+        p = decode(sim_bin, os.path.join(d, "bad.mar"), os.path.join(d, "x.bin"), expect_ok=False)
+        assert p.returncode != 0 and "Bad checksum" in p.stderr
+        raw[len(raw) // 2] ^= 0x10
+        raw[-1] ^= 1                                                  # the stored MD5
+        open(os.path.join(d, "bad2.mar"), "wb").write(raw)
+        p = decode(sim_bin, os.path.join(d, "bad2.mar"), os.path.join(d, "y.bin"), expect_ok=False)
+        assert p.returncode != 0 and "MD5 CHECK FAILED" in p.stderr
 
 
 @pytest.mark.gpu

@@ -173,3 +173,10 @@ def test_tagmap_matches_prefix_xor(gpu_ctx, kind):
     want = check_tagmap(gpu_ctx, data, H.hash_index() if kind == "glibc" else wide_hash_index())
     if kind == "wide":
         assert want[: data.size - 30].min() >= 32
+
+
+def test_runzip_rejects_corruption(gpu_ctx):
+    """The device token replay refuses corrupt streams and a wrong checksum (every parity case above also round-trips
+    through it: parity_common.check)."""
+    from parity_common import check_runzip_rejects_corruption
+    check_runzip_rejects_corruption(gpu_ctx)

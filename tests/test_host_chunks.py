@@ -47,6 +47,11 @@ def test_multi_chunk_variants_vs_oracle_chain(small_bin, slots):
                            env=dict(os.environ, MRZIP="NOCONFIG"), capture_output=True, text=True)
         assert p.returncode == 0, p.stderr[-2000:]
         ar = H.parse_archive(open(fout, "rb").read())
+        # the way back, chunk after chunk (host/runzip_fd.c)
+        fback = os.path.join(d, "back.bin")
+        q = subprocess.run([small_bin, "-d", "-vv", "-f", "-o", fback, fout], env=dict(os.environ, MRZIP="NOCONFIG"), capture_output=True, text=True)
+        assert q.returncode == 0, q.stderr[-2000:]
+        assert open(fback, "rb").read() == data.tobytes() and "gpu: 4 chunk(s)" in q.stderr
     assert len(ar["chunks"]) == len(want) == 4
     for k, (c, r) in enumerate(zip(ar["chunks"], want)):
         assert c["s0"] == r["s0"], "stream 0 of chunk %d" % k
@@ -67,4 +72,7 @@ def test_empty_and_single(small_bin):
             subprocess.run([small_bin, "-n", "-q", "-f", "-w", "4", "-o", fout, fin], env=dict(os.environ, MRZIP="NOCONFIG"), check=True,
                            capture_output=True)
             ar = H.parse_archive(open(fout, "rb").read())
+            fback = os.path.join(d, "back.bin")
+            subprocess.run([small_bin, "-d", "-q", "-f", "-o", fback, fout], env=dict(os.environ, MRZIP="NOCONFIG"), check=True, capture_output=True)
+            assert open(fback, "rb").read() == data.tobytes()
         assert len(ar["chunks"]) == 1 and ar["chunks"][0]["s0"] == want[0]["s0"] and ar["chunks"][0]["s1"] == want[0]["s1"]

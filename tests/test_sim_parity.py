@@ -66,6 +66,11 @@ def test_tagmap_matches_prefix_xor(sim_ctx, kind):
         assert want[: data.size - 30].min() >= 32
 
 
+def test_runzip_rejects_corruption(sim_ctx):
+    from parity_common import check_runzip_rejects_corruption
+    check_runzip_rejects_corruption(sim_ctx)
+
+
 def _sim_ctx(**config):
     """A separate emulator context with its own launch geometry (mrz_config)."""
     import os
