@@ -1692,13 +1692,19 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 if (dbg && j == 0) tm[10] += 1;
                 // ---- the lookup of op k (find_best_match, rzip.c:426-462) by the whole CTA (rank 0): the probe sequence is
                 // walked 4*T slots per step, equal tags are collected in slot order, and the warps share the match_len calls
-                if (rank == 0) {
+                // At the levels with long chains (8, 9: up to 32 / 128 equal tags per lookup, dense repeats) EVERY CTA of the
+                // cluster walks the probe sequence itself - same table, same result - and, when there are more candidates than
+                // one CTA has warps, takes its share of the compares; their results reach rank 0 in one more hop.
+                const bool lead = rank == 0;
+                const bool help = CL > 1 && chain > 2 * (T >> 5);
+                bool many = false;          // uniform over the cluster: the candidates of this lookup are shared out
+                if (lead || help) {
                     int pre_n = -2;   // -2: the filter says no equal tag; -1: ask / walk on the warp; >= 0: candidates compared
                     const i64 c_x0 = clock64();
                     const i64 tk = LDG_(sh->b_tag[k]), pk = LDG_(sh->b_pos[k]);
                     const i64 c_lk0 = clock64();
                     i64 c_lk1 = c_lk0, c_lk2 = c_lk0;
-                    if (dbg && tid == 0) dbg[53] += c_lk0 - c_x0;
+                    if (dbg && lead && tid == 0) dbg[53] += c_lk0 - c_x0;
                     {
                         // ONE round trip: the filter word and the first 4*T slots of the probe sequence, tags and offsets alike
                         const i64 h = tk & hmask;
@@ -1757,7 +1763,43 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                                 const i64 lo_m = w.last > 0 ? w.last : 0;
                                 const i64 maxf = end - pk;
                                 const int NW = T >> 5;
-                                if (n_tot <= NW) {
+                                many = help && n_tot > NW;
+                                if (many) {
+                                    // candidate q belongs to rank q mod CL: its warps compare (up to LK_XCAP2 either side), the
+                                    // whole CTA extends what still matches there, and the result goes to rank 0
+                                    const int mine = rank < n_tot ? (n_tot - rank + CL - 1) / CL : 0;
+                                    for (int i = wid; i < mine; i += NW) {
+                                        const int q = rank + CL * i;
+                                        const i64 off = S->lk_off[q];
+                                        i64 f = 0, r = 0;
+                                        if (off < pk) {
+                                            i64 maxb = pk - lo_m;
+                                            if (off < maxb) maxb = off;
+                                            const i64 mf = maxf < LK_XCAP ? maxf : LK_XCAP, mb = maxb < LK_XCAP ? maxb : LK_XCAP;
+                                            warp_cmp2(buf, pk, off, mf, mb, lane, f, r);
+                                            if (f == LK_XCAP && maxf > LK_XCAP) f += w.extend(pk + LK_XCAP, off + LK_XCAP, (maxf < LK_XCAP2 ? maxf : (i64)LK_XCAP2) - LK_XCAP, true);
+                                            if (r == LK_XCAP && maxb > LK_XCAP) r += w.extend(pk - LK_XCAP, off - LK_XCAP, (maxb < LK_XCAP2 ? maxb : (i64)LK_XCAP2) - LK_XCAP, false);
+                                            __syncwarp();
+                                        }
+                                        if (lane == 0) { S->lk_f[q] = f; S->lk_r[q] = r; }
+                                    }
+                                    __syncthreads();
+                                    for (int i = 0; i < mine; i++) {
+                                        const int q = rank + CL * i;
+                                        const i64 off = S->lk_off[q];
+                                        i64 f = S->lk_f[q], r = S->lk_r[q], m = 0;
+                                        if (off < pk) {
+                                            i64 maxb = pk - lo_m;
+                                            if (off < maxb) maxb = off;
+                                            if (f == LK_XCAP2 && maxf > LK_XCAP2) f += cta_extend(S, buf, pk + LK_XCAP2, off + LK_XCAP2, maxf - LK_XCAP2, true);
+                                            if (r == LK_XCAP2 && maxb > LK_XCAP2) r += cta_extend(S, buf, pk - LK_XCAP2, off - LK_XCAP2, maxb - LK_XCAP2, false);
+                                            m = f + r < MRZ_MIN_MATCH ? 0 : f + r;
+                                        }
+                                        if (tid == 0) { push_to(&S->lk_len[q], 0, m); push_to(&S->lk_rev[q], 0, r); }
+                                    }
+                                } else if (!lead) {
+                                    // (nothing to help with)
+                                } else if (n_tot <= NW) {
                                     // few candidates (the usual case): one after the other, each by the whole CTA, complete
                                     for (int q = 0; q < n_tot; q++) {
                                         const i64 off = S->lk_off[q];
@@ -1828,13 +1870,16 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                             }
                         }
                     }
-                    if (dbg && tid == 0) {
+                    // Every CTA has finished its walk before rank 0's op may change the table (otherwise a slow CTA could see
+                    // the op's own insert and count one candidate more); the shared-out compares arrive by the same barrier.
+                    if (help) csync(CL);
+                    if (dbg && lead && tid == 0) {
                         const i64 c_now = clock64();
                         dbg[18] += c_now - c_lk0; dbg[19] += pre_n != -2;
                         dbg[50] += c_lk1 - c_lk0; dbg[51] += c_lk2 - c_lk1; dbg[52] += c_now - c_lk2;
                     }
                     // ---- op k on the live table, reference semantics (warp 0), on the local replica
-                    if (wid == 0) {
+                    if (lead && wid == 0) {
                         const i64 c_pre0 = clock64();
                         w.load(x.run);
                         w.nlog = 0;
@@ -1888,7 +1933,7 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                     // the result goes into every other replica: one destination CTA per warp (a remote store costs the issuing
                     // warp ~200 clk; one warp pushing to 7 CTAs in turn was 1.5k clk of every exact op).  The write log is the
                     // tail of XRes: only its used part travels - usually one store per lane.
-                    if (CL > 1) {
+                    if (lead && CL > 1) {
                         __syncthreads();
                         const i64 c_pu0 = clock64();
                         const int nwords = (int)((offsetof(XRes, wlog) + 4 * (size_t)(x.nlog > 0 ? x.nlog : 0) + 7) / 8);
