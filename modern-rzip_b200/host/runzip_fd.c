@@ -10,6 +10,7 @@
  */
 #include <errno.h>
 #include <fcntl.h>
+#include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
 #include <sys/stat.h>
@@ -36,6 +37,17 @@ static i64 get_val(const uchar *p, int len) { /* read_val, stream.c:556-564: lit
     i64 v = 0;
     for (int i = 0; i < len; i++) v |= (i64)p[i] << (8 * i);
     return v;
+}
+
+struct md5_span {
+    md5_ctx *ctx;
+    const uchar *p;
+    i64 len;
+};
+static void *md5_span_thread(void *arg) {
+    struct md5_span *s = arg;
+    md5_update(s->ctx, s->p, (size_t)s->len);
+    return NULL;
 }
 
 struct strm {
@@ -136,6 +148,10 @@ i64 runzip_fd(rzip_control *control, int fd_in, int fd_out, i64 first_chunk, i64
         int rc = mrz_runzip_chunk(ctx, st[0].buf, st[0].len, st[1].buf, st[1].len, wl, out, out_cap, &r);
         if (rc) fatal(control, "%s\n", mrz_last_error(ctx)); /* "Bad checksum: 0x.. - expected: 0x.." (runzip.c:319) / corrupt archive */
         if (MAX_VERBOSE) fprintf(stderr, "Checksum for block: 0x%08x\n", r.crc32); /* runzip.c:321 */
+        /* the MD5 chain of this chunk runs beside its write(2) (both only read `out`) */
+        struct md5_span span = {&md5, out, r.out_len};
+        pthread_t th;
+        const int hashing = has_md5 && r.out_len > (1 << 20) && !pthread_create(&th, NULL, md5_span_thread, &span);
         for (i64 o = 0; o < r.out_len;) { /* write_1g */
             i64 n = r.out_len - o > (1 << 30) ? (1 << 30) : r.out_len - o;
             ssize_t w = write(fd_out, out + o, (size_t)n);
@@ -143,7 +159,10 @@ i64 runzip_fd(rzip_control *control, int fd_in, int fd_out, i64 first_chunk, i64
             if (w <= 0) fatal(control, "Failed to write %lld bytes of the chunk\n", (long long)n);
             o += w;
         }
-        if (has_md5) md5_update(&md5, out, (size_t)r.out_len);
+        if (hashing)
+            pthread_join(th, NULL);
+        else if (has_md5)
+            md5_update(&md5, out, (size_t)r.out_len);
         total += r.out_len;
         gpu_ms += r.ms_kernels;
         launches += r.gpu_launches;
