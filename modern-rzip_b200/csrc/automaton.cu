@@ -1338,12 +1338,19 @@ k_automaton(const AutoDesc *__restrict__ descs) {
         const i64 gbase = lo & ~((i64)s - 1);
         const i64 a = gbase + (i64)j * s;
         int nr;
+        i64 n_ins_batch = 0;         // candidates of this batch that pass the insert gate: an upper bound on its sweep steps
         {
-            int cnt = 0;
-            span_candidates(bmap, bsum, a, s, kgate, lo, end, nblocks, [&](i64) { cnt++; return true; });
+            // (the same sum also counts the candidates that pass the INSERT gate - the map byte tells: only those can make
+            // the sweep move, which bounds how far it gets within this batch, see s_safe below)
+            int cnt = 0, icnt = 0;
+            const int kins = __popcll((u64)ins_mask);
+            span_candidates(bmap, bsum, a, s, kgate, lo, end, nblocks, [&](i64 pos) { cnt++; icnt += (int)__ldg(bmap + pos) >= kins; return true; });
             if (tid == 0) S->lgp = 0x7fffffffffffffffLL;
             unsigned long long total;
-            unsigned long long at = cluster_excl_scan((unsigned long long)cnt, S, 1, CL, rank, total, NoExtra());
+            unsigned long long at = cluster_excl_scan((unsigned long long)cnt | ((unsigned long long)icnt << 32), S, 1, CL, rank, total, NoExtra());
+            n_ins_batch = (i64)(total >> 32);
+            total &= 0xffffffffULL;
+            at &= 0xffffffffULL;
             if (cnt) {
                 i64 drop = -1;
                 span_candidates(bmap, bsum, a, s, kgate, lo, end, nblocks, [&](i64 pos) {
@@ -1425,6 +1432,7 @@ k_automaton(const AutoDesc *__restrict__ descs) {
         const i64 dbg_nops0 = x.run.nops;   // emulator build: every op of the batch is accounted for exactly once
         int dbg_done = 0, dbg_skip = 0;
 #endif
+        const i64 ins_at_start = x.run.inserts;
         int qacc = 0x7fffffff;       // smallest ring slot a committed plan overwrote (the ring is cut there at the end of the batch)
         i64 w_lo = x.run.clean_ptr, w_hi = steady ? x.e_scan : w_lo, s_safe = w_lo - 1;
         unsigned long long incl = 0;
@@ -1465,7 +1473,10 @@ k_automaton(const AutoDesc *__restrict__ descs) {
                 }
                 w_lo = x.run.clean_ptr; w_hi = steady ? x.e_scan : w_lo; s_safe = w_lo - 1;
                 if (steady && w_hi > w_lo) {
-                    const unsigned ei = x.e_idx, ec = x.e_cnt, reach = (unsigned)(nr - pos);
+                    // at most one sweep step per op that is still to run - and only an op that inserts can cause one
+                    i64 ins_left = n_ins_batch - (x.run.inserts - ins_at_start);
+                    if (ins_left < 0) ins_left = 0;
+                    const unsigned ei = x.e_idx, ec = x.e_cnt, reach = (unsigned)(ins_left < (i64)(nr - pos) ? ins_left : (i64)(nr - pos));
                     s_safe = (ec - ei > reach) ? (i64)LDG_(sh->E[(ei + reach) & (MRZ_EQ_CAP - 1)]) : w_hi - 1;
                 }
                 if (epoch + 4 * FWD_ITERS + 16 >= CLAIM_EPOCH_MAX) {   // claim keys nearly exhausted: wipe the arrays, restart the epochs
