@@ -805,6 +805,20 @@ extern "C" int mrz_runzip_chunk(mrz_ctx *ctx, const uint8_t *s0, int64_t s0_len,
         pos += len;
         if (pos > ctx->max_chunk) { ctx->err = "the streams describe a chunk larger than this context"; return MRZ_E_CAPACITY; }
     }
+#ifdef MRZ_CUSIM
+    // emulator build (its CTAs run one after the other, which would hide a wrong wave): no match of a wave may read a byte
+    // that another match of the same wave writes - checked against every pair
+    for (size_t w = 0; w < wave_first.size(); w++) {
+        const i64 a = wave_first[w], b = w + 1 < wave_first.size() ? wave_first[w + 1] : (i64)mats.size();
+        for (i64 p = a; p < b; p++)
+            for (i64 q = a; q < b; q++) {
+                if (p == q) continue;
+                const UnzipItem &rd = mats[(size_t)p], &wr = mats[(size_t)q];
+                const i64 ofs = rd.dst - rd.src, rd_hi = rd.src + (rd.len < ofs ? rd.len : ofs);
+                if (rd.src < wr.dst + wr.len && wr.dst < rd_hi) { fprintf(stderr, "unzip: wave %zu holds dependent matches %lld and %lld\n", w, (long long)p, (long long)q); abort(); }
+            }
+    }
+#endif
     if (!ended || i + 4 > s0_len) { ctx->err = "stream 0 ends without terminator and checksum"; return MRZ_E_DATA; }
     if (j != s1_len) { ctx->err = "stream 1 is longer than the literal headers say"; return MRZ_E_DATA; }
     const u32 stored = ((u32)s0[i] << 24) | ((u32)s0[i + 1] << 16) | ((u32)s0[i + 2] << 8) | (u32)s0[i + 3];   // rzip.c:662-665

@@ -101,3 +101,39 @@ def check_runzip_rejects_corruption(ctx):
         ctx.runzip_chunk(s0, s1, cb, data.size - 1)
     _, back = ctx.runzip_chunk(s0, s1, cb, data.size)   # the context is still good
     assert back.tobytes() == data.tobytes()
+
+
+def synthetic_streams(seed, n_tokens, cb=3, max_lit=300, max_len=500, max_ofs=600):
+    """Stream 0 / stream 1 of a made-up chunk with many short, overlapping and chained matches (what the encoder rarely
+    emits), and the chunk they describe (byte-wise replay, runzip.c:159-207)."""
+    import zlib
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    out = bytearray()
+    s0 = bytearray()
+    s1 = bytearray()
+    for _ in range(n_tokens):
+        if not out or rng.random() < 0.4:
+            ln = int(rng.integers(1, max_lit))
+            lit = rng.integers(0, 256, size=ln, dtype=np.uint8).tobytes()
+            s0 += bytes([0, ln & 255, ln >> 8])
+            s1 += lit
+            out += lit
+        else:
+            ln = int(rng.integers(1, max_len))
+            ofs = int(rng.integers(1, min(len(out), max_ofs) + 1))
+            s0 += bytes([1, ln & 255, ln >> 8]) + ofs.to_bytes(cb, "little")
+            start = len(out) - ofs
+            for i in range(ln):                      # byte-wise forward copy: overlaps repeat
+                out.append(out[start + i])
+    crc = zlib.crc32(bytes(out)) & 0xffffffff
+    s0 += bytes([0, 0, 0]) + crc.to_bytes(4, "big")
+    return np.frombuffer(bytes(s0), dtype=np.uint8), np.frombuffer(bytes(s1), dtype=np.uint8), bytes(out)
+
+
+def check_runzip_synthetic(ctx, seeds=(1, 2, 3), n_tokens=3000):
+    for seed in seeds:
+        s0, s1, want = synthetic_streams(seed, n_tokens)
+        res, back = ctx.runzip_chunk(s0, s1, 3, len(want))
+        assert back.tobytes() == want, "seed %d" % seed
+        assert res.waves > 10 and res.matches > n_tokens // 3     # chained matches really split into waves

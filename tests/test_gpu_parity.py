@@ -180,3 +180,9 @@ def test_runzip_rejects_corruption(gpu_ctx):
     through it: parity_common.check)."""
     from parity_common import check_runzip_rejects_corruption
     check_runzip_rejects_corruption(gpu_ctx)
+
+
+def test_runzip_synthetic_streams(gpu_ctx):
+    """Made-up token streams with chained and self-overlapping matches: the wave rule of mrz_runzip_chunk."""
+    from parity_common import check_runzip_synthetic
+    check_runzip_synthetic(gpu_ctx, seeds=(1, 2, 3, 4, 5), n_tokens=20000)

@@ -71,6 +71,12 @@ def test_runzip_rejects_corruption(sim_ctx):
     check_runzip_rejects_corruption(sim_ctx)
 
 
+def test_runzip_synthetic_streams(sim_ctx):
+    """Made-up token streams with chained and self-overlapping matches: the wave rule of mrz_runzip_chunk."""
+    from parity_common import check_runzip_synthetic
+    check_runzip_synthetic(sim_ctx)
+
+
 def _sim_ctx(**config):
     """A separate emulator context with its own launch geometry (mrz_config)."""
     import os
