@@ -21,6 +21,12 @@ sys.path.insert(0, ROOT)
 GPU_BIN = os.path.join(ROOT, "modern-rzip_b200", "mrzip")
 GOLD = json.load(open(os.path.join(H.GOLDEN, "fullsize_vectors.json")))
 pytestmark = pytest.mark.gpu
+# The whole GPU suite has to fit the 20-minute window of the round-end run.  Two of the three 32 GiB cases (3-4 minutes
+# each, mostly generating and hashing 32 GiB) therefore run only on request; they passed on the B200 in round 2
+# (profiles/r2_gpu_tests_full_earlier_build.log), and `bench.py --workload vm32 --window 41` / `bench.py --gpus N` check
+# the same archives / streams against the same golden vectors on every run (profiles/r2_bench_vm32_w41_*.json,
+# r2_bench_tar_*gpu.json).  The 33-chunk case stays in the default suite.
+all_32g = pytest.mark.skipif(not os.environ.get("MRZ_TEST_32G_ALL"), reason="set MRZ_TEST_32G_ALL=1 for every 32 GiB case (adds ~8 minutes)")
 
 
 def blake2b_file(path):
@@ -101,6 +107,7 @@ def test_config4_dense_16gib_R9_archive_equals_reference():
     run_case("dense16g_R9")
 
 
+@all_32g
 def test_config2_vm_32gib_w41_one_gpu_archive_equals_reference():
     """configs[2]: 32 GiB VM-image-like, `-w 41` -> 8 chunks; chunks in flight side by side, each searched for all 16
     values of victim_round_in, the chain resolved on the host (rzip_fd.c)."""
@@ -115,6 +122,7 @@ def test_config2_vm_32gib_w10_all_gpus_archive_equals_reference():
     run_case("vm32g_w10", extra=("-g", ",".join(str(i) for i in range(max(1, n))), "-G", "4"))
 
 
+@all_32g
 def test_tar_32gib_w41_archive_equals_reference():
     """bench.py's multi-GPU weak-scaling input: 8 tar-like pieces of one `-w 41` chunk each."""
     if "tar32g_w41" not in GOLD:
