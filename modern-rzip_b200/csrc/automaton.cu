@@ -238,7 +238,8 @@ extern "C" size_t mrz_automaton_smem_bytes() { return sizeof(Smem); }
 static bool g_selfcheck_on = false;
 static int g_selfcheck_failures = 0;
 static unsigned g_selfcheck_tick = 0;
-extern "C" void mrz_sim_selfcheck(int on) { g_selfcheck_on = on != 0; g_selfcheck_failures = 0; }
+static unsigned g_selfcheck_mask = 63;      // mrz_sim_selfcheck(1): every 64th batch; (2): every batch
+extern "C" void mrz_sim_selfcheck(int on) { g_selfcheck_on = on != 0; g_selfcheck_mask = on >= 2 ? 0 : 63; g_selfcheck_failures = 0; }
 extern "C" int mrz_sim_selfcheck_failures() { return g_selfcheck_failures; }
 #define MRZ_SMEM_PTR(T, name) T *name = reinterpret_cast<T *>(cusim::dyn_smem())
 #else
@@ -1306,7 +1307,10 @@ k_automaton(const AutoDesc *__restrict__ descs) {
         // ================================================================ sweep ring
         if (steady) refill_queue(sh, S, ttag, btm, hsize, B, CL, rank, j, B);
 #ifdef MRZ_CUSIM
-        if (j == 0 && g_selfcheck_on && (g_selfcheck_tick++ & 63) == 0) {   // emulator self-check (every 64th batch): hash_count and the ring against the table itself
+        // (the ring entries of the refill just made are read by other CTAs only behind the next cluster barrier - the gather's
+        // prefix sum; the check reads them right here and needs that barrier itself)
+        if (g_selfcheck_on) csync(CL);
+        if (j == 0 && g_selfcheck_on && (g_selfcheck_tick++ & g_selfcheck_mask) == 0) {   // emulator self-check (every 64th batch): hash_count and the ring against the table itself
             i64 used = 0;
             for (i64 sl = 0; sl < hsize; sl++) used += ttag[sl] != 0 || toff[sl] != 0;
             if (used != x.run.count) {
