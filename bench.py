@@ -14,14 +14,19 @@ Default workload (`--workload tar`):
         (chunk, vr_in) -> vr_out table, every rank walks the chain and emits the variant it selects.  No chunk waits
         for another one's search and none is searched twice.
 Other workloads (lines kept under profiles/):
-  --workload vm32 [--window 41|10]   configs[2]: the 32 GiB VM-image-like input, its chunks dealt round-robin to the
-                                     N ranks (strong scaling), all variants, one all-gather per step
+  --workload vm32 [--window 41|10]   configs[2]: the 32 GiB VM-image-like input through the product's C host
+                                     (`mrzip -n -g 0,..,N-1`: ONE process drives the N GPUs, strong scaling), wall
+                                     clock of the process, archive compared with the reference's (SHA-256)
+  --case NAME                        a golden single-chunk case of tests/fullsize_cases.py (random8g, vm4g, dense4g_R9, ...)
   --workload vm|random|dense --size BYTES [--level L]   one chunk of another data kind (configs[3]: random 8 GiB;
                                      configs[4]: dense 16 GiB --level 9)
   --independent --chunks-per-gpu C   C independent inputs resident per GPU, all their automata in ONE launch
-Prints ONE JSON line (rank 0).  `value` = device-resident throughput; `e2e` = the same with the host<->device copies of
-the step's inputs and streams inside the timed region (pinned host buffers, through the C-ABI).  Once per run, outside
-the timed region, the streams are compared with the reference's (SHA-256 per chunk): "parity_checked".
+Prints ONE JSON line (rank 0).  `value` = device-resident throughput (tag map, CRC, automaton and emission every step);
+`e2e` = the same with the host<->device copies of the step's inputs and streams inside the timed region (pinned host
+buffers, through the C-ABI); at N=1 also `e2e_cli` (wall clock of `mrzip -n`, file -> archive) and `cpu_baseline` (the
+unmodified reference on a bounded sample).  `--impl reference`: the unmodified reference binary on the WHOLE chunk, plus
+the labelled k-processes-on-k-cores figure.  Once per run, outside the timed region, the streams are compared with the
+reference's (SHA-256 per chunk): "parity_checked".
 """
 import argparse
 import json
