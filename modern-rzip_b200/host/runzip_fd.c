@@ -86,10 +86,12 @@ static i64 read_chunk_streams(rzip_control *control, int fd, i64 pos, i64 file_e
         pread_all(control, fd, h, hdr, base + s * hdr, "a stream header");
         if (h[0] != CTYPE_NONE || get_val(h + 1, wl) || get_val(h + 1 + wl, wl))
             fatal(control, "Unexpected initial tag %d in streams: this build reads rzip-only (-n) archives\n", h[0]); /* stream.c:1046 */
-        i64 next = get_val(h + 1 + 2 * wl, wl);
+        i64 next = get_val(h + 1 + 2 * wl, wl), last_at = base;
         while (next) {
             const i64 at = base + next;
             if (at + hdr > file_end) fatal(control, "Invalid data: a block header lies beyond the end of the archive\n");
+            if (at <= last_at) fatal(control, "Invalid data: the block chain of a stream goes backwards\n"); /* blocks are appended: no cycles */
+            last_at = at;
             pread_all(control, fd, h, hdr, at, "a block header");
             const i64 c_len = get_val(h + 1, wl), u_len = get_val(h + 1 + wl, wl);
             if (h[0] != CTYPE_NONE) fatal(control, "Block with compression type %d: this build reads rzip-only (-n) archives\n", h[0]);

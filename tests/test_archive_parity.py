@@ -126,6 +126,32 @@ def test_sim_decode_refuses_a_damaged_archive(sim_bin):
         assert p.returncode != 0 and "MD5 CHECK FAILED" in p.stderr
 
 
+def test_sim_decode_survives_damaged_headers(sim_bin):
+    """One damaged byte anywhere in the container / chunk / block headers: `mrzip -d` either still gives the input back (a
+    byte that does not matter, e.g. the stored levels) or stops with an error - it never hangs, crashes or writes wrong data
+    silently."""
+    data = H.gen_random_repeats(200000, 6, lo=2048, hi=8192)
+    want = H.as_u8(data).tobytes()
+    with tempfile.TemporaryDirectory() as d:
+        fin = os.path.join(d, "in.bin")
+        H.as_u8(data).tofile(fin)
+        raw = run(sim_bin, fin, os.path.join(d, "o.mar"))
+        env = dict(os.environ, MRZIP="NOCONFIG")
+        refused = 0
+        for pos in list(range(0, 70)) + [len(raw) - 17, len(raw) - 16]:
+            bad = bytearray(raw)
+            bad[pos] ^= 0x5a
+            fbad, fout = os.path.join(d, "bad.mar"), os.path.join(d, "bad.out")
+            open(fbad, "wb").write(bad)
+            p = subprocess.run([sim_bin, "-d", "-q", "-f", "-o", fout, fbad], env=env, capture_output=True, text=True, timeout=60)
+            assert p.returncode in (0, 1), "byte %d: killed by a signal (%d)\n%s" % (pos, p.returncode, p.stderr[-500:])
+            if p.returncode == 0:
+                assert open(fout, "rb").read() == want, "byte %d: wrong output accepted" % pos
+            else:
+                refused += 1
+        assert refused > 20
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", ["survey650", "pattern0", "motif_R1", "vm_like_L9", "tar_like"])
 def test_gpu_archive_equals_golden(name):
