@@ -27,9 +27,10 @@ def sim_ctx():
     import mrz_py
     d = os.path.join(ROOT, "tests", "cusim")
     subprocess.check_call(["make", "-C", d, "libmrz_sim.so"], stdout=subprocess.DEVNULL)
-    # a cluster of 2 CTAs x 64 threads per automaton; every work buffer starts poisoned (0xA5), not zeroed
+    # a cluster of 2 CTAs x 64 threads per automaton (MRZ_SIM_GEOMETRY=CLxT overrides); every work buffer starts poisoned (0xA5), not zeroed
     lib = mrz_py.bind(os.path.join(d, "libmrz_sim.so"))
     lib.mrz_sim_selfcheck(1)    # per batch: hash_count and the sweep ring are compared with the table itself (parity_common.check asserts)
-    ctx = mrz_py.Context(0, 1 << 26, library=lib, cluster_size=2, threads=64, poison=1)
+    cl, t = (int(x) for x in os.environ.get("MRZ_SIM_GEOMETRY", "2x64").split("x"))   # soak runs: another cluster shape
+    ctx = mrz_py.Context(0, 1 << 26, library=lib, cluster_size=cl, threads=t, poison=1)
     yield ctx
     ctx.close()

@@ -2,6 +2,8 @@
 differently - random bytes, short periods (self-overlapping matches), copied spans, runs - at random sizes around the
 31-byte minimum match and around batch / tile boundaries, random level and victim_round_in: streams, counters and the
 carried state equal the oracle's, and the device replay gives the input back (tests/parity_common.check)."""
+import os
+
 import numpy as np
 from hypothesis import HealthCheck, given, settings, strategies as st
 
@@ -35,7 +37,7 @@ def textured(draw):
     return buf
 
 
-@settings(max_examples=200, deadline=None, derandomize=True, suppress_health_check=list(HealthCheck))
+@settings(max_examples=int(os.environ.get("MRZ_PROPERTY_EXAMPLES", "200")), deadline=None, derandomize=True, suppress_health_check=list(HealthCheck))
 @given(data=textured(), level=st.integers(0, 9), vr=st.integers(0, 127))
 def test_textured_inputs_match_the_oracle_and_round_trip(sim_ctx, data, level, vr):
     import mrz_py
